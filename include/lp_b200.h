@@ -1,0 +1,107 @@
+/*
+ * include/lp_b200.h -- C ABI of liblp_b200.so, the B200 (sm_100a) dense LP engine.
+ *
+ * This is the drop-in boundary for the ONE hot path of aakarsh/linear_programming:
+ *   - the two-phase tableau simplex   week-2/diet/simplex.py:163-660
+ *     (the solver the course stubs week-2/ad_allocation/ad_allocation.cpp:9-19 and
+ *      week-2/diet/diet.cc:10-15 are meant to contain), and
+ *   - the Gauss-Jordan elimination    week-2/energy_values/energy_values.cc:85-197.
+ *
+ * Conventions (all entry points)
+ *   - extern "C", plain pointers and sizes, no C++/torch types; never throws.
+ *   - Return value: 0 = ok, negative = error (LPB200_E_*); lpb200_last_error() returns a
+ *     thread-local message for the last failing call on this thread.
+ *   - Naming follows the reference: n = number of constraints (rows of A), m = number of
+ *     variables (columns of A); A row-major [n][m], b[n], c[m]; maximise c.x s.t. Ax <= b, x >= 0.
+ *   - "_device" entry points take DEVICE pointers on the current CUDA device and enqueue
+ *     on `stream` (a cudaStream_t passed as void*, NULL = default stream) without
+ *     synchronising; the caller owns every buffer.  Entry points without that suffix take
+ *     HOST pointers, copy in, run, copy out and synchronise (the end-to-end path).
+ *   - Per-problem outcome codes (status[]): the reference's anst values plus the classes in
+ *     which the reference itself does not return:
+ */
+#ifndef LP_B200_H
+#define LP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LPB200_STATUS_BOUNDED 0              /* simplex.py:608,626  "Bounded solution" */
+#define LPB200_STATUS_NO_SOLUTION (-1)       /* simplex.py:614,630  "No solution"      */
+#define LPB200_STATUS_INFINITY 1             /* simplex.py:611,628  "Infinity"         */
+#define LPB200_STATUS_ITERATION_LIMIT 2      /* max_pivots reached (the reference has no cap) */
+#define LPB200_STATUS_REF_ATTRIBUTE_ERROR 3  /* reference raises AttributeError, simplex.py:626 */
+#define LPB200_STATUS_REF_INDEX_ERROR 4      /* reference raises IndexError, simplex.py:541->183 */
+#define LPB200_STATUS_REF_TYPE_ERROR 5       /* reference raises TypeError, simplex.py:409 */
+
+#define LPB200_E_INVALID (-1)     /* bad argument */
+#define LPB200_E_CUDA (-2)        /* CUDA runtime error (message has the cudaError string) */
+#define LPB200_E_NO_DEVICE (-3)   /* no CUDA device / driver: there is NO CPU fallback */
+#define LPB200_E_TOO_LARGE (-4)   /* problem does not fit the requested mode */
+
+/* Library / device probes (never touch the GPU unless stated). */
+const char *lpb200_version(void);
+const char *lpb200_last_error(void);
+int lpb200_device_count(void); /* cudaGetDeviceCount; <= 0 means the engine cannot run */
+
+/* Largest problem the one-CTA-per-LP kernel can hold in shared memory: returns the dynamic
+ * shared memory (bytes) the kernel needs for an n x m LP; > 232448 (227 KB) does not fit. */
+int64_t lpb200_simplex_batch_smem_bytes(int n, int m);
+
+/*
+ * Batched simplex: B independent LPs of one shape, one CTA per LP, tableau resident in
+ * shared memory, persistent CTAs pulling problems off a device work queue.
+ * Replaces, per problem, Simplex(A,b,c,n,m).solve()            simplex.py:496-505, 586-630
+ * i.e. the body of allocate_ads(n,m,A,b,c)                     ad_allocation.cpp:9-19
+ *      and solve_diet_problem(n,m,A,b,c)                       diet.cc:10-15.
+ *   A[B][n][m], b[B][n], c[B][m]    inputs
+ *   tol                              global_tolerance, simplex.py:16 (default 1e-9)
+ *   max_pivots                       cap on pivots per LP (incl. the forced phase-1 pivot)
+ *   status[B]                        outcome code
+ *   x[B][m]                          assignment (zeros unless status == 0), simplex.py:603,622
+ *   objective[B]                     optimum (simplex.py:600,620), 0 unless status == 0
+ *   npivots[B]                       pivots performed
+ *   pivot_log[B][log_cap][2]         nullable; (entering, leaving) variable ids per pivot
+ */
+int lpb200_simplex_batch_device(int B, int n, int m, const double *A, const double *b, const double *c,
+                                double tol, int max_pivots, int32_t *status, double *x,
+                                double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap,
+                                void *stream);
+int lpb200_simplex_batch(int B, int n, int m, const double *A, const double *b, const double *c,
+                         double tol, int max_pivots, int32_t *status, double *x, double *objective,
+                         int32_t *npivots, int32_t *pivot_log, int log_cap);
+
+/*
+ * Single large LP, grid-wide: the condensed tableau lives in HBM and every pivot is one
+ * streaming sweep over it by all SMs (cooperative persistent kernel).  Same semantics and
+ * outputs as one problem of the batch call.  `workspace` is a device buffer of at least
+ * lpb200_simplex_single_workspace_bytes(n, m) bytes (the tableau plus small vectors).
+ * stats[0] = kernel milliseconds (CUDA events), stats[1] = pivots (nullable, host memory).
+ */
+int64_t lpb200_simplex_single_workspace_bytes(int n, int m);
+int lpb200_simplex_single_device(int n, int m, const double *A, const double *b, const double *c,
+                                 double tol, int max_pivots, int32_t *status, double *x,
+                                 double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap,
+                                 void *workspace, int64_t workspace_bytes, void *stream);
+int lpb200_simplex_single(int n, int m, const double *A, const double *b, const double *c, double tol,
+                          int max_pivots, int32_t *status, double *x, double *objective,
+                          int32_t *npivots, int32_t *pivot_log, int log_cap, double *stats);
+
+/*
+ * Batched Gauss-Jordan: B independent n x n systems a.x = b.
+ * Replaces, per system, SolveEquation(Equation{a,b})           energy_values.cc:166-197.
+ *   a[B][n][n], b[B][n]  inputs (not modified);  x[B][n]  solution (b after the last step).
+ * `workspace`: device buffer of lpb200_gauss_jordan_workspace_bytes(B, n) bytes (may be 0).
+ */
+int64_t lpb200_gauss_jordan_workspace_bytes(int B, int n);
+int lpb200_gauss_jordan_batch_device(int B, int n, const double *a, const double *b, double *x,
+                                     void *workspace, int64_t workspace_bytes, void *stream);
+int lpb200_gauss_jordan_batch(int B, int n, const double *a, const double *b, double *x);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LP_B200_H */

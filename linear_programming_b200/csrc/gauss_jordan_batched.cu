@@ -1,0 +1,234 @@
+// gauss_jordan_batched.cu -- batched Gauss-Jordan elimination, one CTA per system (sm_100a).
+//
+// Replaces SolveEquation(Equation{a,b}) of week-2/energy_values/energy_values.cc:166-197:
+//   SelectPivotElement :85-114  step k pivots on (k,k); on an EXACT zero swap with the first
+//                               lower row holding a non-zero in column k; none -> carry on
+//   ProcessPivotElement :132-159  row k /= a[k][k] (division per element); every other row i:
+//                               a[i][j] += (-a[i][k]) * a[k][j], b likewise (mul and add
+//                               rounded separately -- the reference is built without FMA)
+//
+// B200 design.  A step-by-step sweep would stream the whole 2 MB system through HBM 512
+// times (1.08 GB/system).  Instead the elimination is PANEL-BLOCKED without
+// changing a single rounding: for a panel of K = 16 consecutive pivots
+//   1. the n x K panel is factorised in shared memory (K tiny steps), leaving in place the
+//      scale s[i][k] = -a[i][k] every row used at step k and the pivot value of row k;
+//   2. every trailing column j (and b) is then read ONCE, taken through the K updates in the
+//      reference's order in registers -- a = a + s[i][k]*r[k][j], k ascending, product and sum
+//      rounded separately, the pivot rows resolved first by a K x K triangular pass -- and
+//      written ONCE.
+// Each element sees exactly the operations, operands and order of the reference, so x is
+// bit-identical, while HBM traffic drops K-fold (67 MB/system at n = 512) and the kernel is
+// bound by the fp64 pipe instead of HBM.  Columns left of the current pivot are never
+// touched (they are exact zeros the reference only rewrites with zeros).
+// A zero pivot met inside a panel truncates the panel there; the swap happens in global
+// memory at the start of the next panel.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "lp_common.cuh"
+#include "lp_host.h"
+
+namespace lpb {
+
+constexpr int kGjK = 16;            // pivots per panel
+constexpr int kGjPS = kGjK + 2;     // panel row stride in shared memory (16-byte aligned rows)
+constexpr int kGjThreads = 512;
+
+// a: [B][n][n] working copy (destroyed), x: [B][n] holds b on entry and the solution on exit.
+__global__ void __launch_bounds__(kGjThreads, 2)
+gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restrict__ x_all)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    double *P = reinterpret_cast<double *>(smem);                 // [n][kGjPS]
+    int *flag = reinterpret_cast<int *>(P + (size_t)n * kGjPS);   // [2]
+    const int tid = threadIdx.x;
+    double *a = a_all + (size_t)blockIdx.x * n * n;
+    double *bx = x_all + (size_t)blockIdx.x * n;
+
+    for (int k0 = 0; k0 < n;) {
+        const int K = min(kGjK, n - k0);
+        // ---- SelectPivotElement for step k0, on the up-to-date matrix in global memory ----
+        if (tid == 0) {
+            int sw = -1;
+            if (a[(size_t)k0 * n + k0] == 0.0) {
+                sw = k0;
+                while (sw < n && a[(size_t)sw * n + k0] == 0.0) ++sw;
+                if (sw >= n) sw = -1;  // the reference carries on and divides by zero
+            }
+            flag[0] = sw;
+        }
+        __syncthreads();
+        const int sw = flag[0];
+        if (sw > k0) {  // std::swap(a[k0], a[sw]); std::swap(b[k0], b[sw])  (:106-109)
+            for (int j = k0 + tid; j <= n; j += kGjThreads) {
+                double *p0 = (j < n) ? &a[(size_t)k0 * n + j] : &bx[k0];
+                double *p1 = (j < n) ? &a[(size_t)sw * n + j] : &bx[sw];
+                const double t = *p0;
+                *p0 = *p1;
+                *p1 = t;
+            }
+            __syncthreads();
+        }
+        // ---- load the n x K panel ----
+        for (int idx = tid; idx < n * K; idx += kGjThreads) {
+            const int i = idx / K, q = idx - i * K;
+            P[(size_t)i * kGjPS + q] = a[(size_t)i * n + k0 + q];
+        }
+        __syncthreads();
+        // ---- factorise the panel in shared memory ----
+        int Kp = K;
+        for (int q = 0; q < K; ++q) {
+            const int k = k0 + q;
+            const double value = P[(size_t)k * kGjPS + q];
+            if (q > 0 && value == 0.0) {  // needs a row swap: finish this panel at q pivots
+                Kp = q;
+                break;
+            }
+            // scale the pivot row (division per element, :143-145)
+            if (tid > q && tid < K) P[(size_t)k * kGjPS + tid] = __ddiv_rn(P[(size_t)k * kGjPS + tid], value);
+            __syncthreads();
+            for (int i = tid; i < n; i += kGjThreads) {
+                if (i == k) continue;
+                double *Pi = P + (size_t)i * kGjPS;
+                const double s = -Pi[q];  // scale = -1 * a[i][k]  (:151)
+                for (int t = q + 1; t < K; ++t)
+                    Pi[t] = __dadd_rn(Pi[t], __dmul_rn(s, P[(size_t)k * kGjPS + t]));
+                Pi[q] = s;  // keep the scale for the trailing update
+            }
+            __syncthreads();
+        }
+        // ---- trailing update: columns k0+Kp .. n-1 and b (column index n) ----
+        for (int j = k0 + Kp + tid; j <= n; j += kGjThreads) {
+            double *col = (j < n) ? (a + j) : bx;
+            const size_t cs = (j < n) ? (size_t)n : 1;  // element stride down the column
+            double R[kGjK];
+            // pivot rows: updates by earlier pivots of the panel, then the division
+#pragma unroll
+            for (int q = 0; q < kGjK; ++q) {
+                if (q < Kp) {
+                    const double *Pk = P + (size_t)(k0 + q) * kGjPS;
+                    double v = col[(size_t)(k0 + q) * cs];
+#pragma unroll
+                    for (int t = 0; t < q; ++t) v = __dadd_rn(v, __dmul_rn(Pk[t], R[t]));
+                    R[q] = __ddiv_rn(v, Pk[q]);
+                } else {
+                    R[q] = 0.0;
+                }
+            }
+            // pivot rows: eliminated by the later pivots of the panel (Gauss-JORDAN)
+#pragma unroll
+            for (int q = 0; q < kGjK; ++q) {
+                if (q < Kp) {
+                    const double *Pk = P + (size_t)(k0 + q) * kGjPS;
+                    double v = R[q];
+#pragma unroll
+                    for (int t = q + 1; t < kGjK; ++t)
+                        if (t < Kp) v = __dadd_rn(v, __dmul_rn(Pk[t], R[t]));
+                    col[(size_t)(k0 + q) * cs] = v;
+                }
+            }
+            // every other row: Kp updates in the reference's order, one read, one write
+#pragma unroll 2
+            for (int i = 0; i < n; ++i) {
+                if (i >= k0 && i < k0 + Kp) continue;
+                const double *Pi = P + (size_t)i * kGjPS;
+                double v = col[(size_t)i * cs];
+                if (Kp == kGjK) {
+#pragma unroll
+                    for (int t = 0; t < kGjK; t += 2) {
+                        const double2 s2 = *reinterpret_cast<const double2 *>(Pi + t);
+                        v = __dadd_rn(v, __dmul_rn(s2.x, R[t]));
+                        v = __dadd_rn(v, __dmul_rn(s2.y, R[t + 1]));
+                    }
+                } else {
+#pragma unroll
+                    for (int t = 0; t < kGjK; ++t)
+                        if (t < Kp) v = __dadd_rn(v, __dmul_rn(Pi[t], R[t]));
+                }
+                col[(size_t)i * cs] = v;
+            }
+        }
+        __syncthreads();
+        k0 += Kp;
+    }
+}
+
+}  // namespace lpb
+
+using namespace lpb;
+
+extern "C" int64_t lpb200_gauss_jordan_workspace_bytes(int B, int n)
+{
+    if (B < 0 || n < 0) return 0;
+    return (int64_t)B * n * n * 8;
+}
+
+extern "C" int lpb200_gauss_jordan_batch_device(int B, int n, const double *a, const double *b, double *x,
+                                                void *workspace, int64_t workspace_bytes, void *stream_v)
+{
+    if (B < 0 || n < 0) {
+        set_error("lpb200_gauss_jordan_batch: need B >= 0 and n >= 0");
+        return LPB200_E_INVALID;
+    }
+    if (B == 0 || n == 0) return 0;  // size 0 prints nothing (week-2/energy_values/tests/01)
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    DeviceInfo di;
+    int rc = get_device_info(&di);
+    if (rc) return rc;
+    const int smem = n * kGjPS * 8 + 16;
+    if (smem > di.max_smem_optin) {
+        set_error("lpb200_gauss_jordan_batch: n too large for the shared-memory panel (n <= " +
+                  std::to_string((di.max_smem_optin - 16) / (kGjPS * 8)) + ")");
+        return LPB200_E_TOO_LARGE;
+    }
+    if (workspace == nullptr || workspace_bytes < lpb200_gauss_jordan_workspace_bytes(B, n)) {
+        set_error("lpb200_gauss_jordan_batch: workspace too small");
+        return LPB200_E_INVALID;
+    }
+    double *wa = static_cast<double *>(workspace);
+    LPB_CUDA(cudaMemcpyAsync(wa, a, (size_t)B * n * n * 8, cudaMemcpyDeviceToDevice, stream));
+    if (x != b) LPB_CUDA(cudaMemcpyAsync(x, b, (size_t)B * n * 8, cudaMemcpyDeviceToDevice, stream));
+    LPB_CUDA(cudaFuncSetAttribute(gauss_jordan_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    gauss_jordan_batched_kernel<<<B, kGjThreads, smem, stream>>>(n, wa, x);
+    LPB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int lpb200_gauss_jordan_batch(int B, int n, const double *a, const double *b, double *x)
+{
+    if (B < 0 || n < 0) {
+        set_error("lpb200_gauss_jordan_batch: need B >= 0 and n >= 0");
+        return LPB200_E_INVALID;
+    }
+    if (B == 0 || n == 0) return 0;
+    DeviceInfo di;
+    int rc = get_device_info(&di);
+    if (rc) return rc;
+    double *da = nullptr, *dx = nullptr;
+    const size_t na = (size_t)B * n * n * 8, nx = (size_t)B * n * 8;
+    cudaError_t e;
+    // the host copy of `a` lands directly in the working buffer: no device-to-device copy
+    if ((e = cudaMalloc((void **)&da, na)) != cudaSuccess) return cuda_fail(e, "cudaMalloc(a)");
+    if ((e = cudaMalloc((void **)&dx, nx)) != cudaSuccess) { cudaFree(da); return cuda_fail(e, "cudaMalloc(x)"); }
+    rc = 0;
+    if ((e = cudaMemcpy(da, a, na, cudaMemcpyHostToDevice)) != cudaSuccess) rc = cuda_fail(e, "cudaMemcpy(a)");
+    if (!rc && (e = cudaMemcpy(dx, b, nx, cudaMemcpyHostToDevice)) != cudaSuccess) rc = cuda_fail(e, "cudaMemcpy(b)");
+    if (!rc) {
+        const int smem = n * kGjPS * 8 + 16;
+        if (smem > di.max_smem_optin) {
+            set_error("lpb200_gauss_jordan_batch: n too large for the shared-memory panel");
+            rc = LPB200_E_TOO_LARGE;
+        }
+        if (!rc && (e = cudaFuncSetAttribute(gauss_jordan_batched_kernel,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess)
+            rc = cuda_fail(e, "cudaFuncSetAttribute");
+        if (!rc) {
+            gauss_jordan_batched_kernel<<<B, kGjThreads, smem, 0>>>(n, da, dx);
+            if ((e = cudaGetLastError()) != cudaSuccess) rc = cuda_fail(e, "gauss_jordan_batched_kernel");
+        }
+    }
+    if (!rc && (e = cudaMemcpy(x, dx, nx, cudaMemcpyDeviceToHost)) != cudaSuccess) rc = cuda_fail(e, "cudaMemcpy(x)");
+    cudaFree(da);
+    cudaFree(dx);
+    return rc;
+}

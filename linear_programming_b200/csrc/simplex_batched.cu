@@ -1,0 +1,698 @@
+// simplex_batched.cu -- one-CTA-per-LP two-phase simplex for many small dense LPs (sm_100a).
+//
+// Replaces, per problem, the reference's Simplex.solve() (week-2/diet/simplex.py:586-630)
+// with its SlackForm pivot loop (:442-491).  B200 design:
+//   * the condensed tableau ((n+1) x (1+m+1) fp64; 82 KB for 100x100) lives in SHARED MEMORY
+//     for the whole solve; HBM is touched once to read (A,b,c) and once to write (status,x);
+//   * persistent CTAs (2 per SM at 100x100) pull problems off a device-side work queue, so
+//     LPs with 10 pivots and LPs with 1600 pivots balance across the 148 SMs;
+//   * 8 sweep warps + 1 bookkeeping warp: the rank-1 update is a double2-vectorised,
+//     bank-conflict-free sweep (each lane keeps its two pivot-row values in registers and
+//     walks down the rows); the CPython-set emulation that defines the entering order runs
+//     on the 9th warp, overlapped with the sweep;
+//   * entering-column select = redux.sync min over (slot<<16|position); leaving-row select =
+//     warp-shuffle lexicographic argmin over (ratio, variable id); one block barrier each;
+//   * no FMA anywhere on the data path (__dmul_rn/__dadd_rn), IEEE division.
+//
+// Kernel <-> reference map (file:line in /root/reference/week-2/diet/simplex.py)
+//   select_entering()   objective_has_positive_coefficients :387-388, pick_entering_idx :390-392
+//   select_leaving()    pick_leaving_idx :394-436, list_wrapper.min_index :157-161
+//   pivot() phase B     make_pivot_constraint :325-345
+//   pivot() phase C     SlackForm.pivot :348-385 -> Constraint.substitute/sexp :185-214
+//   bookkeeping()       set_replace :369-381 (CPython set order)
+//   solve_one()         Simplex.solve :586-630, find_basic_feasible :514-584,
+//                       make_auxiliary_form :632-660, SlackForm.solve epilogue :473-491
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+#include "lp_common.cuh"
+#include "lp_host.h"
+
+namespace lpb {
+
+constexpr int kSweepWarps = 8;
+constexpr int kSweepThreads = kSweepWarps * 32;  // 256
+constexpr int kThreads = kSweepThreads + 32;     // + bookkeeping warp
+
+typedef int16_t tab_t;
+
+// Shared-memory carve-up, computed on the host and passed by value.
+struct BatchShape {
+    int n, m;
+    int S;        // tableau row stride in doubles (even): 1 constant + m + 1 auxiliary, rounded up
+    int cx;       // lanes across column pairs in the sweep (power of two <= 256)
+    int size_i0;  // initial table size of `independent` (phase 2: m keys / phase 1: m+1 keys)
+    int size_i1;
+    int size_d0;  // initial table size of `dependent` (n keys)
+    int cap_i, cap_d, cap_s;
+    // byte offsets from the (16-byte aligned) dynamic smem base
+    int off_T, off_nr, off_fc, off_redkey, off_rowvar, off_nonecol, off_untouched, off_rowslot,
+        off_colvar, off_colslot, off_varpos, off_basis0, off_redvar, off_redu32, off_misc,
+        off_tab_i, off_tab_d, off_tab_s;
+    int bytes;
+};
+
+static inline int align_up(int v, int a) { return (v + a - 1) / a * a; }
+
+static BatchShape make_batch_shape(int n, int m)
+{
+    BatchShape s;
+    s.n = n;
+    s.m = m;
+    s.S = align_up(m + 2, 2);
+    int cx = 1;
+    while (cx < s.S / 2 && cx < kSweepThreads) cx <<= 1;
+    if (cx > 64) cx = 64;  // keep >= 4 row groups; wider tableaus loop over column pairs
+    s.cx = cx;
+    s.size_i0 = pyset_initial_size(m);
+    s.size_i1 = pyset_initial_size(m + 1);
+    s.size_d0 = pyset_initial_size(n);
+    s.cap_i = pyset_capacity(m + 1);
+    s.cap_d = pyset_capacity(n);
+    s.cap_s = s.cap_i > s.cap_d ? s.cap_i : s.cap_d;
+    const int nv = n + m + 1;
+    int o = 0;
+    s.off_T = o;          o += (n + 1) * s.S * 8;
+    s.off_nr = o;         o += s.S * 8;
+    s.off_fc = o;         o += align_up(n + 1, 2) * 8;
+    s.off_redkey = o;     o += kSweepWarps * 8;
+    s.off_rowvar = o;     o += align_up(n, 4) * 4;
+    s.off_nonecol = o;    o += align_up(n, 4) * 4;
+    s.off_untouched = o;  o += align_up(n, 4) * 4;
+    s.off_rowslot = o;    o += align_up(n, 4) * 4;
+    s.off_colvar = o;     o += align_up(m + 1, 4) * 4;
+    s.off_colslot = o;    o += align_up(m + 1, 4) * 4;
+    s.off_varpos = o;     o += align_up(nv, 4) * 4;
+    s.off_basis0 = o;     o += align_up((nv + 31) / 32, 4) * 4;
+    s.off_redvar = o;     o += kSweepWarps * 4;
+    s.off_redu32 = o;     o += kSweepWarps * 4;
+    s.off_misc = o;       o += 16 * 4;
+    s.off_tab_i = o;      o += align_up(s.cap_i * (int)sizeof(tab_t), 16);
+    s.off_tab_d = o;      o += align_up(s.cap_d * (int)sizeof(tab_t), 16);
+    s.off_tab_s = o;      o += align_up(s.cap_s * (int)sizeof(tab_t), 16);
+    s.bytes = align_up(o, 16);
+    return s;
+}
+
+struct BatchArgs {
+    int B;
+    const double *A, *b, *c;
+    double tol;
+    int max_pivots;
+    int32_t *status;
+    double *x, *objective;
+    int32_t *npivots;
+    int32_t *pivot_log;
+    int log_cap;
+    unsigned int *work_counter;
+};
+
+// misc[] slots
+enum { MI_LP = 0, MI_ISIZE, MI_IFILL, MI_IUSED, MI_DSIZE, MI_DFILL, MI_DUSED, MI_NLIST };
+
+// Per-CTA view of the carved shared memory (pointers live in registers).
+struct Ctx {
+    double *T, *nr, *fc;
+    unsigned long long *redkey;
+    int *rowvar, *nonecol, *untouched, *rowslot, *colvar, *colslot, *varpos;
+    unsigned *basis0;
+    int *redvar;
+    unsigned *redu32;
+    int *misc;
+    tab_t *tab_i, *tab_d, *tab_s;
+    int n, m, S, cx;
+    double tol;
+    bool track_dep;  // the `dependent` set order only matters when phase 1 runs (:538)
+};
+
+// ---- entering column: first positive objective coefficient in set-slot order (:390-392) ----
+// Returns the column position, or -1 when no coefficient is > tol (loop ends, :447).
+__device__ __forceinline__ int select_entering(const Ctx &c, int ncols)
+{
+    const int tid = threadIdx.x;
+    if (tid < kSweepThreads) {
+        unsigned key = 0xffffffffu;
+        const double *obj = c.T + (size_t)c.n * c.S + 1;
+        for (int k = tid; k < ncols; k += kSweepThreads)
+            if (obj[k] > c.tol) key = min(key, ((unsigned)c.colslot[k] << 16) | (unsigned)k);
+        key = __reduce_min_sync(0xffffffffu, key);
+        if ((tid & 31) == 0) c.redu32[tid >> 5] = key;
+    }
+    __syncthreads();
+    unsigned best = c.redu32[0];
+#pragma unroll
+    for (int w = 1; w < kSweepWarps; ++w) best = min(best, c.redu32[w]);
+    return best == 0xffffffffu ? -1 : (int)(best & 0xffffu);
+}
+
+// ---- leaving row: min-ratio test with the reference's degenerate skip (:394-436) ----
+// Returns the leaving VARIABLE id, -1 if unbounded, -2 if the reference would raise TypeError.
+__device__ __forceinline__ int select_leaving(const Ctx &c, int p, int e)
+{
+    const int tid = threadIdx.x;
+    int crash = 0;
+    if (tid < kSweepThreads) {
+        unsigned long long key = kKeyNone;
+        int var = 0x7fffffff;
+        const bool e_in_basis0 = (c.basis0[e >> 5] >> (e & 31)) & 1u;
+        for (int i = tid; i < c.n; i += kSweepThreads) {
+            const int nc = c.nonecol[i];
+            crash |= (nc == kNoneInitial && e < c.n) || (nc == e) || (c.untouched[i] && e_in_basis0);
+            const double *Ti = c.T + (size_t)i * c.S;
+            const double coeff = -Ti[1 + p];
+            if (coeff > c.tol) {
+                const double ratio = snap(__ddiv_rn(Ti[0], coeff), c.tol);
+                if (ratio != 0.0) {  // zero ratios count as +inf in min_index (:161)
+                    const unsigned long long k = order_key(ratio);
+                    const int v = c.rowvar[i];
+                    if (k < key || (k == key && v < var)) {
+                        key = k;
+                        var = v;
+                    }
+                }
+            }
+        }
+        warp_argmin(key, var);
+        if ((tid & 31) == 0) {
+            c.redkey[tid >> 5] = key;
+            c.redvar[tid >> 5] = var;
+        }
+    }
+    if (__syncthreads_or(crash)) return -2;
+    unsigned long long key = c.redkey[0];
+    int var = c.redvar[0];
+#pragma unroll
+    for (int w = 1; w < kSweepWarps; ++w) {
+        const unsigned long long k = c.redkey[w];
+        const int v = c.redvar[w];
+        if (k < key || (k == key && v < var)) {
+            key = k;
+            var = v;
+        }
+    }
+    return key == kKeyNone ? -1 : var;
+}
+
+// ---- set bookkeeping by one lane of the 9th warp, overlapped with the sweep (:369-381) ----
+__device__ __forceinline__ void bookkeeping(const Ctx &c, int p, int r, int e, int l)
+{
+    // row r now belongs to e, column position p to l
+    const int eslot = c.colslot[p];
+    c.rowvar[r] = e;
+    c.colvar[p] = l;
+    c.varpos[e] = ~r;
+    c.varpos[l] = p;
+    bool rebuild;
+    if (c.track_dep) {  // dependent.remove(l); dependent.add(e)
+        PySet d = {c.misc[MI_DSIZE], c.misc[MI_DFILL], c.misc[MI_DUSED]};
+        pyset_remove_slot(c.tab_d, d, c.rowslot[r]);
+        c.rowslot[r] = pyset_add(c.tab_d, d, e, &rebuild);
+        if (rebuild) {
+            pyset_rebuild(c.tab_d, c.tab_s, d);
+            for (int s = 0; s < d.size; ++s) {
+                const int v = (int)c.tab_d[s];
+                if (v >= 0) c.rowslot[~c.varpos[v]] = s;
+            }
+        }
+        c.misc[MI_DSIZE] = d.size;
+        c.misc[MI_DFILL] = d.fill;
+        c.misc[MI_DUSED] = d.used;
+    }
+    {  // independent.remove(e); independent.add(l)
+        PySet s = {c.misc[MI_ISIZE], c.misc[MI_IFILL], c.misc[MI_IUSED]};
+        pyset_remove_slot(c.tab_i, s, eslot);
+        c.colslot[p] = pyset_add(c.tab_i, s, l, &rebuild);
+        if (rebuild) {
+            pyset_rebuild(c.tab_i, c.tab_s, s);
+            for (int t = 0; t < s.size; ++t) {
+                const int v = (int)c.tab_i[t];
+                if (v >= 0) c.colslot[c.varpos[v]] = t;
+            }
+        }
+        c.misc[MI_ISIZE] = s.size;
+        c.misc[MI_IFILL] = s.fill;
+        c.misc[MI_IUSED] = s.used;
+    }
+}
+
+// ---- SlackForm.pivot(e, l) (:348-385): e sits at column position p, l owns row r ----
+__device__ __forceinline__ void pivot(const Ctx &c, int ncols, int p, int r, int e, int l,
+                                      int32_t *log, int log_cap, int npiv)
+{
+    const int tid = threadIdx.x;
+    const int n = c.n, S = c.S, W = 1 + ncols;
+    const double tol = c.tol;
+    // Phase B: scaled pivot row (make_pivot_constraint :325-345) and the pivot column factors.
+    if (tid < kSweepThreads) {
+        const double *Tr = c.T + (size_t)r * S;
+        const double pinv = pivot_inverse(Tr[1 + p], tol);
+        for (int k = tid; k < W; k += kSweepThreads)
+            c.nr[k] = (k == 1 + p) ? snap(-pinv, tol)  // column p now belongs to l: 1/pivot (:343-344)
+                                   : snap(__dmul_rn(pinv, Tr[k]), tol);
+        for (int i = tid; i <= n; i += kSweepThreads) {
+            double *q = c.T + (size_t)i * S + 1 + p;
+            double f = *q;
+            if (fabs(f) <= tol) f = 0.0;  // substitute() returns the row unchanged (:203-205)
+            c.fc[i] = f;
+            if (i != r) *q = 0.0;         // A[i][l] starts from None (:187 opt)
+            if (i < n && (f != 0.0 || i == r)) {  // row is rewritten: its only None is column e
+                c.nonecol[i] = e;
+                c.untouched[i] = 0;
+            }
+        }
+    }
+    __syncthreads();
+    // Phase C: rank-1 sweep on 8 warps, set bookkeeping on the 9th.
+    if (tid < kSweepThreads) {
+        const int cx = tid & (c.cx - 1);
+        const int ry = tid / c.cx;
+        const int RY = kSweepThreads / c.cx;
+        const int npairs = S >> 1;
+        for (int cp = cx; cp < npairs; cp += c.cx) {
+            const double2 r2 = reinterpret_cast<const double2 *>(c.nr)[cp];
+            for (int i = ry; i <= n; i += RY) {
+                double2 *q = reinterpret_cast<double2 *>(c.T + (size_t)i * S) + cp;
+                if (i == r) {  // store(entering_idx, entering_constraint) (:352)
+                    *q = r2;
+                    continue;
+                }
+                const double f = c.fc[i];
+                if (f == 0.0) continue;
+                double2 a = *q;
+                a.x = axpy_snap(a.x, f, r2.x, tol);
+                a.y = axpy_snap(a.y, f, r2.y, tol);
+                *q = a;
+            }
+        }
+    } else if (tid == kSweepThreads) {
+        if (log != nullptr && npiv < log_cap) {
+            log[2 * npiv] = e;
+            log[2 * npiv + 1] = l;
+        }
+        bookkeeping(c, p, r, e, l);
+    }
+    __syncthreads();
+}
+
+// SlackForm.solve loop (:442-466).  Returns 0 when optimal, else a terminal status code.
+__device__ __forceinline__ int run_loop(const Ctx &c, int ncols, int &npiv, int max_pivots, int32_t *log,
+                                        int log_cap)
+{
+    for (;;) {
+        const int p = select_entering(c, ncols);
+        if (p < 0) return 0;
+        const int e = c.colvar[p];
+        const int l = select_leaving(c, p, e);
+        if (l == -2) return LPB200_STATUS_REF_TYPE_ERROR;
+        if (l < 0) return LPB200_STATUS_INFINITY;
+        if (npiv >= max_pivots) return LPB200_STATUS_ITERATION_LIMIT;
+        const int r = ~c.varpos[l];
+        pivot(c, ncols, p, r, e, l, log, log_cap, npiv);
+        ++npiv;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, 2)
+simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int tid = threadIdx.x;
+    const int n = sh.n, m = sh.m, S = sh.S;
+    const int nv = n + m + 1;
+    Ctx c;
+    c.T = reinterpret_cast<double *>(smem + sh.off_T);
+    c.nr = reinterpret_cast<double *>(smem + sh.off_nr);
+    c.fc = reinterpret_cast<double *>(smem + sh.off_fc);
+    c.redkey = reinterpret_cast<unsigned long long *>(smem + sh.off_redkey);
+    c.rowvar = reinterpret_cast<int *>(smem + sh.off_rowvar);
+    c.nonecol = reinterpret_cast<int *>(smem + sh.off_nonecol);
+    c.untouched = reinterpret_cast<int *>(smem + sh.off_untouched);
+    c.rowslot = reinterpret_cast<int *>(smem + sh.off_rowslot);
+    c.colvar = reinterpret_cast<int *>(smem + sh.off_colvar);
+    c.colslot = reinterpret_cast<int *>(smem + sh.off_colslot);
+    c.varpos = reinterpret_cast<int *>(smem + sh.off_varpos);
+    c.basis0 = reinterpret_cast<unsigned *>(smem + sh.off_basis0);
+    c.redvar = reinterpret_cast<int *>(smem + sh.off_redvar);
+    c.redu32 = reinterpret_cast<unsigned *>(smem + sh.off_redu32);
+    c.misc = reinterpret_cast<int *>(smem + sh.off_misc);
+    c.tab_i = reinterpret_cast<tab_t *>(smem + sh.off_tab_i);
+    c.tab_d = reinterpret_cast<tab_t *>(smem + sh.off_tab_d);
+    c.tab_s = reinterpret_cast<tab_t *>(smem + sh.off_tab_s);
+    c.n = n;
+    c.m = m;
+    c.S = S;
+    c.cx = sh.cx;
+    c.tol = a.tol;
+    const double tol = a.tol;
+
+    for (;;) {
+        // ---- next problem off the device work queue ----
+        __syncthreads();
+        if (tid == 0) c.misc[MI_LP] = (int)atomicAdd(a.work_counter, 1u);
+        __syncthreads();
+        const int lp = c.misc[MI_LP];
+        if (lp >= a.B) break;
+        const double *gA = a.A + (size_t)lp * n * m;
+        const double *gb = a.b + (size_t)lp * n;
+        const double *gc = a.c + (size_t)lp * m;
+        int32_t *log = a.pivot_log ? a.pivot_log + (size_t)lp * a.log_cap * 2 : nullptr;
+
+        // ---- min_constant, idx = min_index(b): zeros count as +inf, first minimum wins (:591) ----
+        if (tid < kSweepThreads) {
+            unsigned long long key = kKeyNone;
+            int idx = 0x7fffffff;
+            for (int i = tid; i < n; i += kSweepThreads) {
+                const double bi = gb[i];
+                const unsigned long long k = order_key(bi != 0.0 ? bi : CUDART_INF);
+                if (k < key || (k == key && i < idx)) {
+                    key = k;
+                    idx = i;
+                }
+            }
+            warp_argmin(key, idx);
+            if ((tid & 31) == 0) {
+                c.redkey[tid >> 5] = key;
+                c.redvar[tid >> 5] = idx;
+            }
+        }
+        __syncthreads();
+        int idx0 = c.redvar[0];
+        {
+            unsigned long long key = c.redkey[0];
+#pragma unroll
+            for (int w = 1; w < kSweepWarps; ++w) {
+                const unsigned long long k = c.redkey[w];
+                const int v = c.redvar[w];
+                if (k < key || (k == key && v < idx0)) {
+                    key = k;
+                    idx0 = v;
+                }
+            }
+        }
+        const double min_c = gb[idx0];
+        const bool phase1 = (min_c < 0.0);
+        int status = 0;
+        int npiv = 0;
+        int ncols = phase1 ? m + 1 : m;
+        if (!phase1 && !(min_c > tol)) status = LPB200_STATUS_REF_ATTRIBUTE_ERROR;  // :626
+        c.track_dep = phase1;
+
+        if (status == 0) {
+            // ---- SlackForm.__init__ (:230-302) (+ the x_aux column of :632-660 in phase 1) ----
+            if (tid < kSweepThreads) {
+                const int warp = tid >> 5, lane = tid & 31;
+                for (int i = warp; i < n; i += kSweepWarps) {
+                    double *Ti = c.T + (size_t)i * S;
+                    const double *Ai = gA + (size_t)i * m;
+                    for (int j = lane; j < m; j += 32) Ti[1 + j] = -Ai[j];
+                    if (lane == 0) {
+                        Ti[0] = gb[i];
+                        Ti[1 + m] = phase1 ? 1.0 : 0.0;  // -(-1), :659 then :262
+                    }
+                    for (int k = m + 2 + lane; k < S; k += 32) Ti[k] = 0.0;
+                }
+                double *obj = c.T + (size_t)n * S;
+                for (int k = tid; k < S; k += kSweepThreads) {
+                    double v = 0.0;
+                    if (k >= 1 && k <= m) v = phase1 ? 0.0 : gc[k - 1];
+                    if (k == 1 + m && phase1) v = -1.0;  // objective -x_aux (:644-645)
+                    obj[k] = v;
+                    c.nr[k] = 0.0;
+                }
+                for (int i = tid; i < n; i += kSweepThreads) {
+                    c.rowvar[i] = i;
+                    c.varpos[i] = ~i;
+                    c.nonecol[i] = kNoneInitial;
+                    c.untouched[i] = 0;
+                    c.rowslot[i] = i & (sh.size_d0 - 1);
+                }
+                const int isize = phase1 ? sh.size_i1 : sh.size_i0;
+                for (int k = tid; k <= m; k += kSweepThreads) {
+                    c.colvar[k] = n + k;
+                    c.varpos[n + k] = k;
+                    c.colslot[k] = (n + k) & (isize - 1);
+                }
+                for (int w = tid; w < (nv + 31) / 32; w += kSweepThreads) c.basis0[w] = 0u;
+            } else {
+                // set(range(n, n+ncols)) and set(range(0, n)) (:289-292), built by the 9th warp
+                const int lane = tid - kSweepThreads;
+                const int isize = phase1 ? sh.size_i1 : sh.size_i0;
+                for (int s = lane; s < isize; s += 32) c.tab_i[s] = (tab_t)kSetUnused;
+                __syncwarp();
+                for (int k = n + lane; k < n + ncols; k += 32) c.tab_i[k & (isize - 1)] = (tab_t)k;
+                if (phase1) {
+                    for (int s = lane; s < sh.size_d0; s += 32) c.tab_d[s] = (tab_t)kSetUnused;
+                    __syncwarp();
+                    for (int k = lane; k < n; k += 32) c.tab_d[k & (sh.size_d0 - 1)] = (tab_t)k;
+                }
+                if (lane == 0) {
+                    c.misc[MI_ISIZE] = isize;
+                    c.misc[MI_IFILL] = ncols;
+                    c.misc[MI_IUSED] = ncols;
+                    c.misc[MI_DSIZE] = sh.size_d0;
+                    c.misc[MI_DFILL] = n;
+                    c.misc[MI_DUSED] = n;
+                }
+            }
+            __syncthreads();
+
+            if (phase1) {
+                const int aux = n + m;
+                // forced pivot: x_aux enters, the most negative row leaves (:524)
+                if (npiv >= a.max_pivots) {
+                    status = LPB200_STATUS_ITERATION_LIMIT;
+                } else {
+                    pivot(c, ncols, m, idx0, aux, idx0, log, a.log_cap, npiv);
+                    ++npiv;
+                    status = run_loop(c, ncols, npiv, a.max_pivots, log, a.log_cap);  // :526
+                }
+                if (status == 0) {
+                    if (!(fabs(c.T[(size_t)n * S]) <= tol)) status = LPB200_STATUS_NO_SOLUTION;  // :528-530
+                    else if (c.varpos[aux] < 0) status = LPB200_STATUS_REF_INDEX_ERROR;  // :541 -> :183
+                }
+                if (status == 0) {
+                    // ---- rebuild the original objective (:537-541) ----
+                    // basic ORIGINAL variables in iteration order of the `dependent` set
+                    // (slack rows have objective coefficient None: skipped, :203)
+                    int *list = reinterpret_cast<int *>(c.fc);
+                    if (tid < 32) {
+                        const int dsize = c.misc[MI_DSIZE];
+                        int cnt = 0;
+                        for (int s0 = 0; s0 < dsize; s0 += 32) {
+                            const int s = s0 + tid;
+                            const int v = (s < dsize) ? (int)c.tab_d[s] : -1;
+                            const unsigned msk = __ballot_sync(0xffffffffu, v >= n);
+                            if (v >= n) list[cnt + __popc(msk & ((1u << tid) - 1u))] = v;
+                            cnt += __popc(msk);
+                        }
+                        if (tid == 0) c.misc[MI_NLIST] = cnt;
+                    }
+                    // stage c in nr[], start from (v, c) = (0, [None]*n + float(c)) (:516, :537)
+                    if (tid < kSweepThreads) {
+                        for (int j = tid; j < m; j += kSweepThreads) c.nr[j] = gc[j];
+                    }
+                    __syncthreads();
+                    const int kaux = c.varpos[aux];
+                    if (tid < kSweepThreads) {
+                        double *obj = c.T + (size_t)n * S;
+                        const int nlist = c.misc[MI_NLIST];
+                        for (int k = tid; k < 1 + ncols; k += kSweepThreads) {
+                            if (k == 1 + kaux) continue;  // zip() truncates the x_aux column (:190)
+                            double o = 0.0;
+                            if (k >= 1) {
+                                const int w = c.colvar[k - 1];
+                                o = (w >= n) ? c.nr[w - n] : 0.0;
+                            }
+                            for (int t = 0; t < nlist; ++t) {
+                                const int v = list[t];
+                                const double f = c.nr[v - n];
+                                if (fabs(f) <= tol) continue;
+                                o = axpy_snap(o, f, c.T[(size_t)(~c.varpos[v]) * S + k], tol);
+                            }
+                            obj[k] = o;
+                        }
+                    }
+                    __syncthreads();
+                    // ---- clean-up (:547-575): None out basic columns, drop x_aux, same sets live on ----
+                    const int last = ncols - 1;
+                    if (tid < kSweepThreads) {
+                        for (int w = tid; w < (nv + 31) / 32; w += kSweepThreads) {
+                            unsigned bits = 0u;
+                            for (int bb = 0; bb < 32; ++bb) {
+                                const int v = w * 32 + bb;
+                                if (v < nv && c.varpos[v] < 0) bits |= 1u << bb;
+                            }
+                            c.basis0[w] = bits;
+                        }
+                        for (int i = tid; i < n; i += kSweepThreads) c.untouched[i] = 1;
+                        for (int i = tid; i <= n; i += kSweepThreads) {
+                            double *Ti = c.T + (size_t)i * S;
+                            if (kaux != last) Ti[1 + kaux] = Ti[1 + last];
+                            Ti[1 + last] = 0.0;
+                        }
+                        for (int k = tid; k < S; k += kSweepThreads) c.nr[k] = 0.0;
+                    } else if (tid == kSweepThreads) {
+                        PySet s = {c.misc[MI_ISIZE], c.misc[MI_IFILL], c.misc[MI_IUSED]};
+                        pyset_remove_slot(c.tab_i, s, c.colslot[kaux]);  // independent.remove(nvars) (:574)
+                        c.misc[MI_IUSED] = s.used;
+                        if (kaux != last) {
+                            const int w = c.colvar[last];
+                            c.colvar[kaux] = w;
+                            c.colslot[kaux] = c.colslot[last];
+                            c.varpos[w] = kaux;
+                        }
+                    }
+                    ncols = m;
+                    __syncthreads();
+                    status = run_loop(c, ncols, npiv, a.max_pivots, log, a.log_cap);  // :599
+                }
+            } else {
+                status = run_loop(c, ncols, npiv, a.max_pivots, log, a.log_cap);  // :619
+            }
+        }
+
+        // ---- results (:473-491, 603, 622) ----
+        if (tid < kSweepThreads) {
+            double *gx = a.x + (size_t)lp * m;
+            for (int j = tid; j < m; j += kSweepThreads) {
+                double v = 0.0;
+                if (status == 0) {
+                    const int pos = c.varpos[n + j];
+                    if (pos < 0) v = c.T[(size_t)(~pos) * S];
+                }
+                gx[j] = v;
+            }
+            if (tid == 0) {
+                a.status[lp] = status;
+                a.npivots[lp] = npiv;
+                a.objective[lp] = (status == 0) ? c.T[(size_t)n * S] : 0.0;
+            }
+        }
+    }
+}
+
+}  // namespace lpb
+
+// ======================================================================================
+// Host side: C ABI
+// ======================================================================================
+using namespace lpb;
+
+static int check_batch_args(int B, int n, int m, double tol, int max_pivots, int log_cap)
+{
+    if (B < 0 || n < 1 || m < 1 || !(tol >= 0.0) || max_pivots < 0 || log_cap < 0) {
+        set_error("lpb200_simplex_batch: need B >= 0, n >= 1, m >= 1, tol >= 0, max_pivots >= 0");
+        return LPB200_E_INVALID;
+    }
+    if (n + m + 1 >= 32000) {
+        set_error("lpb200_simplex_batch: n + m too large for the one-CTA-per-LP kernel; use lpb200_simplex_single");
+        return LPB200_E_TOO_LARGE;
+    }
+    return 0;
+}
+
+extern "C" int64_t lpb200_simplex_batch_smem_bytes(int n, int m)
+{
+    if (n < 1 || m < 1 || n + m + 1 >= 32000) return INT64_MAX;
+    return (int64_t)make_batch_shape(n, m).bytes;
+}
+
+extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A, const double *b,
+                                           const double *c, double tol, int max_pivots, int32_t *status,
+                                           double *x, double *objective, int32_t *npivots,
+                                           int32_t *pivot_log, int log_cap, void *stream_v)
+{
+    int rc = check_batch_args(B, n, m, tol, max_pivots, log_cap);
+    if (rc) return rc;
+    if (B == 0) return 0;
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    DeviceInfo di;
+    rc = get_device_info(&di);
+    if (rc) return rc;
+    const BatchShape sh = make_batch_shape(n, m);
+    if (sh.bytes > di.max_smem_optin) {
+        set_error("lpb200_simplex_batch: tableau does not fit shared memory (" + std::to_string(sh.bytes) +
+                  " > " + std::to_string(di.max_smem_optin) + " bytes); use lpb200_simplex_single");
+        return LPB200_E_TOO_LARGE;
+    }
+    LPB_CUDA(cudaFuncSetAttribute(simplex_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sh.bytes));
+    int per_sm = 0;
+    LPB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_batched_kernel, kThreads, sh.bytes));
+    if (per_sm < 1) per_sm = 1;
+    long long grid = (long long)di.sm_count * per_sm;
+    if (grid > B) grid = B;
+    unsigned int *counter = nullptr;
+    LPB_CUDA(cudaMallocAsync((void **)&counter, sizeof(unsigned int), stream));
+    LPB_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned int), stream));
+    BatchArgs a;
+    a.B = B;
+    a.A = A;
+    a.b = b;
+    a.c = c;
+    a.tol = tol;
+    a.max_pivots = max_pivots;
+    a.status = status;
+    a.x = x;
+    a.objective = objective;
+    a.npivots = npivots;
+    a.pivot_log = pivot_log;
+    a.log_cap = log_cap;
+    a.work_counter = counter;
+    simplex_batched_kernel<<<(unsigned)grid, kThreads, sh.bytes, stream>>>(sh, a);
+    LPB_CUDA(cudaGetLastError());
+    LPB_CUDA(cudaFreeAsync(counter, stream));
+    return 0;
+}
+
+extern "C" int lpb200_simplex_batch(int B, int n, int m, const double *A, const double *b, const double *c,
+                                    double tol, int max_pivots, int32_t *status, double *x,
+                                    double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap)
+{
+    int rc = check_batch_args(B, n, m, tol, max_pivots, log_cap);
+    if (rc) return rc;
+    if (B == 0) return 0;
+    DeviceInfo di;
+    rc = get_device_info(&di);
+    if (rc) return rc;
+    const size_t nA = (size_t)B * n * m, nb = (size_t)B * n, nc = (size_t)B * m;
+    const size_t nlog = pivot_log ? (size_t)B * log_cap * 2 : 0;
+    double *dA = nullptr, *db = nullptr, *dc = nullptr, *dx = nullptr, *dobj = nullptr;
+    int32_t *dst = nullptr, *dnp = nullptr, *dlog = nullptr;
+    cudaStream_t stream = nullptr;
+    rc = 0;
+#define LPB_TRY(call)                                   \
+    do {                                                \
+        cudaError_t _e = (call);                        \
+        if (_e != cudaSuccess && rc == 0) rc = cuda_fail(_e, #call); \
+    } while (0)
+    LPB_TRY(cudaMalloc((void **)&dA, nA * 8));
+    LPB_TRY(cudaMalloc((void **)&db, nb * 8));
+    LPB_TRY(cudaMalloc((void **)&dc, nc * 8));
+    LPB_TRY(cudaMalloc((void **)&dx, nc * 8));
+    LPB_TRY(cudaMalloc((void **)&dobj, (size_t)B * 8));
+    LPB_TRY(cudaMalloc((void **)&dst, (size_t)B * 4));
+    LPB_TRY(cudaMalloc((void **)&dnp, (size_t)B * 4));
+    if (nlog) LPB_TRY(cudaMalloc((void **)&dlog, nlog * 4));
+    if (rc == 0) {
+        LPB_TRY(cudaMemcpyAsync(dA, A, nA * 8, cudaMemcpyHostToDevice, stream));
+        LPB_TRY(cudaMemcpyAsync(db, b, nb * 8, cudaMemcpyHostToDevice, stream));
+        LPB_TRY(cudaMemcpyAsync(dc, c, nc * 8, cudaMemcpyHostToDevice, stream));
+        if (nlog) LPB_TRY(cudaMemsetAsync(dlog, 0xff, nlog * 4, stream));
+    }
+    if (rc == 0)
+        rc = lpb200_simplex_batch_device(B, n, m, dA, db, dc, tol, max_pivots, dst, dx, dobj, dnp, dlog,
+                                         log_cap, stream);
+    if (rc == 0) {
+        LPB_TRY(cudaMemcpyAsync(status, dst, (size_t)B * 4, cudaMemcpyDeviceToHost, stream));
+        LPB_TRY(cudaMemcpyAsync(x, dx, nc * 8, cudaMemcpyDeviceToHost, stream));
+        LPB_TRY(cudaMemcpyAsync(objective, dobj, (size_t)B * 8, cudaMemcpyDeviceToHost, stream));
+        LPB_TRY(cudaMemcpyAsync(npivots, dnp, (size_t)B * 4, cudaMemcpyDeviceToHost, stream));
+        if (nlog) LPB_TRY(cudaMemcpyAsync(pivot_log, dlog, nlog * 4, cudaMemcpyDeviceToHost, stream));
+        LPB_TRY(cudaStreamSynchronize(stream));
+    }
+#undef LPB_TRY
+    cudaFree(dA); cudaFree(db); cudaFree(dc); cudaFree(dx); cudaFree(dobj);
+    cudaFree(dst); cudaFree(dnp); cudaFree(dlog);
+    return rc;
+}

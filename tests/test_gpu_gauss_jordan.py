@@ -1,0 +1,67 @@
+"""GPU parity tests for the batched Gauss-Jordan kernel (through the C ABI): bit-identical
+to the compiled reference's outputs (golden) and to the oracle."""
+import numpy as np
+import pytest
+
+from linear_programming_b200 import workloads
+from test_oracle_gauss_jordan import _inputs
+
+pytestmark = pytest.mark.gpu
+
+
+def test_golden_outputs_of_the_reference(gj_golden):
+    import linear_programming_b200 as lp
+    for case in gj_golden["cases"]:
+        a, b = _inputs(case)
+        x = lp.solve_equation(a, b)
+        got = [float(v).hex() for v in x]
+        if case["name"].startswith("singular"):
+            assert all(not np.isfinite(v) for v in x)  # the reference divides by zero too
+            continue
+        assert got == case["x"], case["name"]
+
+
+def test_size_zero_prints_nothing():
+    from linear_programming_b200 import gauss_jordan
+    x = gauss_jordan.solve_equation(np.zeros((0, 0)), np.zeros(0))
+    assert gauss_jordan.format_column(x) == ""
+
+
+@pytest.mark.parametrize("n,count,frac", [(5, 40, 0.5), (16, 40, 0.5), (17, 40, 0.5), (100, 24, 0.3),
+                                          (257, 8, 0.5), (512, 12, 0.25)])
+def test_batches_vs_oracle(oracle_lib, n, count, frac):
+    import linear_programming_b200 as lp
+    a, b = workloads.gauss_jordan_batch(count, n=n, seed=1, swap_frac=frac)
+    x = lp.solve_equation_batch(a, b)
+    want, _ = oracle_lib.gauss_jordan_batch(a, b, full_sweep=False)
+    assert np.array_equal(x.view(np.int64), want.view(np.int64))
+    # solves the system (size-independent property)
+    resid = np.abs(np.einsum("bij,bj->bi", a, x) - b).max()
+    assert resid < 1e-9
+
+
+def test_consecutive_zero_pivots(oracle_lib):
+    """week-2/energy_values/tests/05 style permutation systems: a swap at nearly every step,
+    so panels are truncated again and again."""
+    import linear_programming_b200 as lp
+    rng = np.random.default_rng(4)
+    n = 48
+    a = np.zeros((6, n, n))
+    b = rng.uniform(-1, 1, size=(6, n))
+    for s in range(6):
+        perm = rng.permutation(n)
+        a[s, np.arange(n), perm] = rng.uniform(1, 2, size=n)
+        a[s] += np.triu(rng.uniform(-0.1, 0.1, size=(n, n)), 1) * (rng.random((n, n)) < 0.2)
+    x = lp.solve_equation_batch(a, b)
+    want, _ = oracle_lib.gauss_jordan_batch(a, b, full_sweep=True)
+    assert np.array_equal(x.view(np.int64), want.view(np.int64))
+
+
+def test_torch_device_path(oracle_lib):
+    import torch
+    import linear_programming_b200 as lp
+    a, b = workloads.gauss_jordan_batch(32, n=128, seed=1, swap_frac=0.2)
+    x = lp.solve_equation_batch(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda())
+    torch.cuda.synchronize()
+    want, _ = oracle_lib.gauss_jordan_batch(a, b)
+    assert np.array_equal(x.cpu().numpy().view(np.int64), want.view(np.int64))

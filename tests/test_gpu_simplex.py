@@ -1,0 +1,164 @@
+"""GPU parity tests (run on the B200 box with -m gpu): the CUDA engine, called through the
+C ABI, against the golden vectors of the unmodified reference and against the oracle.
+Bar: status, pivot count and the full pivot sequence identical; x and optimum BIT-identical."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _case_arrays(case):
+    A = np.array(case["A"], dtype=np.float64).reshape(case["n"], case["m"])
+    return A, np.array(case["b"], dtype=np.float64), np.array(case["c"], dtype=np.float64)
+
+
+def _check_against_case(res, p, case):
+    name = case["name"]
+    assert int(res.status[p]) == case["status"], name
+    assert int(res.npivots[p]) == case["npivots"], name
+    assert [list(q) for q in res.pivots(p)] == case["pivots"], name
+    if case["status"] == 0:
+        assert [float(v).hex() for v in res.x[p]] == case["x"], name
+        assert float(res.objective[p]).hex() == case["optimum"], name
+    else:
+        assert not np.any(res.x[p]), name
+
+
+@pytest.mark.parametrize("mode", ["batch", "single"])
+def test_every_golden_case(simplex_golden, mode):
+    """All fixtures of week-2/diet/tests, week-2/diet/fail, week-2/ad_allocation/tests, the
+    unit-test LPs and the seeded random LPs (all outcome classes) -- grouped by shape so
+    each group is one batched launch."""
+    import linear_programming_b200 as lp
+    groups = {}
+    for case in simplex_golden["cases"]:
+        if mode == "single" and case["npivots"] > 400:
+            continue  # the grid-wide kernel pays 4 grid syncs per pivot; keep the test short
+        groups.setdefault((case["n"], case["m"]), []).append(case)
+    checked = 0
+    for (n, m), cases in sorted(groups.items()):
+        A = np.stack([_case_arrays(c)[0] for c in cases])
+        b = np.stack([_case_arrays(c)[1] for c in cases])
+        c_ = np.stack([_case_arrays(c)[2] for c in cases])
+        cap = max(c["npivots"] for c in cases) + 8
+        res = lp.solve_batch(A, b, c_, log_cap=cap, max_pivots=cap, mode=mode)
+        for p, case in enumerate(cases):
+            _check_against_case(res, p, case)
+            checked += 1
+    assert checked >= (430 if mode == "batch" else 400)
+
+
+def test_known_answer_optima():
+    # week-2/diet/test_simplex.py:16-50
+    import linear_programming_b200 as lp
+    s = lp.Simplex([[-1, -1], [1, 0], [0, 1]], [-1, 2, 2], [-1, 2], 3, 2)
+    s.solve()
+    assert s.optimum == 4.0
+    s = lp.Simplex([[1, 1, 3], [2, 2, 5], [4, 1, 2]], [30, 24, 36], [3, 1, 2], 3, 3)
+    s.solve()
+    assert s.optimum == 28
+    s = lp.Simplex([[2, -1], [1, -5]], [2, -4], [2, -1], 2, 2)
+    s.solve()
+    assert s.optimum == 2.0
+
+
+def test_reference_crash_classes_raise_like_the_reference(simplex_golden):
+    import linear_programming_b200 as lp
+    want = {3: AttributeError, 4: IndexError, 5: TypeError}
+    seen = set()
+    for case in simplex_golden["cases"]:
+        if case["status"] in want and case["status"] not in seen:
+            seen.add(case["status"])
+            with pytest.raises(want[case["status"]]):
+                lp.Simplex(case["A"], case["b"], case["c"], case["n"], case["m"]).solve()
+    assert seen == {3, 4, 5}
+
+
+@pytest.mark.parametrize("dist,n,m,count", [("D1", 100, 100, 96), ("D2", 100, 100, 24), ("D3", 100, 100, 12),
+                                            ("D2", 37, 61, 64), ("D3", 64, 20, 64), ("D3", 150, 130, 6)])
+def test_random_batches_vs_oracle(oracle_lib, dist, n, m, count):
+    """Config-4 distributions at sizes the oracle finishes in seconds: bit-exact vs the oracle
+    (itself pinned to the reference)."""
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    A, b, c = workloads.simplex_batch(dist, count, n, m, seed=2)
+    cap = 20000
+    res = lp.solve_batch(A, b, c, log_cap=0, max_pivots=cap)
+    st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=cap)
+    assert np.array_equal(res.status, st)
+    assert np.array_equal(res.npivots, npiv)
+    assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
+    assert np.array_equal(res.objective.view(np.int64), obj.view(np.int64))
+
+
+def test_stress_distribution_vs_oracle(oracle_lib):
+    """Config 2: the stress.py:23-26 distribution with zeros in b (every crash class)."""
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    probs = workloads.stress_batch(4000, seed=3)
+    groups = {}
+    for A, b, c in probs:
+        groups.setdefault(A.shape, []).append((A, b, c))
+    seen = set()
+    for (n, m), lst in groups.items():
+        A = np.stack([q[0] for q in lst]); b = np.stack([q[1] for q in lst]); c = np.stack([q[2] for q in lst])
+        res = lp.solve_batch(A, b, c, log_cap=64, max_pivots=5000)
+        for p in range(len(lst)):
+            o = oracle_lib.simplex(A[p], b[p], c[p], max_pivots=5000)
+            assert int(res.status[p]) == o["status"]
+            assert res.pivots(p) == o["pivots"][:64]
+            assert np.array_equal(res.x[p].view(np.int64), o["x"].view(np.int64))
+            seen.add(o["status"])
+    assert {0, -1, 1, 3} <= seen
+
+
+def test_iteration_limit():
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    A, b, c = workloads.simplex_batch("D2", 4, 40, 40, seed=2)
+    res = lp.solve_batch(A, b, c, max_pivots=5, log_cap=8)
+    assert set(int(s) for s in res.status) <= {2, 1, 0}
+    assert 2 in set(int(s) for s in res.status)
+    assert all(int(k) <= 5 for k in res.npivots)
+
+
+def test_torch_device_tensors_zero_copy(oracle_lib):
+    import torch
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    A, b, c = workloads.simplex_batch("D1", 300, 100, 100, seed=2)
+    dA, db, dc = (torch.from_numpy(v).cuda() for v in (A, b, c))
+    res = lp.solve_batch(dA, db, dc)
+    torch.cuda.synchronize()
+    assert res.x.is_cuda
+    st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c)
+    assert np.array_equal(res.status.cpu().numpy(), st)
+    assert np.array_equal(res.npivots.cpu().numpy(), npiv)
+    assert np.array_equal(res.x.cpu().numpy().view(np.int64), x.view(np.int64))
+
+
+def test_single_mode_mid_size_vs_oracle(oracle_lib):
+    """Grid-wide kernel on a tableau that spans several tiles/strips (D1 and a phase-1 LP)."""
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    for dist, n, m in (("D1", 300, 1200), ("D3", 200, 700)):
+        A, b, c = workloads.single_lp(n, m, seed=5, dist="D1") if dist == "D1" else \
+            tuple(v[0] for v in workloads.simplex_batch("D3", 1, n, m, seed=9))
+        cap = 600
+        res = lp.solve_batch(A[None], b[None], c[None], mode="single", max_pivots=cap, log_cap=cap)
+        o = oracle_lib.simplex(A, b, c, max_pivots=cap)
+        assert int(res.status[0]) == o["status"]
+        assert res.pivots(0) == o["pivots"]
+        assert np.array_equal(res.x[0].view(np.int64), o["x"].view(np.int64))
+        assert float(res.objective[0]).hex() == float(o["objective"]).hex()
+
+
+def test_tolerance_is_a_runtime_argument(oracle_lib):
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    A, b, c = workloads.simplex_batch("D2", 16, 30, 30, seed=6)
+    for tol in (1e-6, 1e-12):
+        res = lp.solve_batch(A, b, c, tol=tol, max_pivots=5000)
+        st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, tol=tol, max_pivots=5000)
+        assert np.array_equal(res.status, st) and np.array_equal(res.npivots, npiv)
+        assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
