@@ -645,6 +645,9 @@ extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A,
     return 0;
 }
 
+// Host-pointer entry point: the batch is cut into chunks that are copied in, solved and
+// copied out on two alternating streams, so the PCIe copy of chunk k+1 overlaps the solve of
+// chunk k and device memory stays bounded (two chunk-sized buffer sets).
 extern "C" int lpb200_simplex_batch(int B, int n, int m, const double *A, const double *b, const double *c,
                                     double tol, int max_pivots, int32_t *status, double *x,
                                     double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap)
@@ -655,44 +658,64 @@ extern "C" int lpb200_simplex_batch(int B, int n, int m, const double *A, const 
     DeviceInfo di;
     rc = get_device_info(&di);
     if (rc) return rc;
-    const size_t nA = (size_t)B * n * m, nb = (size_t)B * n, nc = (size_t)B * m;
-    const size_t nlog = pivot_log ? (size_t)B * log_cap * 2 : 0;
-    double *dA = nullptr, *db = nullptr, *dc = nullptr, *dx = nullptr, *dobj = nullptr;
-    int32_t *dst = nullptr, *dnp = nullptr, *dlog = nullptr;
-    cudaStream_t stream = nullptr;
+    const size_t lpA = (size_t)n * m, lpb = (size_t)n, lpc = (size_t)m;
+    const size_t lplog = pivot_log ? (size_t)log_cap * 2 : 0;
+    const size_t lp_bytes = (lpA + lpb + 2 * lpc + 1) * 8 + 8 + lplog * 4;
+    long long chunk = (long long)((size_t)(96u << 20) / lp_bytes);  // ~96 MB per chunk
+    if (chunk < 1) chunk = 1;
+    if (chunk > B) chunk = B;
+    const int nset = (chunk < B) ? 2 : 1;
+    struct Set {
+        double *A, *b, *c, *x, *obj;
+        int32_t *st, *np, *log;
+        cudaStream_t stream;
+    } set[2] = {};
     rc = 0;
-#define LPB_TRY(call)                                   \
-    do {                                                \
-        cudaError_t _e = (call);                        \
-        if (_e != cudaSuccess && rc == 0) rc = cuda_fail(_e, #call); \
+#define LPB_TRY(call)                                                 \
+    do {                                                              \
+        cudaError_t _e = (call);                                      \
+        if (_e != cudaSuccess && rc == 0) rc = cuda_fail(_e, #call);  \
     } while (0)
-    LPB_TRY(cudaMalloc((void **)&dA, nA * 8));
-    LPB_TRY(cudaMalloc((void **)&db, nb * 8));
-    LPB_TRY(cudaMalloc((void **)&dc, nc * 8));
-    LPB_TRY(cudaMalloc((void **)&dx, nc * 8));
-    LPB_TRY(cudaMalloc((void **)&dobj, (size_t)B * 8));
-    LPB_TRY(cudaMalloc((void **)&dst, (size_t)B * 4));
-    LPB_TRY(cudaMalloc((void **)&dnp, (size_t)B * 4));
-    if (nlog) LPB_TRY(cudaMalloc((void **)&dlog, nlog * 4));
-    if (rc == 0) {
-        LPB_TRY(cudaMemcpyAsync(dA, A, nA * 8, cudaMemcpyHostToDevice, stream));
-        LPB_TRY(cudaMemcpyAsync(db, b, nb * 8, cudaMemcpyHostToDevice, stream));
-        LPB_TRY(cudaMemcpyAsync(dc, c, nc * 8, cudaMemcpyHostToDevice, stream));
-        if (nlog) LPB_TRY(cudaMemsetAsync(dlog, 0xff, nlog * 4, stream));
+    for (int s = 0; s < nset; ++s) {
+        LPB_TRY(cudaStreamCreateWithFlags(&set[s].stream, cudaStreamNonBlocking));
+        LPB_TRY(cudaMalloc((void **)&set[s].A, chunk * lpA * 8));
+        LPB_TRY(cudaMalloc((void **)&set[s].b, chunk * lpb * 8));
+        LPB_TRY(cudaMalloc((void **)&set[s].c, chunk * lpc * 8));
+        LPB_TRY(cudaMalloc((void **)&set[s].x, chunk * lpc * 8));
+        LPB_TRY(cudaMalloc((void **)&set[s].obj, chunk * 8));
+        LPB_TRY(cudaMalloc((void **)&set[s].st, chunk * 4));
+        LPB_TRY(cudaMalloc((void **)&set[s].np, chunk * 4));
+        if (lplog) LPB_TRY(cudaMalloc((void **)&set[s].log, chunk * lplog * 4));
     }
-    if (rc == 0)
-        rc = lpb200_simplex_batch_device(B, n, m, dA, db, dc, tol, max_pivots, dst, dx, dobj, dnp, dlog,
-                                         log_cap, stream);
-    if (rc == 0) {
-        LPB_TRY(cudaMemcpyAsync(status, dst, (size_t)B * 4, cudaMemcpyDeviceToHost, stream));
-        LPB_TRY(cudaMemcpyAsync(x, dx, nc * 8, cudaMemcpyDeviceToHost, stream));
-        LPB_TRY(cudaMemcpyAsync(objective, dobj, (size_t)B * 8, cudaMemcpyDeviceToHost, stream));
-        LPB_TRY(cudaMemcpyAsync(npivots, dnp, (size_t)B * 4, cudaMemcpyDeviceToHost, stream));
-        if (nlog) LPB_TRY(cudaMemcpyAsync(pivot_log, dlog, nlog * 4, cudaMemcpyDeviceToHost, stream));
-        LPB_TRY(cudaStreamSynchronize(stream));
+    int k = 0;
+    for (long long lo = 0; lo < B && rc == 0; lo += chunk, ++k) {
+        const long long cnt = (B - lo < chunk) ? (B - lo) : chunk;
+        Set &q = set[k % nset];
+        LPB_TRY(cudaMemcpyAsync(q.A, A + lo * lpA, cnt * lpA * 8, cudaMemcpyHostToDevice, q.stream));
+        LPB_TRY(cudaMemcpyAsync(q.b, b + lo * lpb, cnt * lpb * 8, cudaMemcpyHostToDevice, q.stream));
+        LPB_TRY(cudaMemcpyAsync(q.c, c + lo * lpc, cnt * lpc * 8, cudaMemcpyHostToDevice, q.stream));
+        if (lplog) LPB_TRY(cudaMemsetAsync(q.log, 0xff, cnt * lplog * 4, q.stream));
+        if (rc == 0)
+            rc = lpb200_simplex_batch_device((int)cnt, n, m, q.A, q.b, q.c, tol, max_pivots, q.st, q.x, q.obj,
+                                             q.np, q.log, log_cap, q.stream);
+        LPB_TRY(cudaMemcpyAsync(status + lo, q.st, cnt * 4, cudaMemcpyDeviceToHost, q.stream));
+        LPB_TRY(cudaMemcpyAsync(x + lo * lpc, q.x, cnt * lpc * 8, cudaMemcpyDeviceToHost, q.stream));
+        LPB_TRY(cudaMemcpyAsync(objective + lo, q.obj, cnt * 8, cudaMemcpyDeviceToHost, q.stream));
+        LPB_TRY(cudaMemcpyAsync(npivots + lo, q.np, cnt * 4, cudaMemcpyDeviceToHost, q.stream));
+        if (lplog)
+            LPB_TRY(cudaMemcpyAsync(pivot_log + lo * lplog, q.log, cnt * lplog * 4, cudaMemcpyDeviceToHost, q.stream));
+    }
+    for (int s = 0; s < nset; ++s) {
+        if (set[s].stream) {
+            cudaError_t e = cudaStreamSynchronize(set[s].stream);
+            if (e != cudaSuccess && rc == 0) rc = cuda_fail(e, "cudaStreamSynchronize");
+        }
     }
 #undef LPB_TRY
-    cudaFree(dA); cudaFree(db); cudaFree(dc); cudaFree(dx); cudaFree(dobj);
-    cudaFree(dst); cudaFree(dnp); cudaFree(dlog);
+    for (int s = 0; s < nset; ++s) {
+        cudaFree(set[s].A); cudaFree(set[s].b); cudaFree(set[s].c); cudaFree(set[s].x); cudaFree(set[s].obj);
+        cudaFree(set[s].st); cudaFree(set[s].np); cudaFree(set[s].log);
+        if (set[s].stream) cudaStreamDestroy(set[s].stream);
+    }
     return rc;
 }
