@@ -1,0 +1,397 @@
+#!/usr/bin/env python3
+"""bench.py -- headline benchmark of the B200 LP engine ("Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--batch B] [--dist D1|D2|D3] [--n 100] [--m 100]
+
+Workload (BASELINE.json configs[3]): B = 65536 random feasible 100x100 LPs per GPU
+(distribution D1 of linear_programming_b200/workloads.py, integer data stored as fp64),
+sharded by problem index across ranks with NO data-path collective (weak scaling: every
+rank solves its own B problems).  One "step" = one pass of the hot path over the batch =
+one launch of simplex_batched_kernel.
+
+  value      LPs/s, whole job, inputs already resident in HBM when the timed region starts
+  e2e        LPs/s through the reference-facing C ABI with HOST (pinned) buffers: host->device
+             copies, solve and device->host copies all inside the timed region
+  roofline   algorithmic bytes of the dominant kernel / its CUDA-event duration vs the measured
+             HBM peak: 16*(n+1)*(m+1) bytes per pivot x pivots per launch
+  cpu_baseline  the C oracle port timed on this box's host cores on a bounded sample
+
+`--impl reference` times the CPU implementation of the path (the reference solver is Python
+and cannot travel to the GPU box, so this is the oracle port -- pinned bit-exact to the
+reference -- on all host threads), same metric/config, bounded sample per step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "LPs/sec (batched 100x100 simplex)"
+UNIT = "LPs/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=65536)
+    ap.add_argument("--dist", default="D1", choices=["D1", "D2", "D3"])
+    ap.add_argument("--n", type=int, default=100)
+    ap.add_argument("--m", type=int, default=100)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def config_dict(args, batch):
+    return {
+        "workload": "configs[3]: batched simplex, %d random feasible %dx%d LPs per GPU (%s), "
+                    "sharded by problem index" % (batch, args.n, args.m, args.dist),
+        "batch_per_gpu": batch, "n": args.n, "m": args.m, "distribution": args.dist,
+        "tolerance": 1e-9, "parallelism": "problem-sharded, no collective",
+        "l2": "inputs (%.1f GB per GPU) larger than L2; every step re-reads them from HBM"
+              % (batch * (args.n * args.m + args.n + args.m) * 8 / 1e9),
+    }
+
+
+# ------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.lines = []
+        self.proc = None
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+                power.append(float(parts[2]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "power_w_max": float(max(power)) if power else None, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the oracle port on the host cores (bounded sample of the same workload)
+# ------------------------------------------------------------------------------------------
+def cpu_sample_size(args, oracle, workloads, target_s=12.0):
+    """Pick a sample of the first LPs of the shard worth ~target_s of wall time on all cores."""
+    A, b, c = workloads.simplex_batch(args.dist, 64, args.n, args.m, seed=2)
+    t0 = time.perf_counter()
+    oracle.simplex_batch(A, b, c, max_pivots=50000, threads=0)
+    dt = max(time.perf_counter() - t0, 1e-4)
+    rate = 64 / dt
+    cnt = int(min(args.batch, max(64, rate * target_s)))
+    return (cnt + 63) // 64 * 64
+
+
+def run_cpu_baseline(args, sample=None, repeats=1):
+    import oracle
+    from linear_programming_b200 import workloads
+    oracle.build()
+    if sample is None:
+        sample = cpu_sample_size(args, oracle, workloads)
+    A, b, c = workloads.simplex_batch(args.dist, sample, args.n, args.m, seed=2)
+    best = None
+    piv = 0
+    used = 1
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        st, x, obj, npiv, used = oracle.simplex_batch(A, b, c, max_pivots=50000, threads=0)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+        piv = int(npiv.sum())
+    return {"value": sample / best, "unit": UNIT, "cores": used, "kind": "port",
+            "sample": "first %d LPs of the same %s batch, C oracle (bit-exact restatement of "
+                      "week-2/diet/simplex.py), one LP per host thread, %.2f s" % (sample, args.dist, best),
+            "pivots_per_s": piv / best, "seconds": best, "lps": sample}
+
+
+def reference_arm(args):
+    """--impl reference: the CPU implementation of the path on all host threads.  The reference
+    solver itself is pure Python under /root/reference (absent on the GPU box, cannot be
+    copied), so this times the oracle port; each step is a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    from linear_programming_b200 import workloads
+    oracle.build()
+    sample = cpu_sample_size(args, oracle, workloads, target_s=6.0)
+    A, b, c = workloads.simplex_batch(args.dist, sample, args.n, args.m, seed=2)
+    used = 1
+    for _ in range(args.warmup):
+        oracle.simplex_batch(A[:64], b[:64], c[:64], max_pivots=50000, threads=0)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        _, _, _, npiv, used = oracle.simplex_batch(A, b, c, max_pivots=50000, threads=0)
+    dt = time.perf_counter() - t0
+    value = sample * args.steps / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": config_dict(args, args.batch),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": used, "kind": "port",
+                         "sample": "each step = first %d LPs of the %s batch on %d host threads"
+                                   % (sample, args.dist, used)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "pivots_per_s": float(npiv.sum()) * args.steps / dt,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------
+def ours_arm(args):
+    import ctypes
+    import torch
+    import torch.distributed as dist
+    from linear_programming_b200 import _lib, workloads
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local_rank])
+
+    def max_over_ranks(v: float) -> float:
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(v: float) -> float:
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    L = _lib.lib()
+    B, n, m = args.batch, args.n, args.m
+    tol, cap = 1e-9, 50000
+    # this rank's shard of the global problem sequence (problem index = rank*B + p)
+    A, b, c = workloads.simplex_batch(args.dist, B, n, m, seed=2, start=rank * B)
+    hA, hb, hc = (torch.from_numpy(v).pin_memory() for v in (A, b, c))
+    del A, b, c
+    dA, db, dc = (v.to(dev, non_blocking=True) for v in (hA, hb, hc))
+    d_st = torch.empty(B, dtype=torch.int32, device=dev)
+    d_x = torch.empty((B, m), dtype=torch.float64, device=dev)
+    d_obj = torch.empty(B, dtype=torch.float64, device=dev)
+    d_np = torch.empty(B, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+
+    def step():
+        _lib.check(L.lpb200_simplex_batch_device(B, n, m, dA.data_ptr(), db.data_ptr(), dc.data_ptr(), tol, cap,
+                                                 d_st.data_ptr(), d_x.data_ptr(), d_obj.data_ptr(),
+                                                 d_np.data_ptr(), None, 0, stream))
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank)
+    K = args.steps
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
+    barrier()
+    torch.cuda.synchronize()
+    sampler.start()
+    evs[0].record()
+    for k in range(K):
+        step()
+        evs[k + 1].record()
+    torch.cuda.synchronize()
+    barrier()
+    clocks = sampler.stop()
+    total_ms = max_over_ranks(evs[0].elapsed_time(evs[K]))
+    kern_ms = [evs[k].elapsed_time(evs[k + 1]) for k in range(K)]
+    pivots_step = int(d_np.sum().item())
+    value = world * B * K / (total_ms * 1e-3)
+    peak, peak_src = measured_peak()
+    avg_kern_s = float(np.mean(kern_ms)) * 1e-3
+    alg_bytes = 16.0 * (n + 1) * (m + 1) * pivots_step
+    achieved = alg_bytes / avg_kern_s / 1e9
+    input_bytes = B * (n * m + n + m) * 8 + B * (m * 8 + 16)
+    roofline = {
+        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        "traffic": None, "kernel": "simplex_batched_kernel", "launch_ms": avg_kern_s * 1e3,
+        "algorithmic_bytes_per_launch": alg_bytes, "pivots_per_launch": pivots_step,
+        "peak_source": peak_src,
+        "note": "tableau is shared-memory resident: 'achieved' is EFFECTIVE GB/s (16*(n+1)*(m+1) B per pivot, "
+                "SURVEY 8(d)) and may exceed the HBM peak; compulsory HBM traffic per launch is %.3f GB "
+                "(inputs once + results once)" % (input_bytes / 1e9),
+    }
+    all_pivots = sum_over_ranks(float(pivots_step))
+
+    # ---- parity spot check + CPU baseline (rank 0, outside every timed region) ----
+    cpu = None
+    parity = None
+    if rank == 0 and not args.no_cpu_baseline:
+        import oracle
+        oracle.build()
+        cpu = run_cpu_baseline(args)
+        s = cpu["lps"]
+        A0, b0, c0 = workloads.simplex_batch(args.dist, s, n, m, seed=2, start=0)
+        st, x, obj, npiv, _ = oracle.simplex_batch(A0, b0, c0, max_pivots=cap)
+        ok = (np.array_equal(d_st[:s].cpu().numpy(), st) and np.array_equal(d_np[:s].cpu().numpy(), npiv)
+              and np.array_equal(d_x[:s].cpu().numpy().view(np.int64), x.view(np.int64)))
+        parity = {"checked_lps": int(s), "bit_exact_vs_oracle": bool(ok)}
+        cpu = {k: v for k, v in cpu.items() if k not in ("seconds", "lps")}
+
+    # ---- end to end through the C ABI with host (pinned) buffers ----
+    e2e = None
+    if not args.no_e2e:
+        h_st = torch.empty(B, dtype=torch.int32).pin_memory()
+        h_x = torch.empty((B, m), dtype=torch.float64).pin_memory()
+        h_obj = torch.empty(B, dtype=torch.float64).pin_memory()
+        h_np = torch.empty(B, dtype=torch.int32).pin_memory()
+
+        def e2e_step():
+            _lib.check(L.lpb200_simplex_batch(B, n, m, hA.data_ptr(), hb.data_ptr(), hc.data_ptr(), tol, cap,
+                                              h_st.data_ptr(), h_x.data_ptr(), h_obj.data_ptr(),
+                                              h_np.data_ptr(), None, 0))
+        Ke = max(1, min(K, 3))
+        e2e_step()  # warm-up
+        barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(Ke):
+            e2e_step()   # synchronous: returns after the last device->host copy
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        barrier()
+        same = bool(torch.equal(h_st, d_st.cpu()) and torch.equal(h_np, d_np.cpu())
+                    and torch.equal(h_x.view(torch.int64), d_x.cpu().view(torch.int64)))
+        e2e = {"value": world * B * Ke / dt, "unit": UNIT,
+               "h2d_bytes_per_step": int(B * (n * m + n + m) * 8),
+               "d2h_bytes_per_step": int(B * (m * 8 + 8 + 4 + 4)), "steps": Ke,
+               "ms_per_step": dt / Ke * 1e3, "matches_device_path": same,
+               "api": "lpb200_simplex_batch (host pointers, pinned; chunked 2-stream copy/solve pipeline)"}
+
+    # ---- extra: pivot-heavy distribution D2 on a smaller batch (pivots/s), rank 0 only, untimed region ----
+    extra = {}
+    if rank == 0 and args.dist == "D1":
+        B2 = min(B, 4096)
+        A2, b2, c2 = (torch.from_numpy(v).to(dev) for v in workloads.simplex_batch("D2", B2, n, m, seed=2))
+        st2 = torch.empty(B2, dtype=torch.int32, device=dev)
+        np2 = torch.empty(B2, dtype=torch.int32, device=dev)
+        x2 = torch.empty((B2, m), dtype=torch.float64, device=dev)
+        o2 = torch.empty(B2, dtype=torch.float64, device=dev)
+
+        def step2():
+            _lib.check(L.lpb200_simplex_batch_device(B2, n, m, A2.data_ptr(), b2.data_ptr(), c2.data_ptr(), tol,
+                                                     cap, st2.data_ptr(), x2.data_ptr(), o2.data_ptr(),
+                                                     np2.data_ptr(), None, 0, stream))
+        step2()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        step2()
+        e1.record()
+        torch.cuda.synchronize()
+        ms2 = e0.elapsed_time(e1)
+        piv2 = int(np2.sum().item())
+        extra = {"D2_batch": B2, "D2_ms": ms2, "D2_pivots": piv2, "D2_pivots_per_s": piv2 / (ms2 * 1e-3),
+                 "D2_lps_per_s": B2 / (ms2 * 1e-3),
+                 "D2_effective_GBps": 16.0 * (n + 1) * (m + 1) * piv2 / (ms2 * 1e-3) / 1e9}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(args.warmup, 3),
+            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": config_dict(args, B),
+            "pivots_per_s": all_pivots * K / (total_ms * 1e-3), "clocks": clocks,
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": K,
+            "parity": parity, "extra": extra,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        ours_arm(args)
+
+
+if __name__ == "__main__":
+    main()
