@@ -91,6 +91,45 @@ int lpb200_simplex_single(int n, int m, const double *A, const double *b, const 
                           int32_t *npivots, int32_t *pivot_log, int log_cap, double *stats);
 
 /*
+ * Single large LP, COLUMN-SHARDED over the GPUs of one NVLink/NVSwitch box (SURVEY.md 8(e),
+ * BASELINE.json configs[4]).  One process per GPU; rank g owns column positions
+ * [g*W, (g+1)*W) of every tableau row (W from lpb200_simplex_sharded_columns); per pivot the
+ * ranks exchange an 8-byte entering key (all-to-all, min) and the owner of the entering
+ * column broadcasts it (n+1 doubles) -- both from inside the persistent kernel, as flagged
+ * packets written straight into peer-mapped exchange buffers.  Same semantics and outputs as
+ * lpb200_simplex_single (every rank receives the full status / x / objective / pivot log).
+ *
+ * Communicator: lpb200_comm_create allocates this rank's exchange buffer on the current
+ * device and returns an opaque lpb200_comm_handle_bytes()-byte handle; the caller gathers
+ * the handles of all ranks (any transport, e.g. torch.distributed.all_gather) and passes
+ * the concatenation, in rank order, to lpb200_comm_connect (CUDA IPC + peer access).  All
+ * ranks must call lpb200_simplex_sharded_device the same number of times with the same
+ * (n, m, tol, max_pivots).  A rank that receives no packet for timeout_s seconds (<= 0: 20 s)
+ * aborts its kernel (the CUDA context reports a launch failure) instead of hanging the GPU.
+ *   A_cols   this rank's columns of A: A_cols[i*lda + j] = A[i][c_lo + j], j < c_count
+ *   b, c     full vectors (replicated on every rank)
+ */
+typedef struct lpb200_comm lpb200_comm_t;
+int64_t lpb200_comm_handle_bytes(void);
+int lpb200_comm_create(int rank, int nranks, int max_n, lpb200_comm_t **comm, void *handle_out);
+int lpb200_comm_connect(lpb200_comm_t *comm, const void *all_handles);
+int lpb200_comm_destroy(lpb200_comm_t *comm);
+int lpb200_simplex_sharded_columns(int m, int nranks, int rank, int *c_lo, int *c_count);
+int64_t lpb200_simplex_sharded_workspace_bytes(int n, int m, int nranks);
+int lpb200_simplex_sharded_device(lpb200_comm_t *comm, int n, int m, const double *A_cols, int64_t lda,
+                                  const double *b, const double *c, double tol, int max_pivots,
+                                  int32_t *status, double *x, double *objective, int32_t *npivots,
+                                  int32_t *pivot_log, int log_cap, void *workspace, int64_t workspace_bytes,
+                                  double timeout_s, void *stream);
+/* The same nranks-way protocol with every rank run as a CTA group of ONE cooperative launch
+ * on the current device (HOST pointers; outputs are per rank: status[nranks], x[nranks][m],
+ * objective[nranks], npivots[nranks], pivot_log[nranks][log_cap][2]).  For parity tests and
+ * for boxes with fewer GPUs than ranks. */
+int lpb200_simplex_sharded_emulated(int nranks, int n, int m, const double *A, const double *b,
+                                    const double *c, double tol, int max_pivots, int32_t *status, double *x,
+                                    double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap);
+
+/*
  * Batched Gauss-Jordan: B independent n x n systems a.x = b.
  * Replaces, per system, SolveEquation(Equation{a,b})           energy_values.cc:166-197.
  *   a[B][n][n], b[B][n]  inputs (not modified);  x[B][n]  solution (b after the last step).

@@ -9,6 +9,8 @@ from .simplex import (BatchResult, IterationLimitError, Simplex, allocate_ads, s
                       solve_diet_problem)
 from .gauss_jordan import solve_equation, solve_equation_batch
 from ._lib import EngineError
+from .sharded import ShardedComm, column_shard, problem_shard, solve_sharded_emulated
 
 __all__ = ["Simplex", "solve", "solve_batch", "BatchResult", "allocate_ads", "solve_diet_problem",
-           "solve_equation", "solve_equation_batch", "EngineError", "IterationLimitError"]
+           "solve_equation", "solve_equation_batch", "EngineError", "IterationLimitError", "ShardedComm", "column_shard", "problem_shard",
+           "solve_sharded_emulated"]

@@ -1,16 +1,21 @@
-// simplex_single.cu -- grid-wide two-phase simplex for ONE large dense LP (sm_100a).
+// simplex_single.cu -- grid-wide two-phase simplex for ONE large dense LP (sm_100a), on one
+// GPU or COLUMN-SHARDED over the GPUs of one NVLink/NVSwitch box.
 //
 // Same semantics as simplex_batched.cu (the reference's Simplex.solve(),
 // week-2/diet/simplex.py:586-630) but the condensed tableau ((n+1) x (m+1) fp64, 4.3 GB at
 // 16384 x 32768) lives in HBM and every pivot is ONE streaming read-modify-write sweep over
-// it by all 148 SMs.  One cooperative persistent kernel runs the whole solve; per pivot:
+// it by all SMs.  One cooperative persistent kernel per GPU runs the whole solve; per pivot:
 //
 //   P1  entering column   every CTA scans a slice of the objective row, block-reduces the
 //                         packed key (set slot << 32 | position), writes one partial     (:390-392)
-//   P2  leaving row       every CTA reduces the partials (-> p), gathers a slice of pivot
-//                         column p into the contiguous buffer fc[], does the min-ratio
-//                         test on it (ratio, variable id) and writes one partial          (:394-436)
-//   P3  pivot row         partials -> (l, r); nr[] = snap(pinv * row r), column p zeroed  (:325-345)
+//       [ranks > 1]       KEY EXCHANGE: every rank pushes its 8-byte key into every peer's
+//                         exchange buffer over NVLink (all-to-all of 16-byte LL packets,
+//                         data+epoch flag in each 8-byte word, no fence) and takes the min
+//   P2  leaving row       the rank that owns column p gathers it and BROADCASTS it (n+1
+//                         doubles as LL packets) into every rank's buffer; every rank decodes
+//                         it into fc[] and runs the min-ratio test redundantly on the
+//                         replicated constant column -> identical (l, r) everywhere       (:394-436)
+//   P3  pivot row         nr[] = snap(pinv * row r) on the rank's own columns             (:325-345)
 //   P4  rank-1 sweep      tiles of 64 rows x 512 columns: the tile's slice of the pivot
 //                         row nr[] and of the pivot column fc[] are staged in shared memory
 //                         by TMA bulk copies (cp.async.bulk + mbarrier, double-buffered
@@ -18,14 +23,23 @@
 //                         and streams the rows with 128-bit loads/stores, 8 rows in flight:
 //                         T[i][k] = snap(T[i][k] + fc[i]*nr[k]), no FMA                  (:348-362, 185-214)
 //   grid.sync() between phases (4 per pivot, ~1 % of a 1.3 ms sweep).
-// The constant column b is kept contiguous (bcol[]) so the ratio test reads it coalesced.
-// Set bookkeeping (CPython set order, :369-381) is done by one thread at the start of P4,
-// overlapped with the sweep.  Tensor cores are not used: the update is a rank-1 AXPY at
-// 0.125 flop/byte, HBM-bound by construction.
+//
+// Column sharding: rank g owns column positions [g*Wc, (g+1)*Wc) of ALL rows
+// incl. the objective row; the constant column, the basis/slot tables and the CPython-set
+// emulation are replicated and updated identically by every rank, so the only traffic per
+// pivot is the 8-byte key all-to-all and the pivot-column broadcast: compute and collective
+// are ONE kernel working on peer-mapped memory, no NCCL call and no host round trip on the
+// pivot path.  Waits are bounded: a rank that sees no packet for `timeout` traps instead of
+// hanging the GPU.  For tests (and boxes with fewer GPUs than ranks) the same kernel runs all
+// ranks as CTA groups of one cooperative launch ("emulated"), which makes every wait safe.
+//
+// Tensor cores are not used: the update is a rank-1 AXPY at 0.125 flop/byte, HBM-bound.
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <math_constants.h>
 #include <stdint.h>
+
+#include <vector>
 
 #include "lp_common.cuh"
 #include "lp_host.h"
@@ -38,42 +52,56 @@ constexpr int kSgThreads = 256;
 constexpr int kTileCols = 2 * kSgThreads;  // 512 doubles: one double2 per thread
 constexpr int kTileRows = 64;
 constexpr int kRowUnroll = 8;
+constexpr int kMaxRanks = 32;
 
-enum {
-    ST_STATUS = 0, ST_NPIV, ST_ISIZE, ST_IFILL, ST_IUSED, ST_DSIZE, ST_DFILL, ST_DUSED, ST_NLIST,
-    ST_COUNT = 16
-};
+enum { ST_ISIZE = 0, ST_IFILL, ST_IUSED, ST_DSIZE, ST_DFILL, ST_DUSED, ST_NLIST, ST_COUNT = 16 };
 
-// Device-side view of the workspace (all pointers into one caller-owned buffer).
+// Exchange buffer of one rank, in 8-byte words.  Every payload word is an "LL" word:
+// low 32 bits data, high 32 bits the epoch of the exchange that wrote it.
+constexpr int kXbEpoch = 0;  // running epoch, persists across solves on the same communicator
+constexpr int kXbKeys = 8;   // [2][nranks] packets of 2 words (double-buffered by exchange parity)
+__host__ __device__ inline int xb_fc(int nranks) { return kXbKeys + 4 * nranks; }  // [(n+2)] packets
+static inline size_t xbuf_bytes_for(int n, int nranks)
+{
+    return ((size_t)(xb_fc(nranks) + 2 * (n + 2)) * 8 + 255) / 256 * 256;
+}
+
+// Per-rank device view: workspace carve-up, column range, exchange buffers, outputs.
 struct SingleWS {
-    int n, m, S;      // S: tableau row stride in doubles (multiple of 16)
+    int n, m, S;                  // S: LOCAL row stride in doubles (multiple of 16) = positions per rank
+    int rank, nranks, c_lo, wloc; // owns global column positions [c_lo, c_lo + wloc)
     int size_i0, size_i1, size_d0, cap_i, cap_d, cap_s;
-    double *T;        // [(n+1)][S]  non-basic columns only; row n = objective
-    double *bcol;     // [n+1]       constant column (b, then v at index n)
-    double *nr;       // [S]         scaled pivot row
-    double *fc;       // [n+1]       pivot column factors
-    double *cstage;   // [m]         scratch: original c / rebuilt objective
-    double *scal;     // [4]         nr constant, misc scalars
-    int *rowvar, *nonecol, *untouched, *rowslot;  // [n]
-    int *colvar, *colslot;                        // [m+1]
-    int *varpos;                                  // [n+m+1]
-    unsigned *basis0;                             // bitmask over variables
+    const double *A;              // this rank's columns of A: A[i*lda + (k - c_lo)]
+    long long lda;
+    double *T;                    // [(n+1)][S]  owned non-basic columns; row n = objective
+    double *bcol;                 // [n+1]       constant column (b, then v at index n), replicated
+    double *nr;                   // [S]         scaled pivot row, owned columns
+    double *fc;                   // [n+1]       pivot column factors, replicated
+    double *cstage;               // scratch: factors of the objective rebuild
+    double *scal;                 // [4]         nr constant
+    int *rowvar, *nonecol, *untouched, *rowslot;  // [n]      replicated
+    int *colvar, *colslot;                        // [m+1]    replicated (global positions)
+    int *varpos;                                  // [n+m+1]  replicated
+    unsigned *basis0;
     int *tab_i, *tab_d, *tab_s;
-    int *list;                                    // [n]
-    unsigned long long *part_key;                 // [2][grid]  set 0: entering, set 1: leaving
-    int *part_var, *part_crash;                   // [2][grid]
-    int *state;                                   // [ST_COUNT]
+    int *list;
+    unsigned long long *part_key;                 // [2][ctas]  set 0: entering, set 1: leaving
+    int *part_var, *part_crash;
+    int *state;
+    unsigned long long *xbuf;                     // this rank's exchange buffer (nranks > 1)
+    unsigned long long *const *peers;             // [nranks] every rank's exchange buffer, peer-mapped
+    int32_t *status;
+    double *x, *objective;
+    int32_t *npivots, *pivot_log;
 };
 
 struct SingleArgs {
-    const double *A, *b, *c;
+    const double *b, *c;
     double tol;
     int max_pivots;
-    int32_t *status;
-    double *x, *objective;
-    int32_t *npivots;
-    int32_t *pivot_log;
     int log_cap;
+    int cpr;  // CTAs per rank in this launch
+    unsigned long long timeout_ns;
 };
 
 // ---- small PTX wrappers: mbarrier + TMA bulk copy (global -> shared) ----
@@ -106,6 +134,38 @@ __device__ __forceinline__ void tma_load_1d(void *dst_smem, const void *src_gmem
                  : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// ---- LL packets over peer-mapped memory: 16 bytes = two (data32 | epoch32) words ----
+// Only 8-byte store atomicity is relied on: the reader accepts a packet when BOTH words
+// carry the expected epoch, so no fence and no separate flag round trip is needed.
+__device__ __forceinline__ void ll_store(unsigned long long *dst, unsigned long long v, unsigned ep)
+{
+    const unsigned long long w0 = (v & 0xffffffffull) | ((unsigned long long)ep << 32);
+    const unsigned long long w1 = (v >> 32) | ((unsigned long long)ep << 32);
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(w0), "l"(w1) : "memory");
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ unsigned long long ll_load(const unsigned long long *src, unsigned ep,
+                                                      unsigned long long timeout_ns)
+{
+    unsigned long long w0, w1, t0 = 0;
+    unsigned spins = 0;
+    for (;;) {
+        asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(src) : "memory");
+        if ((unsigned)(w0 >> 32) == ep && (unsigned)(w1 >> 32) == ep) break;
+        if ((++spins & 0xfffu) == 0) {  // bounded wait: a dead peer must not hang the GPU
+            const unsigned long long t = globaltimer_ns();
+            if (t0 == 0) t0 = t;
+            else if (t - t0 > timeout_ns) __trap();
+        }
+    }
+    return (w0 & 0xffffffffull) | (w1 << 32);
+}
 
 // ---- block-level lexicographic argmin; result broadcast to every thread ----
 struct BlockRed {
@@ -141,15 +201,26 @@ __device__ __forceinline__ void block_argmin(BlockRed &br, unsigned long long &k
     }
 }
 
+// Per-thread loop state (uniform across all threads of all ranks).
+struct LoopCtl {
+    int bid, nblk;    // CTA index within this rank's group, CTAs per rank
+    int ncols;        // column positions alive (m, or m+1 once phase 1 has run)
+    int npiv;
+    bool track_dep;
+    uint32_t parity;  // mbarrier phase bits of the two sweep stages
+    unsigned epoch;   // exchange epoch (continues across solves)
+    unsigned kx;      // key exchanges so far (parity selects the key buffer)
+};
+
 // Reduce the per-CTA partials written before the last grid.sync().
-__device__ __forceinline__ void reduce_partials(BlockRed &br, const SingleWS &w, int set,
+__device__ __forceinline__ void reduce_partials(BlockRed &br, const SingleWS &w, const LoopCtl &ctl, int set,
                                                 unsigned long long &key, int &var, int &flag)
 {
     key = kKeyNone;
     var = 0x7fffffff;
     flag = 0;
-    const int lo = set * (int)gridDim.x;
-    for (int q = lo + threadIdx.x; q < lo + (int)gridDim.x; q += kSgThreads) {
+    const int lo = set * ctl.nblk;
+    for (int q = lo + threadIdx.x; q < lo + ctl.nblk; q += kSgThreads) {
         const unsigned long long k = w.part_key[q];
         const int v = w.part_var[q];
         if (k < key || (k == key && v < var)) {
@@ -161,43 +232,89 @@ __device__ __forceinline__ void reduce_partials(BlockRed &br, const SingleWS &w,
     block_argmin(br, key, var, flag);
 }
 
-__device__ __forceinline__ void write_partial(const SingleWS &w, int set, unsigned long long key, int var,
-                                              int flag)
+__device__ __forceinline__ void write_partial(const SingleWS &w, const LoopCtl &ctl, int set,
+                                              unsigned long long key, int var, int flag)
 {
     if (threadIdx.x == 0) {
-        const int q = set * (int)gridDim.x + (int)blockIdx.x;
+        const int q = set * ctl.nblk + ctl.bid;
         w.part_key[q] = key;
         w.part_var[q] = var;
         w.part_crash[q] = flag;
     }
 }
 
-// ---- P1: entering column (pick_entering_idx :390-392) ----
-__device__ __forceinline__ void phase_entering(BlockRed &br, const SingleWS &w, int ncols, double tol)
+// ---- P1: entering column (pick_entering_idx :390-392), own columns only ----
+__device__ __forceinline__ void phase_entering(BlockRed &br, const SingleWS &w, const LoopCtl &ctl, double tol)
 {
     unsigned long long key = kKeyNone;
     int var = 0, flag = 0;
     const double *obj = w.T + (size_t)w.n * w.S;
-    for (int k = blockIdx.x * kSgThreads + threadIdx.x; k < ncols; k += gridDim.x * kSgThreads) {
-        if (obj[k] > tol) {
+    const int lim = min(w.wloc, ctl.ncols - w.c_lo);
+    for (int kl = ctl.bid * kSgThreads + threadIdx.x; kl < lim; kl += ctl.nblk * kSgThreads) {
+        if (obj[kl] > tol) {
+            const int k = w.c_lo + kl;
             const unsigned long long kk = ((unsigned long long)(unsigned)w.colslot[k] << 32) | (unsigned)k;
             key = kk < key ? kk : key;
         }
     }
     block_argmin(br, key, var, flag);
-    write_partial(w, 0, key, var, flag);
+    write_partial(w, ctl, 0, key, var, flag);
 }
 
-// ---- P2: gather pivot column p into fc[], min-ratio test on it (pick_leaving_idx :394-436) ----
-__device__ __forceinline__ void phase_ratio(BlockRed &br, const SingleWS &w, int p, int e, double tol)
+// ---- all-to-all of the ranks' entering keys over NVLink, min on arrival ----
+__device__ __forceinline__ unsigned long long exchange_key(BlockRed &br, const SingleWS &w, LoopCtl &ctl,
+                                                           unsigned long long key, unsigned long long timeout_ns)
+{
+    if (w.nranks == 1) return key;
+    const int tid = threadIdx.x, G = w.nranks;
+    const unsigned ep = ++ctl.epoch;
+    const int buf = (int)(ctl.kx++ & 1u);
+    if (ctl.bid == 0 && tid < G) ll_store(w.peers[tid] + kXbKeys + 2 * (buf * G + w.rank), key, ep);
+    __syncthreads();  // previous readers of br are done
+    if (tid < 32) {
+        unsigned long long k = kKeyNone;
+        if (tid < G) k = ll_load(w.xbuf + kXbKeys + 2 * (buf * G + tid), ep, timeout_ns);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const unsigned long long o = __shfl_xor_sync(0xffffffffu, k, off);
+            k = o < k ? o : k;
+        }
+        if (tid == 0) br.key[0] = k;
+    }
+    __syncthreads();
+    return br.key[0];
+}
+
+// ---- P2: pivot column p -> fc[] on every rank, min-ratio test on it (pick_leaving_idx :394-436) ----
+__device__ __forceinline__ void phase_ratio(BlockRed &br, const SingleWS &w, LoopCtl &ctl, int p, int e,
+                                            double tol, unsigned long long timeout_ns)
 {
     unsigned long long key = kKeyNone;
     int var = 0x7fffffff, crash = 0;
-    const int n = w.n;
+    const int n = w.n, G = w.nranks;
+    const int owner = p / w.S, pl = p - owner * w.S;
+    const bool mine = (owner == w.rank);
     const bool e_in_basis0 = (w.basis0[e >> 5] >> (e & 31)) & 1u;
-    for (int i = blockIdx.x * kSgThreads + threadIdx.x; i <= n; i += gridDim.x * kSgThreads) {
-        const double f = w.T[(size_t)i * w.S + p];
-        w.fc[i] = (fabs(f) <= tol) ? 0.0 : f;  // substitute() skips a zero coefficient (:203-205)
+    unsigned ep = 0;
+    unsigned long long *fcll = nullptr;
+    if (G > 1) {
+        ep = ++ctl.epoch;
+        fcll = w.xbuf + xb_fc(G);
+    }
+    for (int i = ctl.bid * kSgThreads + threadIdx.x; i <= n; i += ctl.nblk * kSgThreads) {
+        double f = 0.0;
+        if (mine) {
+            f = w.T[(size_t)i * w.S + pl];
+            if (fabs(f) <= tol) f = 0.0;  // substitute() skips a zero coefficient (:203-205)
+        }
+        if (G > 1) {
+            if (mine) {  // broadcast: one LL packet per element into every rank's buffer
+                const unsigned long long bits = (unsigned long long)__double_as_longlong(f);
+                for (int g = 0; g < G; ++g) ll_store(w.peers[g] + xb_fc(G) + 2 * i, bits, ep);
+            }
+            f = __longlong_as_double((long long)ll_load(fcll + 2 * i, ep, timeout_ns));
+        }
+        w.fc[i] = f;
         if (i < n) {
             const int nc = w.nonecol[i];
             crash |= (nc == kNoneInitial && e < n) || (nc == e) || (w.untouched[i] && e_in_basis0);
@@ -216,23 +333,27 @@ __device__ __forceinline__ void phase_ratio(BlockRed &br, const SingleWS &w, int
         }
     }
     block_argmin(br, key, var, crash);
-    write_partial(w, 1, key, var, crash);
+    write_partial(w, ctl, 1, key, var, crash);
 }
 
 // ---- P3: scaled pivot row (make_pivot_constraint :325-345), zero column p, None bookkeeping ----
-__device__ __forceinline__ void phase_pivot_row(const SingleWS &w, int ncols, int p, int r, int e, double tol)
+__device__ __forceinline__ void phase_pivot_row(const SingleWS &w, const LoopCtl &ctl, int p, int r, int e,
+                                                double tol)
 {
-    const int gtid = blockIdx.x * kSgThreads + threadIdx.x, gsize = gridDim.x * kSgThreads;
+    const int gtid = ctl.bid * kSgThreads + threadIdx.x, gsize = ctl.nblk * kSgThreads;
     const double pinv = pivot_inverse(w.fc[r], tol);
     const double *Tr = w.T + (size_t)r * w.S;
-    for (int k = gtid; k < w.S; k += gsize) {
+    const int lim = min(w.wloc, ctl.ncols - w.c_lo);
+    for (int kl = gtid; kl < w.S; kl += gsize) {
         double v = 0.0;
-        if (k < ncols) v = (k == p) ? snap(-pinv, tol) : snap(__dmul_rn(pinv, Tr[k]), tol);
-        w.nr[k] = v;
+        if (kl < lim) v = (w.c_lo + kl == p) ? snap(-pinv, tol) : snap(__dmul_rn(pinv, Tr[kl]), tol);
+        w.nr[kl] = v;
     }
     if (gtid == 0) w.scal[0] = snap(__dmul_rn(pinv, w.bcol[r]), tol);
+    const int owner = p / w.S, pl = p - owner * w.S;
+    const bool mine = (owner == w.rank);
     for (int i = gtid; i <= w.n; i += gsize) {
-        if (i != r) w.T[(size_t)i * w.S + p] = 0.0;
+        if (mine && i != r) w.T[(size_t)i * w.S + pl] = 0.0;
         if (i < w.n && (w.fc[i] != 0.0 || i == r)) {
             w.nonecol[i] = e;
             w.untouched[i] = 0;
@@ -241,7 +362,7 @@ __device__ __forceinline__ void phase_pivot_row(const SingleWS &w, int ncols, in
     fence_proxy_async();  // nr[] / fc[] are read back through the async proxy (TMA) in P4
 }
 
-// ---- set bookkeeping (set_replace :369-381), one thread, tables in global memory ----
+// ---- set bookkeeping (set_replace :369-381), one thread per rank, tables in global memory ----
 __device__ void single_bookkeeping(const SingleWS &w, bool track_dep, int p, int r, int e, int l)
 {
     const int eslot = w.colslot[p];
@@ -300,18 +421,18 @@ __device__ __forceinline__ void sweep_issue(SweepSmem &sm, const SingleWS &w, in
     tma_load_1d(sm.fc[stage], w.fc + r0, bfc, &sm.bar[stage]);
 }
 
-__device__ __forceinline__ void phase_sweep(SweepSmem &sm, const SingleWS &w, int ncols, int r, double tol,
-                                            uint32_t &parity)
+__device__ __forceinline__ void phase_sweep(SweepSmem &sm, const SingleWS &w, LoopCtl &ctl, int r, double tol)
 {
     const int tid = threadIdx.x;
     const int n = w.n, S = w.S;
-    const int nstrips = (ncols + kTileCols - 1) / kTileCols;
+    const int lcols = max(0, min(w.wloc, ctl.ncols - w.c_lo));
+    const int nstrips = (lcols + kTileCols - 1) / kTileCols;
     const int nrb = (n + 1 + kTileRows - 1) / kTileRows;
     const int ntiles = nstrips * nrb;
-    // constant column: b_i = snap(b_i + f_i * nr_const); the pivot row's constant is nr_const
+    // constant column (replicated): b_i = snap(b_i + f_i * nr_const); the pivot row's constant is nr_const
     {
         const double nrc = w.scal[0];
-        for (int i = blockIdx.x * kSgThreads + tid; i <= n; i += gridDim.x * kSgThreads) {
+        for (int i = ctl.bid * kSgThreads + tid; i <= n; i += ctl.nblk * kSgThreads) {
             if (i == r) {
                 w.bcol[i] = nrc;
             } else {
@@ -320,16 +441,16 @@ __device__ __forceinline__ void phase_sweep(SweepSmem &sm, const SingleWS &w, in
             }
         }
     }
-    int tile = blockIdx.x;
+    int tile = ctl.bid;
     if (tile < ntiles && tid == 0) {
         fence_proxy_async();
         sweep_issue(sm, w, 0, tile, nstrips);
     }
-    for (int it = 0; tile < ntiles; tile += gridDim.x, ++it) {
+    for (int it = 0; tile < ntiles; tile += ctl.nblk, ++it) {
         const int stage = it & 1;
-        if (tid == 0 && tile + (int)gridDim.x < ntiles) sweep_issue(sm, w, stage ^ 1, tile + gridDim.x, nstrips);
-        mbar_wait(&sm.bar[stage], (parity >> stage) & 1u);
-        parity ^= 1u << stage;
+        if (tid == 0 && tile + ctl.nblk < ntiles) sweep_issue(sm, w, stage ^ 1, tile + ctl.nblk, nstrips);
+        mbar_wait(&sm.bar[stage], (ctl.parity >> stage) & 1u);
+        ctl.parity ^= 1u << stage;
         const int strip = tile % nstrips, rb = tile / nstrips;
         const int c0 = strip * kTileCols, r0 = rb * kTileRows;
         const int rows = min(kTileRows, n + 1 - r0);
@@ -364,47 +485,41 @@ __device__ __forceinline__ void phase_sweep(SweepSmem &sm, const SingleWS &w, in
     }
 }
 
-struct LoopCtl {
-    int ncols;
-    int npiv;
-    bool track_dep;
-    uint32_t parity;
-};
-
 // P3 + P4 of one pivot: e sits at column position p, l owns row r.
 __device__ __forceinline__ void single_pivot(cg::grid_group &grid, SweepSmem &sm, const SingleWS &w,
                                              const SingleArgs &a, LoopCtl &ctl, int p, int r, int e, int l)
 {
-    phase_pivot_row(w, ctl.ncols, p, r, e, a.tol);
+    phase_pivot_row(w, ctl, p, r, e, a.tol);
     grid.sync();
-    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == kSgThreads - 32) {
-        if (a.pivot_log != nullptr && ctl.npiv < a.log_cap) {
-            a.pivot_log[2 * ctl.npiv] = e;
-            a.pivot_log[2 * ctl.npiv + 1] = l;
+    if (ctl.bid == ctl.nblk - 1 && threadIdx.x == kSgThreads - 32) {
+        if (w.pivot_log != nullptr && ctl.npiv < a.log_cap) {
+            w.pivot_log[2 * ctl.npiv] = e;
+            w.pivot_log[2 * ctl.npiv + 1] = l;
         }
         single_bookkeeping(w, ctl.track_dep, p, r, e, l);
     }
-    phase_sweep(sm, w, ctl.ncols, r, a.tol, ctl.parity);
+    phase_sweep(sm, w, ctl, r, a.tol);
     grid.sync();
     ++ctl.npiv;
 }
 
-// SlackForm.solve loop (:442-466); every CTA takes the same branch (all reduce the same partials).
+// SlackForm.solve loop (:442-466); every CTA of every rank takes the same branch.
 __device__ __forceinline__ int single_run_loop(cg::grid_group &grid, BlockRed &br, SweepSmem &sm,
                                                const SingleWS &w, const SingleArgs &a, LoopCtl &ctl)
 {
     for (;;) {
         unsigned long long key;
         int var, flag;
-        phase_entering(br, w, ctl.ncols, a.tol);
+        phase_entering(br, w, ctl, a.tol);
         grid.sync();
-        reduce_partials(br, w, 0, key, var, flag);
+        reduce_partials(br, w, ctl, 0, key, var, flag);
+        key = exchange_key(br, w, ctl, key, a.timeout_ns);
         if (key == kKeyNone) return 0;
         const int p = (int)(key & 0xffffffffull);
         const int e = w.colvar[p];
-        phase_ratio(br, w, p, e, a.tol);
+        phase_ratio(br, w, ctl, p, e, a.tol, a.timeout_ns);
         grid.sync();
-        reduce_partials(br, w, 1, key, var, flag);
+        reduce_partials(br, w, ctl, 1, key, var, flag);
         if (flag) return LPB200_STATUS_REF_TYPE_ERROR;
         if (key == kKeyNone) return LPB200_STATUS_INFINITY;
         if (ctl.npiv >= a.max_pivots) return LPB200_STATUS_ITERATION_LIMIT;
@@ -415,21 +530,33 @@ __device__ __forceinline__ int single_run_loop(cg::grid_group &grid, BlockRed &b
 }
 
 __global__ void __launch_bounds__(kSgThreads)
-simplex_single_kernel(const SingleWS w, const SingleArgs a)
+simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
 {
     cg::grid_group grid = cg::this_grid();
+    __shared__ SingleWS w;
     __shared__ BlockRed br;
     __shared__ __align__(128) SweepSmem sm;
     const int tid = threadIdx.x;
-    const int gtid = blockIdx.x * kSgThreads + tid, gsize = gridDim.x * kSgThreads;
-    const int n = w.n, m = w.m, S = w.S, nv = n + m + 1;
-    const double tol = a.tol;
+    LoopCtl ctl;
+    {
+        const int grp = blockIdx.x / a.cpr;
+        ctl.bid = blockIdx.x - grp * a.cpr;
+        ctl.nblk = a.cpr;
+        const unsigned *src = reinterpret_cast<const unsigned *>(ranks + grp);
+        unsigned *dst = reinterpret_cast<unsigned *>(&w);
+        for (int i = tid; i < (int)(sizeof(SingleWS) / 4); i += kSgThreads) dst[i] = src[i];
+    }
     if (tid == 0) {
         mbar_init(&sm.bar[0], 1);
         mbar_init(&sm.bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    const int gtid = ctl.bid * kSgThreads + tid, gsize = ctl.nblk * kSgThreads;
+    const int n = w.n, m = w.m, S = w.S, nv = n + m + 1;
+    const double tol = a.tol;
+    ctl.epoch = (w.nranks > 1) ? (unsigned)w.xbuf[kXbEpoch] : 0u;
+    ctl.kx = 0u;
 
     // ---- min_constant, idx = min_index(b) (:591): zeros count as +inf, first minimum wins ----
     int idx0;
@@ -445,16 +572,15 @@ simplex_single_kernel(const SingleWS w, const SingleArgs a)
             }
         }
         block_argmin(br, key, var, flag);
-        write_partial(w, 1, key, var, flag);
+        write_partial(w, ctl, 1, key, var, flag);
         grid.sync();
-        reduce_partials(br, w, 1, key, var, flag);
+        reduce_partials(br, w, ctl, 1, key, var, flag);
         idx0 = var;
     }
     const double min_c = a.b[idx0];
     const bool phase1 = (min_c < 0.0);
     int status = 0;
     if (!phase1 && !(min_c > tol)) status = LPB200_STATUS_REF_ATTRIBUTE_ERROR;  // :626
-    LoopCtl ctl;
     ctl.ncols = phase1 ? m + 1 : m;
     ctl.npiv = 0;
     ctl.track_dep = phase1;
@@ -462,22 +588,28 @@ simplex_single_kernel(const SingleWS w, const SingleArgs a)
 
     if (status == 0) {
         // ---- SlackForm.__init__ (:230-302) (+ the x_aux column of :632-660 in phase 1) ----
-        for (int i = blockIdx.x; i <= n; i += gridDim.x) {
+        for (int i = ctl.bid; i <= n; i += ctl.nblk) {
             double *Ti = w.T + (size_t)i * S;
             if (i < n) {
-                const double *Ai = a.A + (size_t)i * m;
-                for (int k = tid; k < S; k += kSgThreads) {
+                const double *Ai = w.A + (size_t)i * w.lda;
+                for (int kl = tid; kl < S; kl += kSgThreads) {
+                    const int k = w.c_lo + kl;
                     double v = 0.0;
-                    if (k < m) v = -Ai[k];
-                    else if (k == m && phase1) v = 1.0;  // -(-1), :659 then :262
-                    Ti[k] = v;
+                    if (kl < w.wloc) {
+                        if (k < m) v = -Ai[kl];
+                        else if (k == m && phase1) v = 1.0;  // -(-1), :659 then :262
+                    }
+                    Ti[kl] = v;
                 }
             } else {
-                for (int k = tid; k < S; k += kSgThreads) {
+                for (int kl = tid; kl < S; kl += kSgThreads) {
+                    const int k = w.c_lo + kl;
                     double v = 0.0;
-                    if (k < m) v = phase1 ? 0.0 : a.c[k];
-                    else if (k == m && phase1) v = -1.0;  // objective -x_aux (:644-645)
-                    Ti[k] = v;
+                    if (kl < w.wloc) {
+                        if (k < m) v = phase1 ? 0.0 : a.c[k];
+                        else if (k == m && phase1) v = -1.0;  // objective -x_aux (:644-645)
+                    }
+                    Ti[kl] = v;
                 }
             }
         }
@@ -522,7 +654,7 @@ simplex_single_kernel(const SingleWS w, const SingleArgs a)
                 status = LPB200_STATUS_ITERATION_LIMIT;
             } else {
                 // forced pivot: x_aux enters, the most negative row leaves (:524)
-                phase_ratio(br, w, m, aux, tol);  // gathers column m into fc[]; its partial is unused
+                phase_ratio(br, w, ctl, m, aux, tol, a.timeout_ns);  // column m -> fc[]; its partial is unused
                 grid.sync();
                 single_pivot(grid, sm, w, a, ctl, m, idx0, aux, idx0);
                 status = single_run_loop(grid, br, sm, w, a, ctl);  // :526
@@ -535,7 +667,7 @@ simplex_single_kernel(const SingleWS w, const SingleArgs a)
                 // ---- rebuild the original objective (:537-541) ----
                 // (a) basic ORIGINAL variables with a non-zero objective coefficient, in
                 //     iteration order of the `dependent` set: rows -> list[], factors -> cstage[]
-                if (blockIdx.x == 0 && tid < 32) {
+                if (ctl.bid == 0 && tid < 32) {
                     const int dsize = w.state[ST_DSIZE];
                     int cnt = 0;
                     for (int s0 = 0; s0 < dsize; s0 += 32) {
@@ -555,25 +687,32 @@ simplex_single_kernel(const SingleWS w, const SingleArgs a)
                     if (tid == 0) w.state[ST_NLIST] = cnt;
                 }
                 grid.sync();
-                // (b) (v, c) = (0, [None]*n + float(c)); substitute each listed row in order
+                // (b) (v, c) = (0, [None]*n + float(c)); substitute each listed row in order.
+                //     x_aux's column is dropped (:563-575) by zeroing it in place: a zero column
+                //     never enters and stays zero under the sweep, so no data moves between ranks.
                 {
                     const int nlist = w.state[ST_NLIST];
                     const int kaux = w.varpos[aux];
                     double *obj = w.T + (size_t)n * S;
-                    for (int k = gtid; k <= ctl.ncols; k += gsize) {
-                        if (k == kaux) continue;  // zip() truncates the x_aux column (:190)
+                    const int lim = min(w.wloc, ctl.ncols - w.c_lo);
+                    for (int kl = gtid; kl < lim; kl += gsize) {
+                        const int k = w.c_lo + kl;
                         double o = 0.0;
-                        if (k < ctl.ncols) {
+                        if (k != kaux) {  // zip() truncates the x_aux column (:190)
                             const int v = w.colvar[k];
                             o = (v >= n) ? a.c[v - n] : 0.0;
                             for (int t = 0; t < nlist; ++t)
-                                o = axpy_snap(o, w.cstage[t], w.T[(size_t)w.list[t] * S + k], tol);
-                            obj[k] = o;
-                        } else {  // k == ncols: the constant term
-                            for (int t = 0; t < nlist; ++t) o = axpy_snap(o, w.cstage[t], w.bcol[w.list[t]], tol);
-                            w.bcol[n] = o;
+                                o = axpy_snap(o, w.cstage[t], w.T[(size_t)w.list[t] * S + kl], tol);
                         }
+                        obj[kl] = o;
                     }
+                    if (gtid == gsize - 1) {  // the constant term (replicated)
+                        double o = 0.0;
+                        for (int t = 0; t < nlist; ++t) o = axpy_snap(o, w.cstage[t], w.bcol[w.list[t]], tol);
+                        w.bcol[n] = o;
+                    }
+                    if (kaux >= w.c_lo && kaux < w.c_lo + w.wloc)
+                        for (int i = gtid; i < n; i += gsize) w.T[(size_t)i * S + (kaux - w.c_lo)] = 0.0;
                     // clean-up (:547-551): every then-basic column becomes None in every row
                     for (int q = gtid; q < (nv + 31) / 32; q += gsize) {
                         unsigned bits = 0u;
@@ -584,31 +723,13 @@ simplex_single_kernel(const SingleWS w, const SingleArgs a)
                         w.basis0[q] = bits;
                     }
                     for (int i = gtid; i < n; i += gsize) w.untouched[i] = 1;
+                    if (gtid == 0) {  // independent.remove(nvars) (:574); the same sets live on
+                        PySet s = {w.state[ST_ISIZE], w.state[ST_IFILL], w.state[ST_IUSED]};
+                        pyset_remove_slot(w.tab_i, s, w.colslot[kaux]);
+                        w.state[ST_IUSED] = s.used;
+                    }
                 }
                 grid.sync();
-                // (c) drop x_aux (:563-575); the same two set objects live on into phase 2
-                {
-                    const int kaux = w.varpos[aux], last = ctl.ncols - 1;
-                    for (int i = gtid; i <= n; i += gsize) {
-                        double *Ti = w.T + (size_t)i * S;
-                        if (kaux != last) Ti[kaux] = Ti[last];
-                        Ti[last] = 0.0;
-                    }
-                    grid.sync();  // everyone has read varpos[aux] / colvar before they change
-                    if (gtid == 0) {
-                        PySet s = {w.state[ST_ISIZE], w.state[ST_IFILL], w.state[ST_IUSED]};
-                        pyset_remove_slot(w.tab_i, s, w.colslot[kaux]);  // independent.remove(nvars) (:574)
-                        w.state[ST_IUSED] = s.used;
-                        if (kaux != last) {
-                            const int v = w.colvar[last];
-                            w.colvar[kaux] = v;
-                            w.colslot[kaux] = w.colslot[last];
-                            w.varpos[v] = kaux;
-                        }
-                    }
-                    ctl.ncols = m;
-                    grid.sync();
-                }
                 status = single_run_loop(grid, br, sm, w, a, ctl);  // :599
             }
         } else {
@@ -616,19 +737,20 @@ simplex_single_kernel(const SingleWS w, const SingleArgs a)
         }
     }
 
-    // ---- results (:473-491, 603, 622) ----
+    // ---- results (:473-491, 603, 622); every rank holds the full answer ----
     for (int j = gtid; j < m; j += gsize) {
         double v = 0.0;
         if (status == 0) {
             const int pos = w.varpos[n + j];
             if (pos < 0) v = w.bcol[~pos];
         }
-        a.x[j] = v;
+        w.x[j] = v;
     }
     if (gtid == 0) {
-        a.status[0] = status;
-        a.npivots[0] = ctl.npiv;
-        a.objective[0] = (status == 0) ? w.bcol[n] : 0.0;
+        w.status[0] = status;
+        w.npivots[0] = ctl.npiv;
+        w.objective[0] = (status == 0) ? w.bcol[n] : 0.0;
+        if (w.nranks > 1) w.xbuf[kXbEpoch] = ctl.epoch;
     }
 }
 
@@ -640,14 +762,22 @@ simplex_single_kernel(const SingleWS w, const SingleArgs a)
 using namespace lpb;
 
 static inline size_t up256(size_t v) { return (v + 255) / 256 * 256; }
+static const int kMaxSingleGrid = 148 * 8;  // per-rank scratch is sized for any grid up to this
 
-// Carves the workspace; returns the bytes needed.  base == nullptr just measures.
-static size_t carve_single(SingleWS *w, int n, int m, unsigned char *base, int grid)
+static int cols_per_rank(int m, int nranks) { return (((m + 1) + nranks - 1) / nranks + 15) / 16 * 16; }
+
+// Carves one rank's part of the workspace; returns the bytes needed.  base == nullptr just measures.
+static size_t carve_single(SingleWS *w, int n, int m, int rank, int nranks, unsigned char *base)
 {
     const int nv = n + m + 1;
     w->n = n;
     w->m = m;
-    w->S = (m + 1 + 15) / 16 * 16;
+    w->S = cols_per_rank(m, nranks);
+    w->rank = rank;
+    w->nranks = nranks;
+    w->c_lo = rank * w->S;
+    int wl = (m + 1) - w->c_lo;
+    w->wloc = wl < 0 ? 0 : (wl > w->S ? w->S : wl);
     w->size_i0 = pyset_initial_size(m);
     w->size_i1 = pyset_initial_size(m + 1);
     w->size_d0 = pyset_initial_size(n);
@@ -676,15 +806,15 @@ static size_t carve_single(SingleWS *w, int n, int m, unsigned char *base, int g
     CARVE(tab_d, int, w->cap_d)
     CARVE(tab_s, int, w->cap_s)
     CARVE(list, int, n + 1)
-    CARVE(part_key, unsigned long long, 2 * grid)
-    CARVE(part_var, int, 2 * grid)
-    CARVE(part_crash, int, 2 * grid)
+    CARVE(part_key, unsigned long long, 2 * kMaxSingleGrid)
+    CARVE(part_var, int, 2 * kMaxSingleGrid)
+    CARVE(part_crash, int, 2 * kMaxSingleGrid)
     CARVE(state, int, ST_COUNT)
 #undef CARVE
     return o;
 }
 
-static const int kMaxSingleGrid = 148 * 8;  // workspace is sized for any grid up to this
+static const size_t kWsHeader = 4096;  // device copy of the rank's SingleWS lives at the workspace head
 
 static int check_single_args(int n, int m, double tol, int max_pivots, int log_cap)
 {
@@ -699,11 +829,57 @@ static int check_single_args(int n, int m, double tol, int max_pivots, int log_c
     return 0;
 }
 
+// CTAs per rank for a cooperative launch that holds `groups` ranks on the current device.
+static int pick_ctas_per_rank(const DeviceInfo &di, int n, int wcols, int groups, int *out)
+{
+    int coop = 0;
+    LPB_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, di.device));
+    if (!coop) {
+        set_error("lpb200_simplex_single: device does not support cooperative launch");
+        return LPB200_E_CUDA;
+    }
+    int per_sm = 0;
+    LPB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_single_kernel, kSgThreads, 0));
+    if (per_sm < 1) {
+        set_error("lpb200_simplex_single: kernel does not fit on an SM");
+        return LPB200_E_CUDA;
+    }
+    if (per_sm > 2) per_sm = 2;
+    int cpr = di.sm_count * per_sm / groups;
+    if (cpr > kMaxSingleGrid) cpr = kMaxSingleGrid;
+    // small problems: no point in more CTAs than there is work
+    const long long work = ((long long)(n + 1) * (wcols + 1) + kSgThreads * 8 - 1) / (kSgThreads * 8);
+    if (cpr > work) cpr = (int)(work < 1 ? 1 : work);
+    if (cpr < 1) {
+        set_error("lpb200_simplex_single: too many emulated ranks for one cooperative launch");
+        return LPB200_E_TOO_LARGE;
+    }
+    *out = cpr;
+    return 0;
+}
+
+static int launch_single(const SingleWS *d_ranks, int groups, int cpr, const double *b, const double *c,
+                         double tol, int max_pivots, int log_cap, double timeout_s, cudaStream_t stream)
+{
+    SingleArgs a;
+    a.b = b;
+    a.c = c;
+    a.tol = tol;
+    a.max_pivots = max_pivots;
+    a.log_cap = log_cap;
+    a.cpr = cpr;
+    a.timeout_ns = (unsigned long long)(timeout_s * 1e9);
+    void *params[] = {(void *)&d_ranks, (void *)&a};
+    LPB_CUDA(cudaLaunchCooperativeKernel((const void *)simplex_single_kernel, dim3(groups * cpr),
+                                         dim3(kSgThreads), params, 0, stream));
+    return 0;
+}
+
 extern "C" int64_t lpb200_simplex_single_workspace_bytes(int n, int m)
 {
     if (n < 1 || m < 1) return 0;
     SingleWS w;
-    return (int64_t)carve_single(&w, n, m, nullptr, kMaxSingleGrid);
+    return (int64_t)(kWsHeader + carve_single(&w, n, m, 0, 1, nullptr));
 }
 
 extern "C" int lpb200_simplex_single_device(int n, int m, const double *A, const double *b, const double *c,
@@ -718,26 +894,9 @@ extern "C" int lpb200_simplex_single_device(int n, int m, const double *A, const
     DeviceInfo di;
     rc = get_device_info(&di);
     if (rc) return rc;
-    int coop = 0;
-    LPB_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, di.device));
-    if (!coop) {
-        set_error("lpb200_simplex_single: device does not support cooperative launch");
-        return LPB200_E_CUDA;
-    }
-    int per_sm = 0;
-    LPB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_single_kernel, kSgThreads, 0));
-    if (per_sm < 1) {
-        set_error("lpb200_simplex_single: kernel does not fit on an SM");
-        return LPB200_E_CUDA;
-    }
-    if (per_sm > 4) per_sm = 4;
-    int grid = di.sm_count * per_sm;
-    if (grid > kMaxSingleGrid) grid = kMaxSingleGrid;
-    // small problems: no point in more CTAs than there is work
-    const long long work = ((long long)(n + 1) * (m + 1) + kSgThreads * 8 - 1) / (kSgThreads * 8);
-    if (grid > work) grid = (int)(work < 1 ? 1 : work);
     SingleWS w;
-    const size_t need = carve_single(&w, n, m, static_cast<unsigned char *>(workspace), kMaxSingleGrid);
+    unsigned char *base = static_cast<unsigned char *>(workspace);
+    const size_t need = kWsHeader + carve_single(&w, n, m, 0, 1, base ? base + kWsHeader : nullptr);
     if (workspace == nullptr || (size_t)workspace_bytes < need) {
         set_error("lpb200_simplex_single: workspace too small (need " + std::to_string(need) + " bytes)");
         return LPB200_E_INVALID;
@@ -746,22 +905,22 @@ extern "C" int lpb200_simplex_single_device(int n, int m, const double *A, const
         set_error("lpb200_simplex_single: workspace must be 256-byte aligned");
         return LPB200_E_INVALID;
     }
-    SingleArgs a;
-    a.A = A;
-    a.b = b;
-    a.c = c;
-    a.tol = tol;
-    a.max_pivots = max_pivots;
-    a.status = status;
-    a.x = x;
-    a.objective = objective;
-    a.npivots = npivots;
-    a.pivot_log = pivot_log;
-    a.log_cap = log_cap;
-    void *params[] = {(void *)&w, (void *)&a};
-    LPB_CUDA(cudaLaunchCooperativeKernel((const void *)simplex_single_kernel, dim3(grid), dim3(kSgThreads),
-                                         params, 0, stream));
-    return 0;
+    int cpr = 0;
+    rc = pick_ctas_per_rank(di, n, m, 1, &cpr);
+    if (rc) return rc;
+    w.A = A;
+    w.lda = m;
+    w.xbuf = nullptr;
+    w.peers = nullptr;
+    w.status = status;
+    w.x = x;
+    w.objective = objective;
+    w.npivots = npivots;
+    w.pivot_log = pivot_log;
+    // pageable source: the runtime stages it before returning, so the stack copy is safe
+    LPB_CUDA(cudaMemcpyAsync(workspace, &w, sizeof(w), cudaMemcpyHostToDevice, stream));
+    return launch_single(static_cast<const SingleWS *>(workspace), 1, cpr, b, c, tol, max_pivots, log_cap, 0.0,
+                         stream);
 }
 
 extern "C" int lpb200_simplex_single(int n, int m, const double *A, const double *b, const double *c,
@@ -824,10 +983,247 @@ extern "C" int lpb200_simplex_single(int n, int m, const double *A, const double
             stats[1] = (double)*npivots;
         }
     }
-#undef LPB_TRY
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
     cudaFree(dA); cudaFree(db); cudaFree(dc); cudaFree(dx); cudaFree(dobj);
     cudaFree(dst); cudaFree(dnp); cudaFree(dlog); cudaFree(ws);
+    return rc;
+}
+
+// ======================================================================================
+// Column-sharded mode: communicator (peer-mapped exchange buffers) and entry points
+// ======================================================================================
+struct lpb200_comm {
+    int rank, nranks, device, max_n;
+    size_t xbuf_bytes;
+    unsigned long long *xbuf;               // cudaMalloc'ed on this rank's device
+    void *peer_host[kMaxRanks];             // peer-mapped pointers (own entry == xbuf)
+    unsigned long long **peers_dev;         // device table handed to the kernel
+    bool connected;
+};
+
+extern "C" int64_t lpb200_comm_handle_bytes(void) { return (int64_t)sizeof(cudaIpcMemHandle_t); }
+
+extern "C" int lpb200_comm_create(int rank, int nranks, int max_n, lpb200_comm_t **out, void *handle_out)
+{
+    if (out == nullptr || handle_out == nullptr || nranks < 1 || nranks > kMaxRanks || rank < 0 ||
+        rank >= nranks || max_n < 1) {
+        set_error("lpb200_comm_create: need 0 <= rank < nranks <= 32, max_n >= 1, non-null outputs");
+        return LPB200_E_INVALID;
+    }
+    DeviceInfo di;
+    int rc = get_device_info(&di);
+    if (rc) return rc;
+    lpb200_comm *c = new lpb200_comm();
+    c->rank = rank;
+    c->nranks = nranks;
+    c->device = di.device;
+    c->max_n = max_n;
+    c->xbuf_bytes = xbuf_bytes_for(max_n, nranks);
+    c->xbuf = nullptr;
+    c->peers_dev = nullptr;
+    c->connected = false;
+    for (int g = 0; g < kMaxRanks; ++g) c->peer_host[g] = nullptr;
+    cudaError_t e;
+    if ((e = cudaMalloc((void **)&c->xbuf, c->xbuf_bytes)) != cudaSuccess ||
+        (e = cudaMemset(c->xbuf, 0, c->xbuf_bytes)) != cudaSuccess ||
+        (e = cudaDeviceSynchronize()) != cudaSuccess ||
+        (e = cudaIpcGetMemHandle(static_cast<cudaIpcMemHandle_t *>(handle_out), c->xbuf)) != cudaSuccess) {
+        if (c->xbuf) cudaFree(c->xbuf);
+        delete c;
+        return cuda_fail(e, "lpb200_comm_create");
+    }
+    *out = c;
+    return 0;
+}
+
+extern "C" int lpb200_comm_connect(lpb200_comm_t *c, const void *all_handles)
+{
+    if (c == nullptr || all_handles == nullptr) {
+        set_error("lpb200_comm_connect: null argument");
+        return LPB200_E_INVALID;
+    }
+    if (c->connected) return 0;
+    const cudaIpcMemHandle_t *h = static_cast<const cudaIpcMemHandle_t *>(all_handles);
+    for (int g = 0; g < c->nranks; ++g) {
+        if (g == c->rank) {
+            c->peer_host[g] = c->xbuf;
+            continue;
+        }
+        cudaError_t e = cudaIpcOpenMemHandle(&c->peer_host[g], h[g], cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaIpcOpenMemHandle (is peer access available between the GPUs?)");
+    }
+    LPB_CUDA(cudaMalloc((void **)&c->peers_dev, sizeof(void *) * kMaxRanks));
+    LPB_CUDA(cudaMemcpy(c->peers_dev, c->peer_host, sizeof(void *) * kMaxRanks, cudaMemcpyHostToDevice));
+    c->connected = true;
+    return 0;
+}
+
+extern "C" int lpb200_comm_destroy(lpb200_comm_t *c)
+{
+    if (c == nullptr) return 0;
+    for (int g = 0; g < c->nranks; ++g)
+        if (g != c->rank && c->peer_host[g]) cudaIpcCloseMemHandle(c->peer_host[g]);
+    if (c->peers_dev) cudaFree(c->peers_dev);
+    if (c->xbuf) cudaFree(c->xbuf);
+    delete c;
+    return 0;
+}
+
+extern "C" int lpb200_simplex_sharded_columns(int m, int nranks, int rank, int *c_lo, int *c_count)
+{
+    if (m < 1 || nranks < 1 || nranks > kMaxRanks || rank < 0 || rank >= nranks) {
+        set_error("lpb200_simplex_sharded_columns: bad arguments");
+        return LPB200_E_INVALID;
+    }
+    const int S = cols_per_rank(m, nranks);
+    int lo = rank * S;
+    int cnt = m - lo;  // columns of A (position m is the auxiliary column, not part of A)
+    if (cnt < 0) cnt = 0;
+    if (cnt > S) cnt = S;
+    if (lo > m) lo = m;
+    if (c_lo) *c_lo = lo;
+    if (c_count) *c_count = cnt;
+    return 0;
+}
+
+extern "C" int64_t lpb200_simplex_sharded_workspace_bytes(int n, int m, int nranks)
+{
+    if (n < 1 || m < 1 || nranks < 1 || nranks > kMaxRanks) return 0;
+    SingleWS w;
+    return (int64_t)(kWsHeader + carve_single(&w, n, m, 0, nranks, nullptr));
+}
+
+extern "C" int lpb200_simplex_sharded_device(lpb200_comm_t *comm, int n, int m, const double *A_cols,
+                                             int64_t lda, const double *b, const double *c, double tol,
+                                             int max_pivots, int32_t *status, double *x, double *objective,
+                                             int32_t *npivots, int32_t *pivot_log, int log_cap,
+                                             void *workspace, int64_t workspace_bytes, double timeout_s,
+                                             void *stream_v)
+{
+    int rc = check_single_args(n, m, tol, max_pivots, log_cap);
+    if (rc) return rc;
+    if (comm == nullptr || !comm->connected) {
+        set_error("lpb200_simplex_sharded: communicator is not connected");
+        return LPB200_E_INVALID;
+    }
+    if (n > comm->max_n) {
+        set_error("lpb200_simplex_sharded: n exceeds the communicator's max_n");
+        return LPB200_E_TOO_LARGE;
+    }
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    DeviceInfo di;
+    rc = get_device_info(&di);
+    if (rc) return rc;
+    SingleWS w;
+    unsigned char *base = static_cast<unsigned char *>(workspace);
+    const size_t need = kWsHeader + carve_single(&w, n, m, comm->rank, comm->nranks, base ? base + kWsHeader : nullptr);
+    if (workspace == nullptr || (size_t)workspace_bytes < need ||
+        (reinterpret_cast<uintptr_t>(workspace) & 255) != 0) {
+        set_error("lpb200_simplex_sharded: workspace null, misaligned or too small (need " +
+                  std::to_string(need) + " bytes)");
+        return LPB200_E_INVALID;
+    }
+    // every rank must use the same grid shape? No: ranks only meet through the exchange buffers.
+    int cpr = 0;
+    rc = pick_ctas_per_rank(di, n, w.S, 1, &cpr);
+    if (rc) return rc;
+    w.A = A_cols;
+    w.lda = lda;
+    w.xbuf = comm->xbuf;
+    w.peers = comm->peers_dev;
+    w.status = status;
+    w.x = x;
+    w.objective = objective;
+    w.npivots = npivots;
+    w.pivot_log = pivot_log;
+    LPB_CUDA(cudaMemcpyAsync(workspace, &w, sizeof(w), cudaMemcpyHostToDevice, stream));
+    return launch_single(static_cast<const SingleWS *>(workspace), 1, cpr, b, c, tol, max_pivots, log_cap,
+                         timeout_s > 0.0 ? timeout_s : 20.0, stream);
+}
+
+// All `nranks` ranks of the sharded protocol as CTA groups of ONE cooperative launch on the
+// current device (host pointers in, per-rank results out).  Exercises the exact kernel,
+// packet format and exchange schedule of the multi-GPU path; used by the parity tests.
+extern "C" int lpb200_simplex_sharded_emulated(int nranks, int n, int m, const double *A, const double *b,
+                                               const double *c, double tol, int max_pivots, int32_t *status,
+                                               double *x, double *objective, int32_t *npivots,
+                                               int32_t *pivot_log, int log_cap)
+{
+    int rc = check_single_args(n, m, tol, max_pivots, log_cap);
+    if (rc) return rc;
+    if (nranks < 1 || nranks > kMaxRanks) {
+        set_error("lpb200_simplex_sharded_emulated: need 1 <= nranks <= 32");
+        return LPB200_E_INVALID;
+    }
+    DeviceInfo di;
+    rc = get_device_info(&di);
+    if (rc) return rc;
+    const int G = nranks;
+    SingleWS probe;
+    const size_t per_rank = up256(carve_single(&probe, n, m, 0, G, nullptr));
+    const size_t xb = xbuf_bytes_for(n, G);
+    const size_t nA = (size_t)n * m * 8, nb = (size_t)n * 8, nc = (size_t)m * 8;
+    const size_t nlog = pivot_log ? (size_t)log_cap * 2 * 4 : 0;
+    const size_t out_per_rank = up256(nc) + up256(8) + up256(4) + up256(4) + up256(nlog);
+    int cpr = 0;
+    rc = pick_ctas_per_rank(di, n, probe.S, G, &cpr);
+    if (rc) return rc;
+    unsigned char *ws = nullptr, *outs = nullptr, *xbufs = nullptr;
+    double *dA = nullptr, *db = nullptr, *dc = nullptr;
+    SingleWS *d_ranks = nullptr;
+    unsigned long long **d_peers = nullptr;
+    rc = 0;
+    LPB_TRY(cudaMalloc((void **)&ws, per_rank * G));
+    LPB_TRY(cudaMalloc((void **)&outs, out_per_rank * G));
+    LPB_TRY(cudaMalloc((void **)&xbufs, xb * G));
+    LPB_TRY(cudaMalloc((void **)&dA, nA));
+    LPB_TRY(cudaMalloc((void **)&db, nb));
+    LPB_TRY(cudaMalloc((void **)&dc, nc));
+    LPB_TRY(cudaMalloc((void **)&d_ranks, sizeof(SingleWS) * G));
+    LPB_TRY(cudaMalloc((void **)&d_peers, sizeof(void *) * kMaxRanks));
+    if (rc == 0) {
+        LPB_TRY(cudaMemset(xbufs, 0, xb * G));
+        LPB_TRY(cudaMemset(outs, 0xff, out_per_rank * G));
+        LPB_TRY(cudaMemcpy(dA, A, nA, cudaMemcpyHostToDevice));
+        LPB_TRY(cudaMemcpy(db, b, nb, cudaMemcpyHostToDevice));
+        LPB_TRY(cudaMemcpy(dc, c, nc, cudaMemcpyHostToDevice));
+    }
+    std::vector<SingleWS> hw((size_t)G);
+    std::vector<unsigned char *> ho((size_t)G);
+    if (rc == 0) {
+        void *peers[kMaxRanks] = {};
+        for (int g = 0; g < G; ++g) peers[g] = xbufs + xb * g;
+        LPB_TRY(cudaMemcpy(d_peers, peers, sizeof(peers), cudaMemcpyHostToDevice));
+        for (int g = 0; g < G; ++g) {
+            SingleWS &w = hw[g];
+            carve_single(&w, n, m, g, G, ws + per_rank * g);
+            w.A = dA + (w.c_lo < m ? w.c_lo : 0);
+            w.lda = m;
+            w.xbuf = reinterpret_cast<unsigned long long *>(xbufs + xb * g);
+            w.peers = d_peers;
+            unsigned char *o = outs + out_per_rank * g;
+            ho[g] = o;
+            w.x = reinterpret_cast<double *>(o);               o += up256(nc);
+            w.objective = reinterpret_cast<double *>(o);       o += up256(8);
+            w.status = reinterpret_cast<int32_t *>(o);         o += up256(4);
+            w.npivots = reinterpret_cast<int32_t *>(o);        o += up256(4);
+            w.pivot_log = nlog ? reinterpret_cast<int32_t *>(o) : nullptr;
+        }
+        LPB_TRY(cudaMemcpy(d_ranks, hw.data(), sizeof(SingleWS) * G, cudaMemcpyHostToDevice));
+    }
+    if (rc == 0) rc = launch_single(d_ranks, G, cpr, db, dc, tol, max_pivots, log_cap, 20.0, nullptr);
+    if (rc == 0) LPB_TRY(cudaDeviceSynchronize());
+    for (int g = 0; g < G && rc == 0; ++g) {
+        const SingleWS &w = hw[g];
+        LPB_TRY(cudaMemcpy(x + (size_t)g * m, w.x, nc, cudaMemcpyDeviceToHost));
+        LPB_TRY(cudaMemcpy(objective + g, w.objective, 8, cudaMemcpyDeviceToHost));
+        LPB_TRY(cudaMemcpy(status + g, w.status, 4, cudaMemcpyDeviceToHost));
+        LPB_TRY(cudaMemcpy(npivots + g, w.npivots, 4, cudaMemcpyDeviceToHost));
+        if (nlog) LPB_TRY(cudaMemcpy(pivot_log + (size_t)g * log_cap * 2, w.pivot_log, nlog, cudaMemcpyDeviceToHost));
+    }
+#undef LPB_TRY
+    cudaFree(ws); cudaFree(outs); cudaFree(xbufs); cudaFree(dA); cudaFree(db); cudaFree(dc);
+    cudaFree(d_ranks); cudaFree(d_peers);
     return rc;
 }
