@@ -11,6 +11,7 @@ from __future__ import annotations
 import numpy as np
 
 CHUNK = 256
+SINGLE_COLS = 1024  # column-block granularity of single_lp
 
 
 def _chunks(start: int, count: int):
@@ -110,15 +111,28 @@ def gauss_jordan_batch(count: int, n: int = 512, seed: int = 1, swap_frac: float
     return a, b
 
 
-def single_lp(n: int = 16383, m: int = 32767, seed: int = 5, dist: str = "D1"):
+def single_lp(n: int = 16383, m: int = 32767, seed: int = 5, dist: str = "D1", col_lo: int = 0,
+              col_cnt: int | None = None):
     """Config 5 -- one large dense LP (condensed tableau (n+1) x (m+1)); D1-style data so the
-    origin is feasible.  Generated row-block by row-block to bound peak host memory."""
-    rng = np.random.default_rng([seed, 55, n, m])
-    A = np.empty((n, m), dtype=np.float64)
+    origin is feasible.  A is generated in blocks of ``SINGLE_COLS`` columns, each from its own
+    seeded stream, so a rank of the column-sharded solver can generate just ITS columns
+    (``col_lo``, ``col_cnt``) and still hold exactly the data of the full matrix.  Returns
+    (A[n, col_cnt], b[n], c[m]); b and c are always complete."""
+    if col_cnt is None:
+        col_cnt = m - col_lo
     lo_a = 0 if dist == "D1" else -100
-    step = 1024
-    for r in range(0, n, step):
-        A[r:r + step] = rng.integers(lo_a, 101, size=(min(step, n - r), m))
+    A = np.empty((n, col_cnt), dtype=np.float64)
+    blk0 = col_lo // SINGLE_COLS
+    blk1 = (col_lo + col_cnt + SINGLE_COLS - 1) // SINGLE_COLS if col_cnt > 0 else blk0
+    for blk in range(blk0, blk1):
+        k0 = blk * SINGLE_COLS
+        w = min(SINGLE_COLS, m - k0)
+        rng = np.random.default_rng([seed, 55, n, m, blk])
+        part = rng.integers(lo_a, 101, size=(n, w), dtype=np.int16)
+        a = max(col_lo, k0)
+        z = min(col_lo + col_cnt, k0 + w)
+        A[:, a - col_lo:z - col_lo] = part[:, a - k0:z - k0]
+    rng = np.random.default_rng([seed, 56, n, m])
     b = rng.integers(1, 10**6 + 1, size=n).astype(np.float64)
     if dist == "D1":
         c = rng.integers(1, 101, size=m).astype(np.float64)

@@ -71,3 +71,20 @@ def test_one_rank_emulated_equals_single_mode(oracle_lib):
     r2 = lp.solve_batch(A, b, c, mode="single", max_pivots=300, log_cap=300)
     assert int(r1.status[0]) == int(r2.status[0]) and r1.pivots(0) == r2.pivots(0)
     assert np.array_equal(r1.x[0].view(np.int64), r2.x[0].view(np.int64))
+
+
+def test_two_processes_two_gpus_vs_oracle():
+    """The real multi-process path (CUDA IPC peer mapping, one rank per GPU) when the box has
+    at least two GPUs; on a one-GPU box the emulated-rank tests above cover the protocol."""
+    import os
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.join(root, "tools", "gpu", "sharded_parity.py")]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert '"all_ranks_match_oracle": true' in out.stdout

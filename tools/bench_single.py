@@ -1,17 +1,23 @@
 #!/usr/bin/env python3
-"""Config 5: one large dense LP on the grid-wide kernel -- ms/pivot and achieved HBM GB/s.
+"""Config 5: one large dense LP on the grid-wide kernel -- ms/pivot and achieved HBM GB/s,
+on one GPU or column-sharded over N GPUs (one process per GPU).
 
     python tools/bench_single.py [--n 16383] [--m 32767] [--pivots 200] [--reps 2]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P tools/bench_single.py --pivots 200
 
 Algorithmic bytes per pivot = 16*(n+1)*(m+1) (every condensed-tableau element read and
-written once).  Inputs are generated on the host, copied once; the timed region
-(CUDA events on the launching stream) is the whole cooperative kernel including tableau set-up,
-so the set-up cost (one 2x4.3 GB pass) is also measured separately with pivots=0.
+written once), whatever the number of GPUs.  Inputs are generated on the host
+(each rank only its own columns), copied once; the timed region (CUDA events on the launching
+stream, max over ranks, barrier on both sides) is the whole persistent kernel including
+tableau set-up, so the set-up cost is measured separately with max_pivots = 0 and subtracted.
+`pivot_crc` is a checksum of the (entering, leaving) sequence: it must not depend on N.
 """
 import argparse
 import json
 import os
 import sys
+import zlib
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -20,6 +26,7 @@ import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 from linear_programming_b200 import _lib, workloads  # noqa: E402
+from linear_programming_b200.sharded import ShardedComm, column_shard  # noqa: E402
 
 
 def main():
@@ -29,32 +36,74 @@ def main():
     ap.add_argument("--pivots", type=int, default=200)
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--dist", default="D1")
+    ap.add_argument("--gpus", type=int, default=None, help="informational; the world size comes from torchrun")
     args = ap.parse_args()
     n, m = args.n, args.m
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
     L = _lib.lib()
-    dev = torch.device("cuda", 0)
-    A, b, c = workloads.single_lp(n, m, seed=5, dist=args.dist)
+    comm = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+        comm = ShardedComm(max_n=n)
+        lo, cnt = column_shard(m, world, rank)
+    else:
+        lo, cnt = 0, m
+    A, b, c = workloads.single_lp(n, m, seed=5, dist=args.dist, col_lo=lo, col_cnt=cnt)
     dA = torch.from_numpy(A).to(dev)
     db = torch.from_numpy(b).to(dev)
     dc = torch.from_numpy(c).to(dev)
     del A
-    wsb = int(L.lpb200_simplex_single_workspace_bytes(n, m))
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    cap = max(args.pivots, 1)
+    if world == 1:
+        wsb = int(L.lpb200_simplex_single_workspace_bytes(n, m))
+    else:
+        wsb = int(L.lpb200_simplex_sharded_workspace_bytes(n, m, world))
     ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
     st = torch.zeros(1, dtype=torch.int32, device=dev)
     npv = torch.zeros(1, dtype=torch.int32, device=dev)
     x = torch.zeros(m, dtype=torch.float64, device=dev)
     obj = torch.zeros(1, dtype=torch.float64, device=dev)
-    stream = torch.cuda.current_stream(dev).cuda_stream
+    log = torch.full((cap, 2), -1, dtype=torch.int32, device=dev)
 
-    def run(cap):
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local_rank])
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def run(maxpiv):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        torch.cuda.synchronize()
         e0.record()
-        _lib.check(L.lpb200_simplex_single_device(n, m, dA.data_ptr(), db.data_ptr(), dc.data_ptr(), 1e-9, cap,
-                                                  st.data_ptr(), x.data_ptr(), obj.data_ptr(), npv.data_ptr(),
-                                                  None, 0, ws.data_ptr(), wsb, stream))
+        if world == 1:
+            _lib.check(L.lpb200_simplex_single_device(n, m, dA.data_ptr(), db.data_ptr(), dc.data_ptr(), 1e-9,
+                                                      maxpiv, st.data_ptr(), x.data_ptr(), obj.data_ptr(),
+                                                      npv.data_ptr(), log.data_ptr(), cap, ws.data_ptr(), wsb,
+                                                      stream))
+        else:
+            _lib.check(L.lpb200_simplex_sharded_device(comm._comm, n, m, dA.data_ptr() if cnt else None,
+                                                       dA.stride(0) if cnt else 0, db.data_ptr(), dc.data_ptr(),
+                                                       1e-9, maxpiv, st.data_ptr(), x.data_ptr(), obj.data_ptr(),
+                                                       npv.data_ptr(), log.data_ptr(), cap, ws.data_ptr(), wsb,
+                                                       30.0, stream))
         e1.record()
         torch.cuda.synchronize()
-        return e0.elapsed_time(e1), int(npv.item()), int(st.item())
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        barrier()
+        return ms, int(npv.item()), int(st.item())
 
     run(2)  # warm-up
     setup_ms = min(run(0)[0] for _ in range(args.reps))
@@ -64,19 +113,29 @@ def main():
         if best is None or ms < best[0]:
             best = (ms, piv, status)
     ms, piv, status = best
+    crc = zlib.crc32(log[:piv].cpu().numpy().tobytes())
     per_pivot_ms = (ms - setup_ms) / max(piv, 1)
     alg = 16.0 * (n + 1) * (m + 1)
-    peak = 6549.4
+    peak = 6456.5
     try:
         peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
     except Exception:
         pass
     gbs = alg / (per_pivot_ms * 1e-3) / 1e9
-    print(json.dumps({
-        "workload": "configs[4]: single dense LP, condensed tableau %d x %d (n=%d, m=%d), %s" % (n + 1, m + 1, n, m, args.dist),
-        "pivots": piv, "status": status, "total_ms": ms, "setup_ms": setup_ms, "ms_per_pivot": per_pivot_ms,
-        "algorithmic_bytes_per_pivot": alg, "achieved_GBps": gbs, "peak_GBps": peak, "frac": gbs / peak,
-        "pivots_per_s": 1e3 / per_pivot_ms}))
+    if rank == 0:
+        print(json.dumps({
+            "workload": "configs[4]: single dense LP, condensed tableau %d x %d (n=%d, m=%d), %s, "
+                        "column-sharded over %d GPU(s)" % (n + 1, m + 1, n, m, args.dist, world),
+            "n_gpus": world, "pivots": piv, "status": status, "pivot_crc": crc, "total_ms": ms,
+            "setup_ms": setup_ms, "ms_per_pivot": per_pivot_ms, "algorithmic_bytes_per_pivot": alg,
+            "achieved_GBps": gbs, "peak_GBps_per_gpu": peak, "frac_of_aggregate_peak": gbs / (peak * world),
+            "pivots_per_s": 1e3 / per_pivot_ms,
+            "exchange": "none" if world == 1 else
+                        "in-kernel LL packets over peer-mapped buffers: key all-to-all + pivot-column broadcast"}),
+            flush=True)
+    if world > 1:
+        comm.close()
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
