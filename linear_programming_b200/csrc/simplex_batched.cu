@@ -2,29 +2,37 @@
 //
 // Replaces, per problem, the reference's Simplex.solve() (week-2/diet/simplex.py:586-630)
 // with its SlackForm pivot loop (:442-491).  B200 design:
-//   * the condensed tableau ((n+1) x (1+m+1) fp64; 82 KB for 100x100) lives in SHARED MEMORY
+//   * the condensed tableau ((n+2) x (1+m+1) fp64; 83 KB for 100x100) lives in SHARED MEMORY
 //     for the whole solve; HBM is touched once to read (A,b,c) and once to write (status,x);
 //   * persistent CTAs (2 per SM at 100x100) pull problems off a device-side work queue, so
 //     LPs with 10 pivots and LPs with 1600 pivots balance across the 148 SMs;
-//   * 8 sweep warps + 1 bookkeeping warp: the rank-1 update is a double2-vectorised,
-//     bank-conflict-free sweep (each lane keeps its two pivot-row values in registers and
-//     walks down the rows); the CPython-set emulation that defines the entering order runs
-//     on the 9th warp, overlapped with the sweep;
-//   * entering-column select = redux.sync min over (slot<<16|position); leaving-row select =
-//     warp-shuffle lexicographic argmin over (ratio, variable id); one block barrier each;
+//   * 8 sweep warps + 1 bookkeeping warp, TWO block barriers per pivot:
+//       step 1  one thread per row reads its pivot-column entry, stages it in fc[], zeroes it
+//               in place (the column now belongs to the leaving variable), and runs the
+//               min-ratio test: warp-shuffle lexicographic argmin over (ratio, variable id);
+//       step 2  the rank-1 sweep: every lane derives its double2 of the scaled pivot row from
+//               the (read-only) old pivot row, keeps it in registers and walks down a block of
+//               rows, 4 at a time, with 128-bit shared-memory loads/stores (conflict-free).
+//               The new pivot row is written into a SPARE physical row and the old one becomes
+//               the next spare (rows are slots: rowvar[] maps slot -> variable), so no thread
+//               ever reads a location another thread writes within a step.  The lanes that
+//               update the objective row also pick the NEXT entering column (redux.sync min
+//               over set-slot priority), and the 9th warp runs the CPython-set emulation that
+//               defines that priority, both overlapped with the sweep;
 //   * no FMA anywhere on the data path (__dmul_rn/__dadd_rn), IEEE division.
 //
 // Kernel <-> reference map (file:line in /root/reference/week-2/diet/simplex.py)
 //   select_entering()   objective_has_positive_coefficients :387-388, pick_entering_idx :390-392
-//   select_leaving()    pick_leaving_idx :394-436, list_wrapper.min_index :157-161
-//   pivot() phase B     make_pivot_constraint :325-345
-//   pivot() phase C     SlackForm.pivot :348-385 -> Constraint.substitute/sexp :185-214
+//   stage_and_ratio()   pick_leaving_idx :394-436, list_wrapper.min_index :157-161
+//   sweep()             make_pivot_constraint :325-345,
+//                       SlackForm.pivot :348-385 -> Constraint.substitute/sexp :185-214
 //   bookkeeping()       set_replace :369-381 (CPython set order)
 //   solve_one()         Simplex.solve :586-630, find_basic_feasible :514-584,
 //                       make_auxiliary_form :632-660, SlackForm.solve epilogue :473-491
 #include <cuda_runtime.h>
 #include <math_constants.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "lp_common.cuh"
 #include "lp_host.h"
@@ -34,6 +42,7 @@ namespace lpb {
 constexpr int kSweepWarps = 8;
 constexpr int kSweepThreads = kSweepWarps * 32;  // 256
 constexpr int kThreads = kSweepThreads + 32;     // + bookkeeping warp
+constexpr int kRowChunk = 4;                     // rows per unrolled sweep step
 
 typedef int16_t tab_t;
 
@@ -41,7 +50,8 @@ typedef int16_t tab_t;
 struct BatchShape {
     int n, m;
     int S;        // tableau row stride in doubles (even): 1 constant + m + 1 auxiliary, rounded up
-    int cx;       // lanes across column pairs in the sweep (power of two <= 256)
+    int cx;       // lanes across column pairs in the sweep (power of two <= 64)
+    int rpg;      // physical rows per row group (multiple of kRowChunk); groups = 256 / cx
     int size_i0;  // initial table size of `independent` (phase 2: m keys / phase 1: m+1 keys)
     int size_i1;
     int size_d0;  // initial table size of `dependent` (n keys)
@@ -62,9 +72,11 @@ static BatchShape make_batch_shape(int n, int m)
     s.m = m;
     s.S = align_up(m + 2, 2);
     int cx = 1;
-    while (cx < s.S / 2 && cx < kSweepThreads) cx <<= 1;
-    if (cx > 64) cx = 64;  // keep >= 4 row groups; wider tableaus loop over column pairs
+    while (cx < s.S / 2 && cx < 64) cx <<= 1;  // keep >= 4 row groups; wider tableaus loop over column pairs
     s.cx = cx;
+    const int nphys = n + 2;  // n basic rows + objective row + one spare slot
+    const int groups = kSweepThreads / cx;
+    s.rpg = align_up((nphys + groups - 1) / groups, kRowChunk);
     s.size_i0 = pyset_initial_size(m);
     s.size_i1 = pyset_initial_size(m + 1);
     s.size_d0 = pyset_initial_size(n);
@@ -73,20 +85,20 @@ static BatchShape make_batch_shape(int n, int m)
     s.cap_s = s.cap_i > s.cap_d ? s.cap_i : s.cap_d;
     const int nv = n + m + 1;
     int o = 0;
-    s.off_T = o;          o += (n + 1) * s.S * 8;
+    s.off_T = o;          o += nphys * s.S * 8;
     s.off_nr = o;         o += s.S * 8;
-    s.off_fc = o;         o += align_up(n + 1, 2) * 8;
+    s.off_fc = o;         o += (groups * s.rpg + kRowChunk) * 8;
     s.off_redkey = o;     o += kSweepWarps * 8;
-    s.off_rowvar = o;     o += align_up(n, 4) * 4;
-    s.off_nonecol = o;    o += align_up(n, 4) * 4;
-    s.off_untouched = o;  o += align_up(n, 4) * 4;
-    s.off_rowslot = o;    o += align_up(n, 4) * 4;
+    s.off_rowvar = o;     o += align_up(nphys, 4) * 4;
+    s.off_nonecol = o;    o += align_up(nphys, 4) * 4;
+    s.off_untouched = o;  o += align_up(nphys, 4) * 4;
+    s.off_rowslot = o;    o += align_up(nphys, 4) * 4;
     s.off_colvar = o;     o += align_up(m + 1, 4) * 4;
     s.off_colslot = o;    o += align_up(m + 1, 4) * 4;
     s.off_varpos = o;     o += align_up(nv, 4) * 4;
     s.off_basis0 = o;     o += align_up((nv + 31) / 32, 4) * 4;
     s.off_redvar = o;     o += kSweepWarps * 4;
-    s.off_redu32 = o;     o += kSweepWarps * 4;
+    s.off_redu32 = o;     o += (kSweepWarps + 4) * 4;
     s.off_misc = o;       o += 16 * 4;
     s.off_tab_i = o;      o += align_up(s.cap_i * (int)sizeof(tab_t), 16);
     s.off_tab_d = o;      o += align_up(s.cap_d * (int)sizeof(tab_t), 16);
@@ -109,7 +121,7 @@ struct BatchArgs {
 };
 
 // misc[] slots
-enum { MI_LP = 0, MI_ISIZE, MI_IFILL, MI_IUSED, MI_DSIZE, MI_DFILL, MI_DUSED, MI_NLIST };
+enum { MI_LP = 0, MI_ISIZE, MI_IFILL, MI_IUSED, MI_DSIZE, MI_DFILL, MI_DUSED, MI_NLIST, MI_RESELECT };
 
 // Per-CTA view of the carved shared memory (pointers live in registers).
 struct Ctx {
@@ -121,13 +133,15 @@ struct Ctx {
     unsigned *redu32;
     int *misc;
     tab_t *tab_i, *tab_d, *tab_s;
-    int n, m, S, cx;
+    int n, m, S, cx, rpg;
+    int spare;  // physical row slot currently unused (uniform across the CTA)
     double tol;
     bool track_dep;  // the `dependent` set order only matters when phase 1 runs (:538)
 };
 
 // ---- entering column: first positive objective coefficient in set-slot order (:390-392) ----
-// Returns the column position, or -1 when no coefficient is > tol (loop ends, :447).
+// Stand-alone pass (loop entry, and after a set-table rebuild).  Returns the column position,
+// or -1 when no coefficient is > tol (loop ends, :447).
 __device__ __forceinline__ int select_entering(const Ctx &c, int ncols)
 {
     const int tid = threadIdx.x;
@@ -143,32 +157,53 @@ __device__ __forceinline__ int select_entering(const Ctx &c, int ncols)
     unsigned best = c.redu32[0];
 #pragma unroll
     for (int w = 1; w < kSweepWarps; ++w) best = min(best, c.redu32[w]);
+    __syncthreads();  // redu32 is rewritten by the next sweep
     return best == 0xffffffffu ? -1 : (int)(best & 0xffffu);
 }
 
-// ---- leaving row: min-ratio test with the reference's degenerate skip (:394-436) ----
-// Returns the leaving VARIABLE id, -1 if unbounded, -2 if the reference would raise TypeError.
-__device__ __forceinline__ int select_leaving(const Ctx &c, int p, int e)
+// ---- step 1: stage the pivot column, min-ratio test with the reference's degenerate skip (:394-436) ----
+// One thread per physical row: fc[i] = snapped T[i][1+p]; the entry is zeroed in place (the
+// column now belongs to the leaving variable, whose coefficient starts from None, :187 opt).
+// Returns (leaving VARIABLE id << 16 | its physical row), -1 if unbounded, -2 if the reference
+// would raise TypeError.  The row travels with the id through the reduction because varpos[]
+// is rewritten by the bookkeeping lane as soon as the barrier below is passed.
+__device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool forced)
 {
     const int tid = threadIdx.x;
+    const int nphys = c.n + 2;
     int crash = 0;
     if (tid < kSweepThreads) {
         unsigned long long key = kKeyNone;
         int var = 0x7fffffff;
         const bool e_in_basis0 = (c.basis0[e >> 5] >> (e & 31)) & 1u;
-        for (int i = tid; i < c.n; i += kSweepThreads) {
-            const int nc = c.nonecol[i];
-            crash |= (nc == kNoneInitial && e < c.n) || (nc == e) || (c.untouched[i] && e_in_basis0);
-            const double *Ti = c.T + (size_t)i * c.S;
-            const double coeff = -Ti[1 + p];
-            if (coeff > c.tol) {
-                const double ratio = snap(__ddiv_rn(Ti[0], coeff), c.tol);
-                if (ratio != 0.0) {  // zero ratios count as +inf in min_index (:161)
-                    const unsigned long long k = order_key(ratio);
-                    const int v = c.rowvar[i];
-                    if (k < key || (k == key && v < var)) {
-                        key = k;
-                        var = v;
+        const bool e_is_slack = e < c.n;
+        for (int i = tid; i < nphys; i += kSweepThreads) {
+            const int v = c.rowvar[i];
+            double f = 0.0;
+            if (v >= 0 || i == c.n) {
+                double *q = c.T + (size_t)i * c.S + 1 + p;
+                f = *q;
+                *q = 0.0;
+                if (fabs(f) <= c.tol) f = 0.0;  // substitute() returns the row unchanged (:203-205)
+            }
+            c.fc[i] = f;
+            if (v >= 0) {
+                const int nc = c.nonecol[i];
+                crash |= (nc == kNoneInitial && e_is_slack) || (nc == e) || (c.untouched[i] && e_in_basis0);
+                if (f != 0.0) {  // row is rewritten by this pivot: its only None is column e
+                    c.nonecol[i] = e;
+                    c.untouched[i] = 0;
+                }
+                const double coeff = -f;
+                if (coeff > c.tol) {
+                    const double ratio = snap(__ddiv_rn(c.T[(size_t)i * c.S], coeff), c.tol);
+                    if (ratio != 0.0) {  // zero ratios count as +inf in min_index (:161)
+                        const unsigned long long k = order_key(ratio);
+                        const int vi = (v << 16) | i;  // ties -> lowest variable id (rows are unique per id)
+                        if (k < key || (k == key && vi < var)) {
+                            key = k;
+                            var = vi;
+                        }
                     }
                 }
             }
@@ -179,6 +214,7 @@ __device__ __forceinline__ int select_leaving(const Ctx &c, int p, int e)
             c.redvar[tid >> 5] = var;
         }
     }
+    if (forced) crash = 0;
     if (__syncthreads_or(crash)) return -2;
     unsigned long long key = c.redkey[0];
     int var = c.redvar[0];
@@ -195,19 +231,25 @@ __device__ __forceinline__ int select_leaving(const Ctx &c, int p, int e)
 }
 
 // ---- set bookkeeping by one lane of the 9th warp, overlapped with the sweep (:369-381) ----
-__device__ __forceinline__ void bookkeeping(const Ctx &c, int p, int r, int e, int l)
+// e sat at column position p; l owned physical row `src`; the new row of e is written to `dest`.
+// Also publishes the entering-key candidate of column p (now variable l) for the next pivot.
+__device__ __forceinline__ void bookkeeping(const Ctx &c, int p, int src, int dest, int e, int l, double pinv)
 {
-    // row r now belongs to e, column position p to l
     const int eslot = c.colslot[p];
-    c.rowvar[r] = e;
+    const int lrowslot = c.rowslot[src];
+    c.rowvar[src] = -1;  // becomes the spare slot
+    c.rowvar[dest] = e;
+    c.nonecol[dest] = e;
+    c.untouched[dest] = 0;
     c.colvar[p] = l;
-    c.varpos[e] = ~r;
+    c.varpos[e] = ~dest;
     c.varpos[l] = p;
     bool rebuild;
+    int reselect = 0;
     if (c.track_dep) {  // dependent.remove(l); dependent.add(e)
         PySet d = {c.misc[MI_DSIZE], c.misc[MI_DFILL], c.misc[MI_DUSED]};
-        pyset_remove_slot(c.tab_d, d, c.rowslot[r]);
-        c.rowslot[r] = pyset_add(c.tab_d, d, e, &rebuild);
+        pyset_remove_slot(c.tab_d, d, lrowslot);
+        c.rowslot[dest] = pyset_add(c.tab_d, d, e, &rebuild);
         if (rebuild) {
             pyset_rebuild(c.tab_d, c.tab_s, d);
             for (int s = 0; s < d.size; ++s) {
@@ -223,93 +265,151 @@ __device__ __forceinline__ void bookkeeping(const Ctx &c, int p, int r, int e, i
         PySet s = {c.misc[MI_ISIZE], c.misc[MI_IFILL], c.misc[MI_IUSED]};
         pyset_remove_slot(c.tab_i, s, eslot);
         c.colslot[p] = pyset_add(c.tab_i, s, l, &rebuild);
-        if (rebuild) {
+        if (rebuild) {  // every slot moved: the keys computed by the sweep lanes are stale
             pyset_rebuild(c.tab_i, c.tab_s, s);
             for (int t = 0; t < s.size; ++t) {
                 const int v = (int)c.tab_i[t];
                 if (v >= 0) c.colslot[c.varpos[v]] = t;
             }
+            reselect = 1;
         }
         c.misc[MI_ISIZE] = s.size;
         c.misc[MI_IFILL] = s.fill;
         c.misc[MI_IUSED] = s.used;
     }
+    // new objective coefficient of column p: snap(None + c_e * (1/pivot)) (:314-318, :343-344)
+    unsigned key = 0xffffffffu;
+    const double fobj = c.fc[c.n];
+    if (fobj != 0.0) {
+        const double v = axpy_snap(0.0, fobj, snap(-pinv, c.tol), c.tol);
+        if (v > c.tol) key = ((unsigned)c.colslot[p] << 16) | (unsigned)p;
+    }
+    c.redu32[kSweepWarps] = key;
+    c.misc[MI_RESELECT] = reselect;
 }
 
-// ---- SlackForm.pivot(e, l) (:348-385): e sits at column position p, l owns row r ----
-__device__ __forceinline__ void pivot(const Ctx &c, int ncols, int p, int r, int e, int l,
-                                      int32_t *log, int log_cap, int npiv)
+// ---- step 2: SlackForm.pivot(e, l) (:348-385) as one sweep; returns the next entering position ----
+// e sits at column position p, l owns physical row src, c.spare receives the new row of e.
+__device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, int l, int32_t *log,
+                                      int log_cap, int npiv)
 {
     const int tid = threadIdx.x;
-    const int n = c.n, S = c.S, W = 1 + ncols;
+    const int n = c.n, S = c.S;
+    const int nphys = n + 2;
+    const int dest = c.spare;
     const double tol = c.tol;
-    // Phase B: scaled pivot row (make_pivot_constraint :325-345) and the pivot column factors.
+    const double pinv = pivot_inverse(c.fc[src], tol);  // fc[src] is the pivot element (> tol in size)
     if (tid < kSweepThreads) {
-        const double *Tr = c.T + (size_t)r * S;
-        const double pinv = pivot_inverse(Tr[1 + p], tol);
-        for (int k = tid; k < W; k += kSweepThreads)
-            c.nr[k] = (k == 1 + p) ? snap(-pinv, tol)  // column p now belongs to l: 1/pivot (:343-344)
-                                   : snap(__dmul_rn(pinv, Tr[k]), tol);
-        for (int i = tid; i <= n; i += kSweepThreads) {
-            double *q = c.T + (size_t)i * S + 1 + p;
-            double f = *q;
-            if (fabs(f) <= tol) f = 0.0;  // substitute() returns the row unchanged (:203-205)
-            c.fc[i] = f;
-            if (i != r) *q = 0.0;         // A[i][l] starts from None (:187 opt)
-            if (i < n && (f != 0.0 || i == r)) {  // row is rewritten: its only None is column e
-                c.nonecol[i] = e;
-                c.untouched[i] = 0;
-            }
-        }
-    }
-    __syncthreads();
-    // Phase C: rank-1 sweep on 8 warps, set bookkeeping on the 9th.
-    if (tid < kSweepThreads) {
-        const int cx = tid & (c.cx - 1);
+        const int cxi = tid & (c.cx - 1);
         const int ry = tid / c.cx;
-        const int RY = kSweepThreads / c.cx;
+        const int row0 = ry * c.rpg, row1 = row0 + c.rpg;
         const int npairs = S >> 1;
-        for (int cp = cx; cp < npairs; cp += c.cx) {
-            const double2 r2 = reinterpret_cast<const double2 *>(c.nr)[cp];
-            for (int i = ry; i <= n; i += RY) {
-                double2 *q = reinterpret_cast<double2 *>(c.T + (size_t)i * S) + cp;
-                if (i == r) {  // store(entering_idx, entering_constraint) (:352)
-                    *q = r2;
-                    continue;
+        const double2 *Tsrc = reinterpret_cast<const double2 *>(c.T + (size_t)src * S);
+        unsigned mykey = 0xffffffffu;
+        for (int cp = cxi; cp < npairs; cp += c.cx) {
+            // this lane's two entries of the scaled pivot row (make_pivot_constraint :325-345)
+            double2 r2 = Tsrc[cp];
+            r2.x = (2 * cp == 1 + p) ? snap(-pinv, tol) : snap(__dmul_rn(pinv, r2.x), tol);
+            r2.y = (2 * cp + 1 == 1 + p) ? snap(-pinv, tol) : snap(__dmul_rn(pinv, r2.y), tol);
+            double2 *col = reinterpret_cast<double2 *>(c.T) + cp;
+            const int rs = S >> 1;  // row stride in double2
+            for (int i = row0; i < row1; i += kRowChunk) {
+                const double2 fa = *reinterpret_cast<const double2 *>(c.fc + i);
+                const double2 fb = *reinterpret_cast<const double2 *>(c.fc + i + 2);
+                const bool special = ((unsigned)(src - i) < (unsigned)kRowChunk) ||
+                                     ((unsigned)(dest - i) < (unsigned)kRowChunk) ||
+                                     ((unsigned)(n - i) < (unsigned)kRowChunk);
+                if (!special && fa.x != 0.0 && fa.y != 0.0 && fb.x != 0.0 && fb.y != 0.0) {
+                    double2 *q = col + (size_t)i * rs;
+                    double2 a0 = q[0], a1 = q[rs], a2 = q[2 * rs], a3 = q[3 * rs];
+                    a0.x = __dadd_rn(a0.x, __dmul_rn(fa.x, r2.x));
+                    a0.y = __dadd_rn(a0.y, __dmul_rn(fa.x, r2.y));
+                    a1.x = __dadd_rn(a1.x, __dmul_rn(fa.y, r2.x));
+                    a1.y = __dadd_rn(a1.y, __dmul_rn(fa.y, r2.y));
+                    a2.x = __dadd_rn(a2.x, __dmul_rn(fb.x, r2.x));
+                    a2.y = __dadd_rn(a2.y, __dmul_rn(fb.x, r2.y));
+                    a3.x = __dadd_rn(a3.x, __dmul_rn(fb.y, r2.x));
+                    a3.y = __dadd_rn(a3.y, __dmul_rn(fb.y, r2.y));
+                    a0.x = snap(a0.x, tol); a0.y = snap(a0.y, tol);
+                    a1.x = snap(a1.x, tol); a1.y = snap(a1.y, tol);
+                    a2.x = snap(a2.x, tol); a2.y = snap(a2.y, tol);
+                    a3.x = snap(a3.x, tol); a3.y = snap(a3.y, tol);
+                    q[0] = a0;
+                    q[rs] = a1;
+                    q[2 * rs] = a2;
+                    q[3 * rs] = a3;
+                } else {
+                    const double f4[kRowChunk] = {fa.x, fa.y, fb.x, fb.y};
+#pragma unroll
+                    for (int j = 0; j < kRowChunk; ++j) {
+                        const int ii = i + j;
+                        if (ii >= nphys || ii == src) continue;
+                        double2 *q = col + (size_t)ii * rs;
+                        if (ii == dest) {  // store(entering_idx, entering_constraint) (:352)
+                            *q = r2;
+                            continue;
+                        }
+                        double2 a = *q;
+                        const double f = f4[j];
+                        if (f != 0.0) {
+                            a.x = axpy_snap(a.x, f, r2.x, tol);
+                            a.y = axpy_snap(a.y, f, r2.y, tol);
+                            *q = a;
+                        }
+                        if (ii == n) {  // objective row: candidates for the NEXT entering column (:390-392)
+                            const int k0 = 2 * cp - 1;  // column position of a.x (position -1 is the constant)
+                            if (k0 >= 0 && k0 < ncols && k0 != p && a.x > tol)
+                                mykey = min(mykey, ((unsigned)c.colslot[k0] << 16) | (unsigned)k0);
+                            if (k0 + 1 < ncols && k0 + 1 != p && a.y > tol)
+                                mykey = min(mykey, ((unsigned)c.colslot[k0 + 1] << 16) | (unsigned)(k0 + 1));
+                        }
+                    }
                 }
-                const double f = c.fc[i];
-                if (f == 0.0) continue;
-                double2 a = *q;
-                a.x = axpy_snap(a.x, f, r2.x, tol);
-                a.y = axpy_snap(a.y, f, r2.y, tol);
-                *q = a;
             }
         }
+        mykey = __reduce_min_sync(0xffffffffu, mykey);
+        if ((tid & 31) == 0) c.redu32[tid >> 5] = mykey;
     } else if (tid == kSweepThreads) {
         if (log != nullptr && npiv < log_cap) {
             log[2 * npiv] = e;
             log[2 * npiv + 1] = l;
         }
-        bookkeeping(c, p, r, e, l);
+        bookkeeping(c, p, src, dest, e, l, pinv);
     }
+    c.spare = src;
     __syncthreads();
 }
 
+// Next entering position after a sweep: the partial keys it left in redu32[] (or a fresh pass
+// when the set table was rebuilt and every slot moved).
+__device__ __forceinline__ int next_entering(const Ctx &c, int ncols)
+{
+    if (c.misc[MI_RESELECT]) {
+        __syncthreads();  // everyone has read the flag before the bookkeeping lane can rewrite it
+        return select_entering(c, ncols);
+    }
+    unsigned best = c.redu32[0];
+#pragma unroll
+    for (int w = 1; w <= kSweepWarps; ++w) best = min(best, c.redu32[w]);
+    return best == 0xffffffffu ? -1 : (int)(best & 0xffffu);
+}
+
 // SlackForm.solve loop (:442-466).  Returns 0 when optimal, else a terminal status code.
-__device__ __forceinline__ int run_loop(const Ctx &c, int ncols, int &npiv, int max_pivots, int32_t *log,
+__device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pivots, int32_t *log,
                                         int log_cap)
 {
+    int p = select_entering(c, ncols);
     for (;;) {
-        const int p = select_entering(c, ncols);
         if (p < 0) return 0;
         const int e = c.colvar[p];
-        const int l = select_leaving(c, p, e);
-        if (l == -2) return LPB200_STATUS_REF_TYPE_ERROR;
-        if (l < 0) return LPB200_STATUS_INFINITY;
+        const int lr = stage_and_ratio(c, p, e, false);
+        if (lr == -2) return LPB200_STATUS_REF_TYPE_ERROR;
+        if (lr < 0) return LPB200_STATUS_INFINITY;
         if (npiv >= max_pivots) return LPB200_STATUS_ITERATION_LIMIT;
-        const int r = ~c.varpos[l];
-        pivot(c, ncols, p, r, e, l, log, log_cap, npiv);
+        const int l = lr >> 16, src = lr & 0xffff;
+        sweep(c, ncols, p, src, e, l, log, log_cap, npiv);
         ++npiv;
+        p = next_entering(c, ncols);
     }
 }
 
@@ -320,6 +420,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
     const int tid = threadIdx.x;
     const int n = sh.n, m = sh.m, S = sh.S;
     const int nv = n + m + 1;
+    const int nphys = n + 2;
     Ctx c;
     c.T = reinterpret_cast<double *>(smem + sh.off_T);
     c.nr = reinterpret_cast<double *>(smem + sh.off_nr);
@@ -343,8 +444,10 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
     c.m = m;
     c.S = S;
     c.cx = sh.cx;
+    c.rpg = sh.rpg;
     c.tol = a.tol;
     const double tol = a.tol;
+    const int nfc = (kSweepThreads / sh.cx) * sh.rpg + kRowChunk;
 
     for (;;) {
         // ---- next problem off the device work queue ----
@@ -397,6 +500,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
         int ncols = phase1 ? m + 1 : m;
         if (!phase1 && !(min_c > tol)) status = LPB200_STATUS_REF_ATTRIBUTE_ERROR;  // :626
         c.track_dep = phase1;
+        c.spare = n + 1;
 
         if (status == 0) {
             // ---- SlackForm.__init__ (:230-302) (+ the x_aux column of :632-660 in phase 1) ----
@@ -418,14 +522,16 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                     if (k >= 1 && k <= m) v = phase1 ? 0.0 : gc[k - 1];
                     if (k == 1 + m && phase1) v = -1.0;  // objective -x_aux (:644-645)
                     obj[k] = v;
+                    obj[S + k] = 0.0;  // the spare slot
                     c.nr[k] = 0.0;
                 }
-                for (int i = tid; i < n; i += kSweepThreads) {
-                    c.rowvar[i] = i;
-                    c.varpos[i] = ~i;
+                for (int i = tid; i < nfc; i += kSweepThreads) c.fc[i] = 0.0;
+                for (int i = tid; i < nphys; i += kSweepThreads) {
+                    c.rowvar[i] = (i < n) ? i : -1;
                     c.nonecol[i] = kNoneInitial;
                     c.untouched[i] = 0;
                     c.rowslot[i] = i & (sh.size_d0 - 1);
+                    if (i < n) c.varpos[i] = ~i;
                 }
                 const int isize = phase1 ? sh.size_i1 : sh.size_i0;
                 for (int k = tid; k <= m; k += kSweepThreads) {
@@ -453,6 +559,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                     c.misc[MI_DSIZE] = sh.size_d0;
                     c.misc[MI_DFILL] = n;
                     c.misc[MI_DUSED] = n;
+                    c.misc[MI_RESELECT] = 0;
                 }
             }
             __syncthreads();
@@ -463,7 +570,8 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                 if (npiv >= a.max_pivots) {
                     status = LPB200_STATUS_ITERATION_LIMIT;
                 } else {
-                    pivot(c, ncols, m, idx0, aux, idx0, log, a.log_cap, npiv);
+                    (void)stage_and_ratio(c, m, aux, true);
+                    sweep(c, ncols, m, idx0, aux, idx0, log, a.log_cap, npiv);
                     ++npiv;
                     status = run_loop(c, ncols, npiv, a.max_pivots, log, a.log_cap);  // :526
                 }
@@ -525,13 +633,14 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                             }
                             c.basis0[w] = bits;
                         }
-                        for (int i = tid; i < n; i += kSweepThreads) c.untouched[i] = 1;
-                        for (int i = tid; i <= n; i += kSweepThreads) {
+                        for (int i = tid; i < nphys; i += kSweepThreads) c.untouched[i] = 1;
+                        for (int i = tid; i < nphys; i += kSweepThreads) {
                             double *Ti = c.T + (size_t)i * S;
                             if (kaux != last) Ti[1 + kaux] = Ti[1 + last];
                             Ti[1 + last] = 0.0;
                         }
                         for (int k = tid; k < S; k += kSweepThreads) c.nr[k] = 0.0;
+                        for (int i = tid; i < nfc; i += kSweepThreads) c.fc[i] = 0.0;  // list[] lived here
                     } else if (tid == kSweepThreads) {
                         PySet s = {c.misc[MI_ISIZE], c.misc[MI_IFILL], c.misc[MI_IUSED]};
                         pyset_remove_slot(c.tab_i, s, c.colslot[kaux]);  // independent.remove(nvars) (:574)
@@ -616,11 +725,14 @@ extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A,
                   " > " + std::to_string(di.max_smem_optin) + " bytes); use lpb200_simplex_single");
         return LPB200_E_TOO_LARGE;
     }
-    LPB_CUDA(cudaFuncSetAttribute(simplex_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sh.bytes));
+    int dyn_smem = sh.bytes;
+    if (const char *g = getenv("LPB_DEBUG_PAD")) dyn_smem += atoi(g);
+    LPB_CUDA(cudaFuncSetAttribute(simplex_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
     int per_sm = 0;
-    LPB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_batched_kernel, kThreads, sh.bytes));
+    LPB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_batched_kernel, kThreads, dyn_smem));
     if (per_sm < 1) per_sm = 1;
     long long grid = (long long)di.sm_count * per_sm;
+    if (const char *g = getenv("LPB_DEBUG_GRID")) grid = atoi(g);
     if (grid > B) grid = B;
     unsigned int *counter = nullptr;
     LPB_CUDA(cudaMallocAsync((void **)&counter, sizeof(unsigned int), stream));
@@ -639,7 +751,7 @@ extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A,
     a.pivot_log = pivot_log;
     a.log_cap = log_cap;
     a.work_counter = counter;
-    simplex_batched_kernel<<<(unsigned)grid, kThreads, sh.bytes, stream>>>(sh, a);
+    simplex_batched_kernel<<<(unsigned)grid, kThreads, dyn_smem, stream>>>(sh, a);
     LPB_CUDA(cudaGetLastError());
     LPB_CUDA(cudaFreeAsync(counter, stream));
     return 0;

@@ -162,3 +162,20 @@ def test_tolerance_is_a_runtime_argument(oracle_lib):
         st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, tol=tol, max_pivots=5000)
         assert np.array_equal(res.status, st) and np.array_equal(res.npivots, npiv)
         assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
+
+
+def test_full_gpu_two_ctas_per_sm_vs_oracle(oracle_lib):
+    """Enough 100x100 LPs to keep two CTAs resident on every SM with several problems per CTA
+    (persistent work queue): warp skew between co-resident CTAs once exposed a read of varpos[]
+    racing the bookkeeping lane, which never shows with one CTA per SM."""
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    for dist, count, cap in (("D2", 900, 400), ("D1", 1500, 50000)):
+        A, b, c = workloads.simplex_batch(dist, count, 100, 100, seed=2, start=4096)
+        for _ in range(2):
+            res = lp.solve_batch(A, b, c, max_pivots=cap)
+            st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=cap)
+            assert np.array_equal(res.status, st)
+            assert np.array_equal(res.npivots, npiv)
+            assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
+            assert np.array_equal(res.objective.view(np.int64), obj.view(np.int64))
