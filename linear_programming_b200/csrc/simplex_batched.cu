@@ -32,6 +32,7 @@
 #include <cuda_runtime.h>
 #include <math_constants.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "lp_common.cuh"
@@ -50,14 +51,16 @@ typedef int16_t tab_t;
 struct BatchShape {
     int n, m;
     int S;        // tableau row stride in doubles (even): 1 constant + m + 1 auxiliary, rounded up
-    int cx;       // lanes across column pairs in the sweep (power of two <= 64)
-    int rpg;      // physical rows per row group (multiple of kRowChunk); groups = 256 / cx
+    int cx;       // lanes across column pairs in the sweep (<= 64)
+    int groups;   // row groups = 256 / cx
+    int rpg;      // physical rows per row group (multiple of kRowChunk)
+    int nfc;      // doubles in fc[] (groups * rpg + one chunk of zero padding)
     int size_i0;  // initial table size of `independent` (phase 2: m keys / phase 1: m+1 keys)
     int size_i1;
     int size_d0;  // initial table size of `dependent` (n keys)
     int cap_i, cap_d, cap_s;
     // byte offsets from the (16-byte aligned) dynamic smem base
-    int off_T, off_nr, off_fc, off_redkey, off_rowvar, off_nonecol, off_untouched, off_rowslot,
+    int off_T, off_nr, off_fc, off_pinvs, off_redkey, off_rowvar, off_nonecol, off_untouched, off_rowslot,
         off_colvar, off_colslot, off_varpos, off_basis0, off_redvar, off_redu32, off_misc,
         off_tab_i, off_tab_d, off_tab_s;
     int bytes;
@@ -71,12 +74,13 @@ static BatchShape make_batch_shape(int n, int m)
     s.n = n;
     s.m = m;
     s.S = align_up(m + 2, 2);
-    int cx = 1;
-    while (cx < s.S / 2 && cx < 64) cx <<= 1;  // keep >= 4 row groups; wider tableaus loop over column pairs
-    s.cx = cx;
+    const int npairs = s.S / 2;
+    const int passes = (npairs + 63) / 64;          // column pairs per lane (wide tableaus loop)
+    s.cx = (npairs + passes - 1) / passes;           // lanes across column pairs: 51 at m = 100
     const int nphys = n + 2;  // n basic rows + objective row + one spare slot
-    const int groups = kSweepThreads / cx;
-    s.rpg = align_up((nphys + groups - 1) / groups, kRowChunk);
+    s.groups = kSweepThreads / s.cx;                 // row groups: 5 at m = 100 (255 of 256 threads busy)
+    s.rpg = align_up((nphys + s.groups - 1) / s.groups, kRowChunk);
+    s.nfc = s.groups * s.rpg + kRowChunk;
     s.size_i0 = pyset_initial_size(m);
     s.size_i1 = pyset_initial_size(m + 1);
     s.size_d0 = pyset_initial_size(n);
@@ -87,8 +91,9 @@ static BatchShape make_batch_shape(int n, int m)
     int o = 0;
     s.off_T = o;          o += nphys * s.S * 8;
     s.off_nr = o;         o += s.S * 8;
-    s.off_fc = o;         o += (groups * s.rpg + kRowChunk) * 8;
-    s.off_redkey = o;     o += kSweepWarps * 8;
+    s.off_fc = o;         o += s.nfc * 8;
+    s.off_pinvs = o;      o += s.nfc * 8;
+    s.off_redkey = o;     o += kSweepWarps * 16;
     s.off_rowvar = o;     o += align_up(nphys, 4) * 4;
     s.off_nonecol = o;    o += align_up(nphys, 4) * 4;
     s.off_untouched = o;  o += align_up(nphys, 4) * 4;
@@ -118,6 +123,7 @@ struct BatchArgs {
     int32_t *pivot_log;
     int log_cap;
     unsigned int *work_counter;
+    unsigned long long *timing;  // debug (LPB_DEBUG_TIMING): per-phase cycle counters, else null
 };
 
 // misc[] slots
@@ -125,7 +131,7 @@ enum { MI_LP = 0, MI_ISIZE, MI_IFILL, MI_IUSED, MI_DSIZE, MI_DFILL, MI_DUSED, MI
 
 // Per-CTA view of the carved shared memory (pointers live in registers).
 struct Ctx {
-    double *T, *nr, *fc;
+    double *T, *nr, *fc, *pinvs;
     unsigned long long *redkey;
     int *rowvar, *nonecol, *untouched, *rowslot, *colvar, *colslot, *varpos;
     unsigned *basis0;
@@ -134,9 +140,11 @@ struct Ctx {
     int *misc;
     tab_t *tab_i, *tab_d, *tab_s;
     int n, m, S, cx, rpg;
+    int cxi, row0, row1;  // this thread's column-pair lane and physical row block [row0, row1)
     int spare;  // physical row slot currently unused (uniform across the CTA)
     double tol;
     bool track_dep;  // the `dependent` set order only matters when phase 1 runs (:538)
+    unsigned long long *timing;
 };
 
 // ---- entering column: first positive objective coefficient in set-slot order (:390-392) ----
@@ -164,20 +172,31 @@ __device__ __forceinline__ int select_entering(const Ctx &c, int ncols)
 // ---- step 1: stage the pivot column, min-ratio test with the reference's degenerate skip (:394-436) ----
 // One thread per physical row: fc[i] = snapped T[i][1+p]; the entry is zeroed in place (the
 // column now belongs to the leaving variable, whose coefficient starts from None, :187 opt).
+// Every candidate row also leaves its scaled reciprocal pivot in pinvs[i] (:328-330), so the
+// sweep starts without a division on its critical path.
 // Returns (leaving VARIABLE id << 16 | its physical row), -1 if unbounded, -2 if the reference
 // would raise TypeError.  The row travels with the id through the reduction because varpos[]
 // is rewritten by the bookkeeping lane as soon as the barrier below is passed.
+struct __align__(16) RatioPartial {
+    unsigned long long key;
+    int id;
+    int pad;
+};
+
 __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool forced)
 {
     const int tid = threadIdx.x;
     const int nphys = c.n + 2;
     int crash = 0;
-    if (tid < kSweepThreads) {
+    // only the warps that own rows take part (4 of 8 at n = 100)
+    const int nsw = min(kSweepWarps, (nphys + 31) >> 5);
+    RatioPartial *part = reinterpret_cast<RatioPartial *>(c.redkey);
+    if (tid < nsw * 32) {
         unsigned long long key = kKeyNone;
         int var = 0x7fffffff;
         const bool e_in_basis0 = (c.basis0[e >> 5] >> (e & 31)) & 1u;
         const bool e_is_slack = e < c.n;
-        for (int i = tid; i < nphys; i += kSweepThreads) {
+        for (int i = tid; i < nphys; i += nsw * 32) {
             const int v = c.rowvar[i];
             double f = 0.0;
             if (v >= 0 || i == c.n) {
@@ -195,7 +214,9 @@ __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool 
                     c.untouched[i] = 0;
                 }
                 const double coeff = -f;
-                if (coeff > c.tol) {
+                const bool cand = coeff > c.tol;
+                if (cand || (forced && f != 0.0)) c.pinvs[i] = pivot_inverse(f, c.tol);
+                if (cand) {
                     const double ratio = snap(__ddiv_rn(c.T[(size_t)i * c.S], coeff), c.tol);
                     if (ratio != 0.0) {  // zero ratios count as +inf in min_index (:161)
                         const unsigned long long k = order_key(ratio);
@@ -208,26 +229,27 @@ __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool 
                 }
             }
         }
-        warp_argmin(key, var);
+        // lexicographic (key, id) minimum across the warp with three redux.sync steps
+        const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+        const unsigned mh = __reduce_min_sync(0xffffffffu, hi);
+        const unsigned ml = __reduce_min_sync(0xffffffffu, hi == mh ? lo : 0xffffffffu);
+        const unsigned mi = __reduce_min_sync(0xffffffffu, (hi == mh && lo == ml) ? (unsigned)var : 0x7fffffffu);
         if ((tid & 31) == 0) {
-            c.redkey[tid >> 5] = key;
-            c.redvar[tid >> 5] = var;
+            RatioPartial r;
+            r.key = ((unsigned long long)mh << 32) | ml;
+            r.id = (int)mi;
+            r.pad = 0;
+            part[tid >> 5] = r;
         }
     }
     if (forced) crash = 0;
     if (__syncthreads_or(crash)) return -2;
-    unsigned long long key = c.redkey[0];
-    int var = c.redvar[0];
-#pragma unroll
-    for (int w = 1; w < kSweepWarps; ++w) {
-        const unsigned long long k = c.redkey[w];
-        const int v = c.redvar[w];
-        if (k < key || (k == key && v < var)) {
-            key = k;
-            var = v;
-        }
+    RatioPartial best = part[0];
+    for (int w = 1; w < nsw; ++w) {
+        const RatioPartial r = part[w];
+        if (r.key < best.key || (r.key == best.key && r.id < best.id)) best = r;
     }
-    return key == kKeyNone ? -1 : var;
+    return best.key == kKeyNone ? -1 : best.id;
 }
 
 // ---- set bookkeeping by one lane of the 9th warp, overlapped with the sweep (:369-381) ----
@@ -285,83 +307,116 @@ __device__ __forceinline__ void bookkeeping(const Ctx &c, int p, int src, int de
         if (v > c.tol) key = ((unsigned)c.colslot[p] << 16) | (unsigned)p;
     }
     c.redu32[kSweepWarps] = key;
-    c.misc[MI_RESELECT] = reselect;
+    c.redu32[kSweepWarps + 1] = (unsigned)reselect;
 }
 
-// ---- step 2: SlackForm.pivot(e, l) (:348-385) as one sweep; returns the next entering position ----
+// ---- shared-memory helpers for the sweep (32-bit shared addresses, explicit instruction forms) ----
+__device__ __forceinline__ void lds_f64x2(uint32_t addr, double &x, double &y)
+{
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void sts_f64x2(uint32_t addr, double x, double y)
+{
+    asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(addr), "d"(x), "d"(y) : "memory");
+}
+// snap-to-zero as a predicated 8-byte store of +0.0 over a value already stored (|v| <= tol is
+// rare; this replaces a compare + two selects + register shuffling per element by compare + store)
+__device__ __forceinline__ void sts_zero_if_snapped(uint32_t addr, double v, double tol)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .f64 t;\n"
+        "abs.f64 t, %1;\n"
+        "setp.le.f64 p, t, %2;\n"
+        "@p st.shared.u64 [%0], 0;\n"
+        "}\n" ::"r"(addr), "d"(v), "d"(tol) : "memory");
+}
+
+// ---- step 2: SlackForm.pivot(e, l) (:348-385) as one sweep ----
 // e sits at column position p, l owns physical row src, c.spare receives the new row of e.
 __device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, int l, int32_t *log,
-                                      int log_cap, int npiv)
+                                      int log_cap, int npiv, long long *t_own = nullptr)
 {
     const int tid = threadIdx.x;
     const int n = c.n, S = c.S;
     const int nphys = n + 2;
     const int dest = c.spare;
     const double tol = c.tol;
-    const double pinv = pivot_inverse(c.fc[src], tol);  // fc[src] is the pivot element (> tol in size)
+    const double pinv = c.pinvs[src];  // snap(-1 * (1.0 / pivot)), left by the row's own thread in step 1
     if (tid < kSweepThreads) {
-        const int cxi = tid & (c.cx - 1);
-        const int ry = tid / c.cx;
-        const int row0 = ry * c.rpg, row1 = row0 + c.rpg;
-        const int npairs = S >> 1;
-        const double2 *Tsrc = reinterpret_cast<const double2 *>(c.T + (size_t)src * S);
         unsigned mykey = 0xffffffffu;
-        for (int cp = cxi; cp < npairs; cp += c.cx) {
-            // this lane's two entries of the scaled pivot row (make_pivot_constraint :325-345)
-            double2 r2 = Tsrc[cp];
-            r2.x = (2 * cp == 1 + p) ? snap(-pinv, tol) : snap(__dmul_rn(pinv, r2.x), tol);
-            r2.y = (2 * cp + 1 == 1 + p) ? snap(-pinv, tol) : snap(__dmul_rn(pinv, r2.y), tol);
-            double2 *col = reinterpret_cast<double2 *>(c.T) + cp;
-            const int rs = S >> 1;  // row stride in double2
-            for (int i = row0; i < row1; i += kRowChunk) {
-                const double2 fa = *reinterpret_cast<const double2 *>(c.fc + i);
-                const double2 fb = *reinterpret_cast<const double2 *>(c.fc + i + 2);
-                const bool special = ((unsigned)(src - i) < (unsigned)kRowChunk) ||
-                                     ((unsigned)(dest - i) < (unsigned)kRowChunk) ||
-                                     ((unsigned)(n - i) < (unsigned)kRowChunk);
-                if (!special && fa.x != 0.0 && fa.y != 0.0 && fb.x != 0.0 && fb.y != 0.0) {
-                    double2 *q = col + (size_t)i * rs;
-                    double2 a0 = q[0], a1 = q[rs], a2 = q[2 * rs], a3 = q[3 * rs];
-                    a0.x = __dadd_rn(a0.x, __dmul_rn(fa.x, r2.x));
-                    a0.y = __dadd_rn(a0.y, __dmul_rn(fa.x, r2.y));
-                    a1.x = __dadd_rn(a1.x, __dmul_rn(fa.y, r2.x));
-                    a1.y = __dadd_rn(a1.y, __dmul_rn(fa.y, r2.y));
-                    a2.x = __dadd_rn(a2.x, __dmul_rn(fb.x, r2.x));
-                    a2.y = __dadd_rn(a2.y, __dmul_rn(fb.x, r2.y));
-                    a3.x = __dadd_rn(a3.x, __dmul_rn(fb.y, r2.x));
-                    a3.y = __dadd_rn(a3.y, __dmul_rn(fb.y, r2.y));
-                    a0.x = snap(a0.x, tol); a0.y = snap(a0.y, tol);
-                    a1.x = snap(a1.x, tol); a1.y = snap(a1.y, tol);
-                    a2.x = snap(a2.x, tol); a2.y = snap(a2.y, tol);
-                    a3.x = snap(a3.x, tol); a3.y = snap(a3.y, tol);
-                    q[0] = a0;
-                    q[rs] = a1;
-                    q[2 * rs] = a2;
-                    q[3 * rs] = a3;
-                } else {
-                    const double f4[kRowChunk] = {fa.x, fa.y, fb.x, fb.y};
+        if (c.row0 < c.row1) {
+            const int npairs = S >> 1;
+            const double2 *Tsrc = reinterpret_cast<const double2 *>(c.T + (size_t)src * S);
+            const uint32_t tbase = (uint32_t)__cvta_generic_to_shared(c.T);
+            const uint32_t rsb = (uint32_t)S * 8u;  // row stride in bytes
+            const int src4 = src & ~(kRowChunk - 1), dest4 = dest & ~(kRowChunk - 1),
+                      n4 = n & ~(kRowChunk - 1);
+            for (int cp = c.cxi; cp < npairs; cp += c.cx) {
+                // this lane's two entries of the scaled pivot row (make_pivot_constraint :325-345)
+                double2 r2 = Tsrc[cp];
+                r2.x = (2 * cp == 1 + p) ? snap(-pinv, tol) : snap(__dmul_rn(pinv, r2.x), tol);
+                r2.y = (2 * cp + 1 == 1 + p) ? snap(-pinv, tol) : snap(__dmul_rn(pinv, r2.y), tol);
+                uint32_t qa = tbase + (uint32_t)c.row0 * rsb + (uint32_t)cp * 16u;
+                const double *fcp = c.fc + c.row0;
+                for (int i = c.row0; i < c.row1; i += kRowChunk, qa += kRowChunk * rsb, fcp += kRowChunk) {
+                    const double2 fa = *reinterpret_cast<const double2 *>(fcp);
+                    const double2 fb = *reinterpret_cast<const double2 *>(fcp + 2);
+                    const bool special = (i == src4) | (i == dest4) | (i == n4);
+                    if (!special && fa.x != 0.0 && fa.y != 0.0 && fb.x != 0.0 && fb.y != 0.0) {
+                        double a0x, a0y, a1x, a1y, a2x, a2y, a3x, a3y;
+                        lds_f64x2(qa, a0x, a0y);
+                        lds_f64x2(qa + rsb, a1x, a1y);
+                        lds_f64x2(qa + 2 * rsb, a2x, a2y);
+                        lds_f64x2(qa + 3 * rsb, a3x, a3y);
+                        a0x = __dadd_rn(a0x, __dmul_rn(fa.x, r2.x));
+                        a0y = __dadd_rn(a0y, __dmul_rn(fa.x, r2.y));
+                        a1x = __dadd_rn(a1x, __dmul_rn(fa.y, r2.x));
+                        a1y = __dadd_rn(a1y, __dmul_rn(fa.y, r2.y));
+                        a2x = __dadd_rn(a2x, __dmul_rn(fb.x, r2.x));
+                        a2y = __dadd_rn(a2y, __dmul_rn(fb.x, r2.y));
+                        a3x = __dadd_rn(a3x, __dmul_rn(fb.y, r2.x));
+                        a3y = __dadd_rn(a3y, __dmul_rn(fb.y, r2.y));
+                        sts_f64x2(qa, a0x, a0y);
+                        sts_f64x2(qa + rsb, a1x, a1y);
+                        sts_f64x2(qa + 2 * rsb, a2x, a2y);
+                        sts_f64x2(qa + 3 * rsb, a3x, a3y);
+                        sts_zero_if_snapped(qa, a0x, tol);
+                        sts_zero_if_snapped(qa + 8, a0y, tol);
+                        sts_zero_if_snapped(qa + rsb, a1x, tol);
+                        sts_zero_if_snapped(qa + rsb + 8, a1y, tol);
+                        sts_zero_if_snapped(qa + 2 * rsb, a2x, tol);
+                        sts_zero_if_snapped(qa + 2 * rsb + 8, a2y, tol);
+                        sts_zero_if_snapped(qa + 3 * rsb, a3x, tol);
+                        sts_zero_if_snapped(qa + 3 * rsb + 8, a3y, tol);
+                    } else {
+                        const double f4[kRowChunk] = {fa.x, fa.y, fb.x, fb.y};
+                        double2 *col = reinterpret_cast<double2 *>(c.T) + cp;
+                        const int rs = S >> 1;  // row stride in double2
 #pragma unroll
-                    for (int j = 0; j < kRowChunk; ++j) {
-                        const int ii = i + j;
-                        if (ii >= nphys || ii == src) continue;
-                        double2 *q = col + (size_t)ii * rs;
-                        if (ii == dest) {  // store(entering_idx, entering_constraint) (:352)
-                            *q = r2;
-                            continue;
-                        }
-                        double2 a = *q;
-                        const double f = f4[j];
-                        if (f != 0.0) {
-                            a.x = axpy_snap(a.x, f, r2.x, tol);
-                            a.y = axpy_snap(a.y, f, r2.y, tol);
-                            *q = a;
-                        }
-                        if (ii == n) {  // objective row: candidates for the NEXT entering column (:390-392)
-                            const int k0 = 2 * cp - 1;  // column position of a.x (position -1 is the constant)
-                            if (k0 >= 0 && k0 < ncols && k0 != p && a.x > tol)
-                                mykey = min(mykey, ((unsigned)c.colslot[k0] << 16) | (unsigned)k0);
-                            if (k0 + 1 < ncols && k0 + 1 != p && a.y > tol)
-                                mykey = min(mykey, ((unsigned)c.colslot[k0 + 1] << 16) | (unsigned)(k0 + 1));
+                        for (int j = 0; j < kRowChunk; ++j) {
+                            const int ii = i + j;
+                            if (ii >= nphys || ii == src) continue;
+                            double2 *q = col + (size_t)ii * rs;
+                            if (ii == dest) {  // store(entering_idx, entering_constraint) (:352)
+                                *q = r2;
+                                continue;
+                            }
+                            double2 a = *q;
+                            const double f = f4[j];
+                            if (f != 0.0) {
+                                a.x = axpy_snap(a.x, f, r2.x, tol);
+                                a.y = axpy_snap(a.y, f, r2.y, tol);
+                                *q = a;
+                            }
+                            if (ii == n) {  // objective row: candidates for the NEXT entering column (:390-392)
+                                const int k0 = 2 * cp - 1;  // column position of a.x (-1 is the constant)
+                                if (k0 >= 0 && k0 < ncols && k0 != p && a.x > tol)
+                                    mykey = min(mykey, ((unsigned)c.colslot[k0] << 16) | (unsigned)k0);
+                                if (k0 + 1 < ncols && k0 + 1 != p && a.y > tol)
+                                    mykey = min(mykey, ((unsigned)c.colslot[k0 + 1] << 16) | (unsigned)(k0 + 1));
+                            }
                         }
                     }
                 }
@@ -377,20 +432,24 @@ __device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, 
         bookkeeping(c, p, src, dest, e, l, pinv);
     }
     c.spare = src;
+    if (t_own) *t_own = clock64();
     __syncthreads();
 }
 
-// Next entering position after a sweep: the partial keys it left in redu32[] (or a fresh pass
-// when the set table was rebuilt and every slot moved).
+// Next entering position after a sweep: the partial keys it left in redu32[0..8] (three
+// 128-bit loads), or a fresh pass when the set table was rebuilt and every slot moved
+// (redu32[9] != 0; redu32[10..11] stay 0xffffffff).
 __device__ __forceinline__ int next_entering(const Ctx &c, int ncols)
 {
-    if (c.misc[MI_RESELECT]) {
+    const uint4 k0 = reinterpret_cast<const uint4 *>(c.redu32)[0];
+    const uint4 k1 = reinterpret_cast<const uint4 *>(c.redu32)[1];
+    const uint4 k2 = reinterpret_cast<const uint4 *>(c.redu32)[2];
+    if (k2.y != 0u) {
         __syncthreads();  // everyone has read the flag before the bookkeeping lane can rewrite it
         return select_entering(c, ncols);
     }
-    unsigned best = c.redu32[0];
-#pragma unroll
-    for (int w = 1; w <= kSweepWarps; ++w) best = min(best, c.redu32[w]);
+    const unsigned best = min(min(min(k0.x, k0.y), min(k0.z, k0.w)),
+                              min(min(min(k1.x, k1.y), min(k1.z, k1.w)), k2.x));
     return best == 0xffffffffu ? -1 : (int)(best & 0xffffu);
 }
 
@@ -399,17 +458,29 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
                                         int log_cap)
 {
     int p = select_entering(c, ncols);
+    const bool tm = (c.timing != nullptr) && ((threadIdx.x & 31) == 0);
+    const int tw = threadIdx.x >> 5;
     for (;;) {
         if (p < 0) return 0;
+        long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+        if (tm) t0 = clock64();
         const int e = c.colvar[p];
         const int lr = stage_and_ratio(c, p, e, false);
+        if (tm) t1 = clock64();
         if (lr == -2) return LPB200_STATUS_REF_TYPE_ERROR;
         if (lr < 0) return LPB200_STATUS_INFINITY;
         if (npiv >= max_pivots) return LPB200_STATUS_ITERATION_LIMIT;
         const int l = lr >> 16, src = lr & 0xffff;
-        sweep(c, ncols, p, src, e, l, log, log_cap, npiv);
+        sweep(c, ncols, p, src, e, l, log, log_cap, npiv, tm ? &t2 : nullptr);
+        if (tm) t3 = clock64();
         ++npiv;
         p = next_entering(c, ncols);
+        if (tm) {  // [warp][0]=stage incl. barrier, [1]=own sweep work, [2]=sweep incl. barrier, [3]=pivots
+            atomicAdd(c.timing + tw * 4 + 0, (unsigned long long)(t1 - t0));
+            atomicAdd(c.timing + tw * 4 + 1, (unsigned long long)(t2 - t1));
+            atomicAdd(c.timing + tw * 4 + 2, (unsigned long long)(t3 - t1));
+            atomicAdd(c.timing + tw * 4 + 3, 1ull);
+        }
     }
 }
 
@@ -425,6 +496,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
     c.T = reinterpret_cast<double *>(smem + sh.off_T);
     c.nr = reinterpret_cast<double *>(smem + sh.off_nr);
     c.fc = reinterpret_cast<double *>(smem + sh.off_fc);
+    c.pinvs = reinterpret_cast<double *>(smem + sh.off_pinvs);
     c.redkey = reinterpret_cast<unsigned long long *>(smem + sh.off_redkey);
     c.rowvar = reinterpret_cast<int *>(smem + sh.off_rowvar);
     c.nonecol = reinterpret_cast<int *>(smem + sh.off_nonecol);
@@ -446,8 +518,16 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
     c.cx = sh.cx;
     c.rpg = sh.rpg;
     c.tol = a.tol;
+    c.timing = a.timing;
     const double tol = a.tol;
-    const int nfc = (kSweepThreads / sh.cx) * sh.rpg + kRowChunk;
+    const int nfc = sh.nfc;
+    {
+        const int ry = tid / sh.cx;
+        c.cxi = tid - ry * sh.cx;
+        c.row0 = ry * sh.rpg;
+        c.row1 = min(c.row0 + sh.rpg, (nphys + kRowChunk - 1) / kRowChunk * kRowChunk);
+        if (ry >= sh.groups) c.row1 = c.row0;  // leftover threads (256 - groups*cx) have no block
+    }
 
     for (;;) {
         // ---- next problem off the device work queue ----
@@ -559,7 +639,9 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                     c.misc[MI_DSIZE] = sh.size_d0;
                     c.misc[MI_DFILL] = n;
                     c.misc[MI_DUSED] = n;
-                    c.misc[MI_RESELECT] = 0;
+                    c.redu32[kSweepWarps + 1] = 0u;
+                    c.redu32[kSweepWarps + 2] = 0xffffffffu;
+                    c.redu32[kSweepWarps + 3] = 0xffffffffu;
                 }
             }
             __syncthreads();
@@ -751,9 +833,26 @@ extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A,
     a.pivot_log = pivot_log;
     a.log_cap = log_cap;
     a.work_counter = counter;
+    a.timing = nullptr;
+    const bool dbg_timing = getenv("LPB_DEBUG_TIMING") != nullptr;
+    if (dbg_timing) {
+        LPB_CUDA(cudaMalloc((void **)&a.timing, 9 * 4 * 8));
+        LPB_CUDA(cudaMemset(a.timing, 0, 9 * 4 * 8));
+    }
     simplex_batched_kernel<<<(unsigned)grid, kThreads, dyn_smem, stream>>>(sh, a);
     LPB_CUDA(cudaGetLastError());
     LPB_CUDA(cudaFreeAsync(counter, stream));
+    if (dbg_timing) {  // debug only: synchronises
+        unsigned long long h[36];
+        LPB_CUDA(cudaStreamSynchronize(stream));
+        LPB_CUDA(cudaMemcpy(h, a.timing, sizeof(h), cudaMemcpyDeviceToHost));
+        for (int w = 0; w < 9; ++w)
+            if (h[w * 4 + 3])
+                fprintf(stderr, "[lpb timing] warp %d: stage+bar %.0f  own sweep %.0f  sweep+bar %.0f cycles/pivot (%llu pivots)\n",
+                        w, (double)h[w * 4] / h[w * 4 + 3], (double)h[w * 4 + 1] / h[w * 4 + 3],
+                        (double)h[w * 4 + 2] / h[w * 4 + 3], h[w * 4 + 3]);
+        cudaFree(a.timing);
+    }
     return 0;
 }
 
