@@ -10,7 +10,7 @@ import ctypes
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "liblp_b200.so")
+LIB_PATH = os.environ.get("LPB_LIB_PATH") or os.path.join(HERE, "liblp_b200.so")  # override: kernel experiments
 
 c_dp = ctypes.POINTER(ctypes.c_double)
 c_ip = ctypes.POINTER(ctypes.c_int32)

@@ -40,7 +40,10 @@
 
 namespace lpb {
 
-constexpr int kSweepWarps = 8;
+#ifndef LPB_SWEEP_WARPS
+#define LPB_SWEEP_WARPS 8
+#endif
+constexpr int kSweepWarps = LPB_SWEEP_WARPS;
 constexpr int kSweepThreads = kSweepWarps * 32;  // 256
 constexpr int kThreads = kSweepThreads + 32;     // + bookkeeping warp
 constexpr int kRowChunk = 4;                     // rows per unrolled sweep step
@@ -441,47 +444,72 @@ __device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, 
 // (redu32[9] != 0; redu32[10..11] stay 0xffffffff).
 __device__ __forceinline__ int next_entering(const Ctx &c, int ncols)
 {
-    const uint4 k0 = reinterpret_cast<const uint4 *>(c.redu32)[0];
-    const uint4 k1 = reinterpret_cast<const uint4 *>(c.redu32)[1];
-    const uint4 k2 = reinterpret_cast<const uint4 *>(c.redu32)[2];
-    if (k2.y != 0u) {
+    constexpr int kVec = (kSweepWarps + 4) / 4;
+    static_assert((kSweepWarps & 3) == 0, "redu32[] is read as uint4");
+    uint4 k[kVec];
+#pragma unroll
+    for (int q = 0; q < kVec; ++q) k[q] = reinterpret_cast<const uint4 *>(c.redu32)[q];
+    if (k[kVec - 1].y != 0u) {
         __syncthreads();  // everyone has read the flag before the bookkeeping lane can rewrite it
         return select_entering(c, ncols);
     }
-    const unsigned best = min(min(min(k0.x, k0.y), min(k0.z, k0.w)),
-                              min(min(min(k1.x, k1.y), min(k1.z, k1.w)), k2.x));
+    unsigned best = k[kVec - 1].x;
+#pragma unroll
+    for (int q = 0; q < kVec - 1; ++q) best = min(best, min(min(k[q].x, k[q].y), min(k[q].z, k[q].w)));
     return best == 0xffffffffu ? -1 : (int)(best & 0xffffu);
 }
 
 // SlackForm.solve loop (:442-466).  Returns 0 when optimal, else a terminal status code.
+// forced_row >= 0: the first pivot is the forced one of phase 1 (:524) -- x_aux (column
+// position m) enters, the basic variable of row forced_row leaves -- then the loop runs.
 __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pivots, int32_t *log,
-                                        int log_cap)
+                                        int log_cap, int forced_row)
 {
-    int p = select_entering(c, ncols);
+    bool forced = forced_row >= 0;
+    int p = forced ? c.m : select_entering(c, ncols);
+#ifdef LPB_TIMING
     const bool tm = (c.timing != nullptr) && ((threadIdx.x & 31) == 0);
-    const int tw = threadIdx.x >> 5;
+    unsigned long long acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
+#endif
+    int status = 0;
     for (;;) {
-        if (p < 0) return 0;
-        long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
-        if (tm) t0 = clock64();
+        if (p < 0) break;
+#ifdef LPB_TIMING
+        long long t0 = clock64(), t1, t2 = 0, t3;
+#endif
         const int e = c.colvar[p];
-        const int lr = stage_and_ratio(c, p, e, false);
-        if (tm) t1 = clock64();
-        if (lr == -2) return LPB200_STATUS_REF_TYPE_ERROR;
-        if (lr < 0) return LPB200_STATUS_INFINITY;
-        if (npiv >= max_pivots) return LPB200_STATUS_ITERATION_LIMIT;
+        int lr = stage_and_ratio(c, p, e, forced);
+#ifdef LPB_TIMING
+        t1 = clock64();
+#endif
+        if (forced) lr = (forced_row << 16) | forced_row;  // rows still hold their own slack variable
+        if (lr == -2) { status = LPB200_STATUS_REF_TYPE_ERROR; break; }
+        if (lr < 0) { status = LPB200_STATUS_INFINITY; break; }
+        if (npiv >= max_pivots) { status = LPB200_STATUS_ITERATION_LIMIT; break; }
         const int l = lr >> 16, src = lr & 0xffff;
-        sweep(c, ncols, p, src, e, l, log, log_cap, npiv, tm ? &t2 : nullptr);
-        if (tm) t3 = clock64();
+#ifdef LPB_TIMING
+        sweep(c, ncols, p, src, e, l, log, log_cap, npiv, &t2);
+        t3 = clock64();
+        if (tm) { acc0 += t1 - t0; acc1 += t2 - t1; acc2 += t3 - t1; acc3 += 1; }
+#else
+        sweep(c, ncols, p, src, e, l, log, log_cap, npiv);
+#endif
         ++npiv;
-        p = next_entering(c, ncols);
-        if (tm) {  // [warp][0]=stage incl. barrier, [1]=own sweep work, [2]=sweep incl. barrier, [3]=pivots
-            atomicAdd(c.timing + tw * 4 + 0, (unsigned long long)(t1 - t0));
-            atomicAdd(c.timing + tw * 4 + 1, (unsigned long long)(t2 - t1));
-            atomicAdd(c.timing + tw * 4 + 2, (unsigned long long)(t3 - t1));
-            atomicAdd(c.timing + tw * 4 + 3, 1ull);
+        if (forced) {
+            forced = false;
+            p = select_entering(c, ncols);
+        } else {
+            p = next_entering(c, ncols);
         }
     }
+#ifdef LPB_TIMING
+    // [warp][0]=stage incl. barrier, [1]=own sweep work, [2]=sweep incl. barrier, [3]=pivots
+    if (tm && acc3) {
+        unsigned long long *t = c.timing + (threadIdx.x >> 5) * 4;
+        atomicAdd(t + 0, acc0); atomicAdd(t + 1, acc1); atomicAdd(t + 2, acc2); atomicAdd(t + 3, acc3);
+    }
+#endif
+    return status;
 }
 
 __global__ void __launch_bounds__(kThreads, 2)
@@ -646,22 +674,20 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
             }
             __syncthreads();
 
-            if (phase1) {
+            // One instance of the pivot loop serves phase 1 (:526, entered through the forced
+            // pivot), phase 2 after it (:599) and phase 2 alone (:619).
+            int forced_row = phase1 ? idx0 : -1;
+            for (;;) {
+                status = run_loop(c, ncols, npiv, a.max_pivots, log, a.log_cap, forced_row);
+                if (forced_row < 0) break;  // phase 2 is done
+                forced_row = -1;
                 const int aux = n + m;
-                // forced pivot: x_aux enters, the most negative row leaves (:524)
-                if (npiv >= a.max_pivots) {
-                    status = LPB200_STATUS_ITERATION_LIMIT;
-                } else {
-                    (void)stage_and_ratio(c, m, aux, true);
-                    sweep(c, ncols, m, idx0, aux, idx0, log, a.log_cap, npiv);
-                    ++npiv;
-                    status = run_loop(c, ncols, npiv, a.max_pivots, log, a.log_cap);  // :526
-                }
                 if (status == 0) {
                     if (!(fabs(c.T[(size_t)n * S]) <= tol)) status = LPB200_STATUS_NO_SOLUTION;  // :528-530
                     else if (c.varpos[aux] < 0) status = LPB200_STATUS_REF_INDEX_ERROR;  // :541 -> :183
                 }
-                if (status == 0) {
+                if (status != 0) break;
+                {
                     // ---- rebuild the original objective (:537-541) ----
                     // basic ORIGINAL variables in iteration order of the `dependent` set
                     // (slack rows have objective coefficient None: skipped, :203)
@@ -736,10 +762,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                     }
                     ncols = m;
                     __syncthreads();
-                    status = run_loop(c, ncols, npiv, a.max_pivots, log, a.log_cap);  // :599
                 }
-            } else {
-                status = run_loop(c, ncols, npiv, a.max_pivots, log, a.log_cap);  // :619
             }
         }
 
@@ -836,17 +859,17 @@ extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A,
     a.timing = nullptr;
     const bool dbg_timing = getenv("LPB_DEBUG_TIMING") != nullptr;
     if (dbg_timing) {
-        LPB_CUDA(cudaMalloc((void **)&a.timing, 9 * 4 * 8));
-        LPB_CUDA(cudaMemset(a.timing, 0, 9 * 4 * 8));
+        LPB_CUDA(cudaMalloc((void **)&a.timing, 32 * 4 * 8));
+        LPB_CUDA(cudaMemset(a.timing, 0, 32 * 4 * 8));
     }
     simplex_batched_kernel<<<(unsigned)grid, kThreads, dyn_smem, stream>>>(sh, a);
     LPB_CUDA(cudaGetLastError());
     LPB_CUDA(cudaFreeAsync(counter, stream));
     if (dbg_timing) {  // debug only: synchronises
-        unsigned long long h[36];
+        unsigned long long h[32 * 4];
         LPB_CUDA(cudaStreamSynchronize(stream));
         LPB_CUDA(cudaMemcpy(h, a.timing, sizeof(h), cudaMemcpyDeviceToHost));
-        for (int w = 0; w < 9; ++w)
+        for (int w = 0; w <= kSweepWarps; ++w)
             if (h[w * 4 + 3])
                 fprintf(stderr, "[lpb timing] warp %d: stage+bar %.0f  own sweep %.0f  sweep+bar %.0f cycles/pivot (%llu pivots)\n",
                         w, (double)h[w * 4] / h[w * 4 + 3], (double)h[w * 4 + 1] / h[w * 4 + 3],
