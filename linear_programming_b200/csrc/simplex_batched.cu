@@ -564,6 +564,18 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
         __syncthreads();
         const int lp = c.misc[MI_LP];
         if (lp >= a.B) break;
+        if (tid >= kSweepThreads) {
+            // The 9th warp pulls the inputs of problem lp + gridDim.x into L2: with the queue
+            // handing out indices in order, that is the problem some CTA (usually this one) sets
+            // up one solve from now, which then reads A at L2 rather than HBM latency.
+            const long long nxt = (long long)lp + gridDim.x;
+            if (nxt < a.B) {
+                const char *pa = reinterpret_cast<const char *>(a.A + (size_t)nxt * n * m);
+                const size_t bytes = (size_t)n * m * 8;
+                for (size_t o = (size_t)(tid - kSweepThreads) * 128; o < bytes; o += 32 * 128)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pa + o));
+            }
+        }
         const double *gA = a.A + (size_t)lp * n * m;
         const double *gb = a.b + (size_t)lp * n;
         const double *gc = a.c + (size_t)lp * m;
@@ -614,15 +626,41 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
             // ---- SlackForm.__init__ (:230-302) (+ the x_aux column of :632-660 in phase 1) ----
             if (tid < kSweepThreads) {
                 const int warp = tid >> 5, lane = tid & 31;
-                for (int i = warp; i < n; i += kSweepWarps) {
-                    double *Ti = c.T + (size_t)i * S;
-                    const double *Ai = gA + (size_t)i * m;
-                    for (int j = lane; j < m; j += 32) Ti[1 + j] = -Ai[j];
-                    if (lane == 0) {
-                        Ti[0] = gb[i];
-                        Ti[1 + m] = phase1 ? 1.0 : 0.0;  // -(-1), :659 then :262
+                if ((m & 1) == 0 && ((reinterpret_cast<uintptr_t>(gA) & 15) == 0)) {
+                    // A as a flat stream of 128-bit loads, four in flight per thread; element pairs
+                    // never straddle a row because m is even
+                    const double2 *g2 = reinterpret_cast<const double2 *>(gA);
+                    const int total = (n * m) >> 1, hm = m >> 1;
+                    for (int base = tid; base < total; base += 4 * kSweepThreads) {
+                        double2 v[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int idx = base + u * kSweepThreads;
+                            if (idx < total) v[u] = __ldcs(g2 + idx);
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int idx = base + u * kSweepThreads;
+                            if (idx < total) {
+                                const int i = idx / hm, j = (idx - i * hm) * 2;
+                                double *Ti = c.T + (size_t)i * S + 1 + j;
+                                Ti[0] = -v[u].x;
+                                Ti[1] = -v[u].y;
+                            }
+                        }
                     }
-                    for (int k = m + 2 + lane; k < S; k += 32) Ti[k] = 0.0;
+                } else {
+                    for (int i = warp; i < n; i += kSweepWarps) {
+                        double *Ti = c.T + (size_t)i * S;
+                        const double *Ai = gA + (size_t)i * m;
+                        for (int j = lane; j < m; j += 32) Ti[1 + j] = -Ai[j];
+                    }
+                }
+                for (int i = tid; i < n; i += kSweepThreads) {
+                    double *Ti = c.T + (size_t)i * S;
+                    Ti[0] = gb[i];
+                    Ti[1 + m] = phase1 ? 1.0 : 0.0;  // -(-1), :659 then :262
+                    for (int k = m + 2; k < S; ++k) Ti[k] = 0.0;
                 }
                 double *obj = c.T + (size_t)n * S;
                 for (int k = tid; k < S; k += kSweepThreads) {
