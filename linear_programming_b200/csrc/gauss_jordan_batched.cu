@@ -33,9 +33,24 @@ namespace lpb {
 constexpr int kGjK = 16;            // pivots per panel
 constexpr int kGjPS = kGjK + 2;     // panel row stride in shared memory (16-byte aligned rows)
 constexpr int kGjThreads = 512;
+#ifndef LPB_GJ_ROWS
+#define LPB_GJ_ROWS 2
+#endif
+#ifndef LPB_GJ_AHEAD
+#define LPB_GJ_AHEAD 6
+#endif
+constexpr int kGjAhead = LPB_GJ_AHEAD;  // prefetch distance in chunks of kGjRows rows
+constexpr int kGjRows = LPB_GJ_ROWS;
+#ifndef LPB_GJ_BLOCK
+#define LPB_GJ_BLOCK 32
+#endif
+constexpr int kGjBlockRows = LPB_GJ_BLOCK;  // rows per work item of the trailing update   // rows in flight per thread in the trailing update
 
 // a: [B][n][n] working copy (destroyed), x: [B][n] holds b on entry and the solution on exit.
-__global__ void __launch_bounds__(kGjThreads, 2)
+#ifndef LPB_GJ_MINB
+#define LPB_GJ_MINB 2
+#endif
+__global__ void __launch_bounds__(kGjThreads, LPB_GJ_MINB)
 gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restrict__ x_all)
 {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -98,11 +113,21 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
             __syncthreads();
         }
         // ---- trailing update: columns k0+Kp .. n-1 and b (column index n) ----
-        for (int j = k0 + Kp + tid; j <= n; j += kGjThreads) {
+        // Three passes with a block barrier between them, so that the non-pivot rows can be
+        // split over SEVERAL threads per column once the trailing matrix is narrower than the
+        // CTA (otherwise most threads idle through the second half of the elimination):
+        //   1. one thread per column: the Kp pivot rows are taken through the updates of the
+        //      earlier pivots of the panel and the division, R[q]; R is parked in the pivot rows;
+        //   2. (column, row block) threads: every other row, Kp updates in the reference's
+        //      order, one read and one write per element, four rows in flight;
+        //   3. one thread per column: the pivot rows are eliminated by the later pivots of the
+        //      panel (Gauss-JORDAN) and take their final values.
+        const int jfirst = k0 + Kp;
+        const int C = n + 1 - jfirst;
+        for (int j = jfirst + tid; j <= n; j += kGjThreads) {
             double *col = (j < n) ? (a + j) : bx;
             const size_t cs = (j < n) ? (size_t)n : 1;  // element stride down the column
             double R[kGjK];
-            // pivot rows: updates by earlier pivots of the panel, then the division
 #pragma unroll
             for (int q = 0; q < kGjK; ++q) {
                 if (q < Kp) {
@@ -111,11 +136,73 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
 #pragma unroll
                     for (int t = 0; t < q; ++t) v = __dadd_rn(v, __dmul_rn(Pk[t], R[t]));
                     R[q] = __ddiv_rn(v, Pk[q]);
-                } else {
-                    R[q] = 0.0;
+                    col[(size_t)(k0 + q) * cs] = R[q];
                 }
             }
-            // pivot rows: eliminated by the later pivots of the panel (Gauss-JORDAN)
+        }
+        __syncthreads();
+        {
+            // work items = (column, block of kGjBlockRows rows), dealt round-robin: consecutive
+            // threads take consecutive columns (coalesced) and every thread gets the same number
+            // of items to within one, however narrow the trailing matrix has become
+            const int nblk = (n + kGjBlockRows - 1) / kGjBlockRows;
+            const int items = C * nblk;
+            for (int item = tid; item < items; item += kGjThreads) {
+                const int blk = item / C, jj = item - blk * C;
+                const int i0 = blk * kGjBlockRows, i1 = min(n, i0 + kGjBlockRows);
+                const int j = jfirst + jj;
+                double *col = (j < n) ? (a + j) : bx;
+                const size_t cs = (j < n) ? (size_t)n : 1;
+                double R[kGjK];
+#pragma unroll
+                for (int q = 0; q < kGjK; ++q) R[q] = (q < Kp) ? __ldcg(col + (size_t)(k0 + q) * cs) : 0.0;
+                int i = i0;
+                while (i < i1) {
+                    if (Kp == kGjK && i + kGjRows <= i1 && !(i + kGjRows > k0 && i < k0 + Kp)) {
+                        // kGjRows rows in flight, none of them a pivot row of this panel
+                        double v[kGjRows];
+#pragma unroll
+                        for (int r = 0; r < kGjRows; ++r) v[r] = col[(size_t)(i + r) * cs];
+                        // pull the rows kGjAhead chunks further down towards L1 while these are worked on
+#pragma unroll
+                        for (int r = 0; r < kGjRows; ++r) {
+                            const int ip = i + kGjAhead * kGjRows + r;
+                            if (ip < i1) asm volatile("prefetch.global.L1 [%0];" ::"l"(col + (size_t)ip * cs));
+                        }
+                        const double *Pi = P + (size_t)i * kGjPS;
+#pragma unroll
+                        for (int t = 0; t < kGjK; t += 2) {
+#pragma unroll
+                            for (int r = 0; r < kGjRows; ++r) {
+                                const double2 s2 = *reinterpret_cast<const double2 *>(Pi + r * kGjPS + t);
+                                v[r] = __dadd_rn(v[r], __dmul_rn(s2.x, R[t]));
+                                v[r] = __dadd_rn(v[r], __dmul_rn(s2.y, R[t + 1]));
+                            }
+                        }
+#pragma unroll
+                        for (int r = 0; r < kGjRows; ++r) col[(size_t)(i + r) * cs] = v[r];
+                        i += kGjRows;
+                    } else {
+                        if (!(i >= k0 && i < k0 + Kp)) {  // pivot rows are handled by passes 1 and 3
+                            const double *Pi = P + (size_t)i * kGjPS;
+                            double v = col[(size_t)i * cs];
+#pragma unroll
+                            for (int t = 0; t < kGjK; ++t)
+                                if (t < Kp) v = __dadd_rn(v, __dmul_rn(Pi[t], R[t]));
+                            col[(size_t)i * cs] = v;
+                        }
+                        ++i;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        for (int j = jfirst + tid; j <= n; j += kGjThreads) {
+            double *col = (j < n) ? (a + j) : bx;
+            const size_t cs = (j < n) ? (size_t)n : 1;
+            double R[kGjK];
+#pragma unroll
+            for (int q = 0; q < kGjK; ++q) R[q] = (q < Kp) ? __ldcg(col + (size_t)(k0 + q) * cs) : 0.0;
 #pragma unroll
             for (int q = 0; q < kGjK; ++q) {
                 if (q < Kp) {
@@ -126,26 +213,6 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
                         if (t < Kp) v = __dadd_rn(v, __dmul_rn(Pk[t], R[t]));
                     col[(size_t)(k0 + q) * cs] = v;
                 }
-            }
-            // every other row: Kp updates in the reference's order, one read, one write
-#pragma unroll 2
-            for (int i = 0; i < n; ++i) {
-                if (i >= k0 && i < k0 + Kp) continue;
-                const double *Pi = P + (size_t)i * kGjPS;
-                double v = col[(size_t)i * cs];
-                if (Kp == kGjK) {
-#pragma unroll
-                    for (int t = 0; t < kGjK; t += 2) {
-                        const double2 s2 = *reinterpret_cast<const double2 *>(Pi + t);
-                        v = __dadd_rn(v, __dmul_rn(s2.x, R[t]));
-                        v = __dadd_rn(v, __dmul_rn(s2.y, R[t + 1]));
-                    }
-                } else {
-#pragma unroll
-                    for (int t = 0; t < kGjK; ++t)
-                        if (t < Kp) v = __dadd_rn(v, __dmul_rn(Pi[t], R[t]));
-                }
-                col[(size_t)i * cs] = v;
             }
         }
         __syncthreads();
