@@ -9,13 +9,33 @@
 the C++ shims accept floats (cin >> double) and print "%.18f" separated by spaces.
 Reference crash classes propagate as the same Python exception (non-zero exit), as in the
 reference process.
+
+Stream mode -- add ``--stream``: stdin holds MANY problems of the same
+program, simply concatenated (whitespace separated, exactly the single-problem format
+repeated).  They are grouped by shape, each group goes to the GPU as ONE batched call
+(lpb200_simplex_batch / lpb200_gauss_jordan_batch), and the answers are printed in input
+order, each exactly as the single-problem program prints it.  An input on which the
+reference process dies prints the exception class name on a line of its own
+("AttributeError" / "IndexError" / "TypeError", or "IterationLimit") and the stream goes on,
+so `stress.py`-style drivers (week-2/diet/stress.py:30) can pipe a whole run through one
+process instead of one subprocess per LP.
 """
 from __future__ import annotations
 
 import sys
 
+import numpy as np
+
 from . import gauss_jordan
+from . import simplex as _simplex
 from .simplex import Simplex
+
+_CRASH_NAMES = {
+    _simplex.STATUS_REF_ATTRIBUTE_ERROR: "AttributeError",   # simplex.py:626
+    _simplex.STATUS_REF_INDEX_ERROR: "IndexError",           # simplex.py:541 -> :183
+    _simplex.STATUS_REF_TYPE_ERROR: "TypeError",             # simplex.py:409
+    _simplex.STATUS_ITERATION_LIMIT: "IterationLimit",       # engine-only: the reference would hang
+}
 
 
 def format_answer(anst, ansx) -> str:
@@ -37,9 +57,105 @@ def parse_lp_floats(text: str):
     return n, m, A, b, c
 
 
+def iter_lp_problems(text: str, integer: bool):
+    """Concatenated LP problems -> (n, m, A[n,m], b[n], c[m]) float64 arrays, in input order.
+    integer=True applies the reference parser's int() (simplex.py:712-717: a non-integer token
+    raises ValueError); integer=False reads doubles like the C++ stubs."""
+    toks = text.split()
+    conv = int if integer else float
+    pos = 0
+    while pos < len(toks):
+        if pos + 2 > len(toks):
+            raise ValueError("truncated problem header at token %d" % pos)
+        n, m = int(toks[pos]), int(toks[pos + 1])
+        need = n * m + n + m
+        body = toks[pos + 2:pos + 2 + need]
+        if n < 1 or m < 1 or len(body) < need:
+            raise ValueError("truncated or malformed problem at token %d (n=%d, m=%d)" % (pos, n, m))
+        vals = np.array([conv(t) for t in body], dtype=np.float64)
+        yield n, m, vals[:n * m].reshape(n, m), vals[n * m:n * m + n], vals[n * m + n:]
+        pos += 2 + need
+
+
+def iter_equations(text: str):
+    """Concatenated energy_values systems (energy_values.cc:66-80) -> (a[size,size], b[size])."""
+    toks = text.split()
+    pos = 0
+    while pos < len(toks):
+        size = int(toks[pos])
+        need = size * (size + 1)
+        body = toks[pos + 1:pos + 1 + need]
+        if size < 0 or len(body) < need:
+            raise ValueError("truncated system at token %d (size=%d)" % (pos, size))
+        vals = np.array([float(t) for t in body], dtype=np.float64).reshape(size, size + 1)
+        yield np.ascontiguousarray(vals[:, :size]), np.ascontiguousarray(vals[:, size])
+        pos += 1 + need
+
+
+def _solve_lp_batch(A, b, c):
+    """One shape group on the engine; separated out so CPU tests can substitute the checker."""
+    r = _simplex.solve_batch(A, b, c)
+    return r.status, r.x
+
+
+def _solve_eq_batch(a, b):
+    return gauss_jordan.solve_equation_batch(a, b)
+
+
+def solve_lp_stream(text: str, integer: bool) -> str:
+    problems = list(iter_lp_problems(text, integer))
+    groups = {}
+    for idx, (n, m, _, _, _) in enumerate(problems):
+        groups.setdefault((n, m), []).append(idx)
+    out = [None] * len(problems)
+    for (n, m), idxs in groups.items():
+        A = np.stack([problems[i][2] for i in idxs])
+        b = np.stack([problems[i][3] for i in idxs])
+        c = np.stack([problems[i][4] for i in idxs])
+        status, x = _solve_lp_batch(A, b, c)
+        for k, i in enumerate(idxs):
+            st = int(status[k])
+            if st in (-1, 0, 1):
+                out[i] = format_answer(st, [float(v) for v in x[k]])
+            else:
+                out[i] = _CRASH_NAMES.get(st, "Status%d" % st) + "\n"
+    return "".join(out)
+
+
+def solve_equation_stream(text: str) -> str:
+    systems = list(iter_equations(text))
+    groups = {}
+    for idx, (a, _) in enumerate(systems):
+        groups.setdefault(a.shape[0], []).append(idx)
+    out = [None] * len(systems)
+    for size, idxs in groups.items():
+        if size == 0:
+            for i in idxs:
+                out[i] = ""   # size 0 prints nothing (week-2/energy_values/tests/01)
+            continue
+        a = np.stack([systems[i][0] for i in idxs])
+        b = np.stack([systems[i][1] for i in idxs])
+        x = _solve_eq_batch(a, b)
+        for k, i in enumerate(idxs):
+            out[i] = gauss_jordan.format_column(x[k])
+    return "".join(out)
+
+
 def main(argv=None) -> int:
-    argv = sys.argv[1:] if argv is None else argv
+    argv = list(sys.argv[1:] if argv is None else argv)
+    stream = "--stream" in argv
+    argv = [t for t in argv if t != "--stream"]
     prog = argv[0] if argv else "simplex"
+    if prog not in ("simplex", "ad_allocation", "diet", "energy_values"):
+        sys.stderr.write("unknown program %r\n" % prog)
+        return 2
+    if stream:
+        text = sys.stdin.read()
+        if prog == "energy_values":
+            sys.stdout.write(solve_equation_stream(text))
+        else:
+            sys.stdout.write(solve_lp_stream(text, integer=(prog == "simplex")))
+        return 0
     if prog == "simplex":
         s = Simplex.parse(sys.stdin)
         anst, ansx = s.solve()
@@ -48,12 +164,9 @@ def main(argv=None) -> int:
         n, m, A, b, c = parse_lp_floats(sys.stdin.read())
         anst, ansx = Simplex(A, b, c, n, m).solve()
         sys.stdout.write(format_answer(anst, ansx))
-    elif prog == "energy_values":
+    else:
         a, b = gauss_jordan.read_equation(sys.stdin.read())
         sys.stdout.write(gauss_jordan.format_column(gauss_jordan.solve_equation(a, b)))
-    else:
-        sys.stderr.write("unknown program %r\n" % prog)
-        return 2
     return 0
 
 

@@ -1,0 +1,93 @@
+"""Stream mode of the stdin/stdout shims.
+
+CPU part: parsing, grouping by shape, ordering and formatting, with the engine call
+substituted by the checker (the product itself never imports oracle/).  GPU part: the real
+engine on the concatenated fixtures of the reference, against the reference's own answers."""
+import io
+import sys
+
+import numpy as np
+import pytest
+
+
+def _expected_stdout(case):
+    from linear_programming_b200.cli import format_answer
+    names = {3: "AttributeError\n", 4: "IndexError\n", 5: "TypeError\n"}
+    st = case["status"]
+    if st in names:
+        return names[st]
+    x = [float.fromhex(h) for h in case["x"]] if case["x"] is not None else None
+    return format_answer(st, x)
+
+
+def _fixture_cases(simplex_golden, limit=None):
+    cases = [c for c in simplex_golden["cases"] if c.get("stdin")]
+    return cases[:limit] if limit else cases
+
+
+def test_iter_lp_problems_roundtrip_and_errors():
+    from linear_programming_b200.cli import iter_lp_problems
+    text = "2 3\n1 2 3\n4 5 6\n7 8\n9 10 11\n" + "1 1\n-5\n3\n2\n"
+    got = list(iter_lp_problems(text, integer=True))
+    assert [(g[0], g[1]) for g in got] == [(2, 3), (1, 1)]
+    assert got[0][2].tolist() == [[1, 2, 3], [4, 5, 6]] and got[0][3].tolist() == [7, 8]
+    assert got[1][4].tolist() == [2]
+    with pytest.raises(ValueError):
+        list(iter_lp_problems("2 2\n1 2\n3 4\n5\n", integer=True))       # truncated
+    with pytest.raises(ValueError):
+        list(iter_lp_problems("1 1\n1.5\n2\n3\n", integer=True))          # int() like simplex.py:712-717
+    assert list(iter_lp_problems("1 1\n1.5\n2\n3\n", integer=False))[0][2][0, 0] == 1.5   # cin >> double
+    assert list(iter_lp_problems("  \n", integer=True)) == []
+
+
+def test_lp_stream_orders_and_formats_like_the_reference(monkeypatch, oracle_lib, simplex_golden):
+    from linear_programming_b200 import cli
+
+    def checker(A, b, c):
+        st, x, _, _, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=100000)
+        return st, x
+    monkeypatch.setattr(cli, "_solve_lp_batch", checker)
+    cases = _fixture_cases(simplex_golden)
+    assert len(cases) >= 30
+    # interleave shapes so that grouping has to restore the input order
+    text = "\n".join(c["stdin"] for c in cases)
+    assert cli.solve_lp_stream(text, integer=True) == "".join(_expected_stdout(c) for c in cases)
+
+
+def test_equation_stream_on_cpu(monkeypatch, oracle_lib, gj_golden):
+    from linear_programming_b200 import cli, gauss_jordan
+    monkeypatch.setattr(cli, "_solve_eq_batch", lambda a, b: oracle_lib.gauss_jordan_batch(a, b)[0])
+    cases = [c for c in gj_golden["cases"] if c.get("stdin") is not None]
+    text = "\n".join(c["stdin"] for c in cases)
+    want = "".join(gauss_jordan.format_column([float.fromhex(h) for h in c["x"]]) for c in cases)
+    assert cli.solve_equation_stream(text) == want
+    assert cli.solve_equation_stream("0\n") == ""     # size 0 prints nothing (tests/01)
+
+
+@pytest.mark.gpu
+def test_stream_cli_on_gpu_matches_reference_answers(monkeypatch, capsys, simplex_golden, gj_golden):
+    from linear_programming_b200 import cli, gauss_jordan
+    cases = _fixture_cases(simplex_golden)
+    monkeypatch.setattr(sys, "stdin", io.StringIO("\n".join(c["stdin"] for c in cases)))
+    assert cli.main(["simplex", "--stream"]) == 0
+    assert capsys.readouterr().out == "".join(_expected_stdout(c) for c in cases)
+    # the same stream through the C++-stub reader (doubles)
+    monkeypatch.setattr(sys, "stdin", io.StringIO("\n".join(c["stdin"] for c in cases)))
+    assert cli.main(["ad_allocation", "--stream"]) == 0
+    assert capsys.readouterr().out == "".join(_expected_stdout(c) for c in cases)
+    gcases = [c for c in gj_golden["cases"] if c.get("stdin") is not None]
+    monkeypatch.setattr(sys, "stdin", io.StringIO("\n".join(c["stdin"] for c in gcases)))
+    assert cli.main(["energy_values", "--stream"]) == 0
+    want = "".join(gauss_jordan.format_column([float.fromhex(h) for h in c["x"]]) for c in gcases)
+    assert capsys.readouterr().out == want
+
+
+@pytest.mark.gpu
+def test_single_problem_cli_is_byte_compatible(monkeypatch, capsys, simplex_golden):
+    from linear_programming_b200 import cli
+    for case in _fixture_cases(simplex_golden, limit=12):
+        if case["status"] not in (-1, 0, 1):
+            continue
+        monkeypatch.setattr(sys, "stdin", io.StringIO(case["stdin"]))
+        assert cli.main(["simplex"]) == 0
+        assert capsys.readouterr().out == _expected_stdout(case)
