@@ -65,6 +65,26 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def ncu_traffic(args, batch):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from the
+    committed ncu --set full capture of this very command (profiles/, see tools/gpu/profile_r1f.sh).
+    Only valid for the configuration that was captured; anything else reports null."""
+    path = os.path.join(ROOT, "profiles", "r1f_batched_ncu_summary.csv")
+    if not (batch == 65536 and args.dist == "D1" and args.n == 100 and args.m == 100 and os.path.exists(path)):
+        return None, None
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    total = 0.0
+    try:
+        import csv
+        with open(path) as f:
+            for row in csv.DictReader(f):
+                if row["launch"] == "0" and row["metric"] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    total += float(row["value"]) * unit[row["unit"]]
+    except Exception:
+        return None, None
+    return (total if total > 0 else None), "profiles/r1f_batched_ncu_summary.csv (ncu --set full, same command)"
+
+
 def config_dict(args, batch):
     return {
         "workload": "configs[3]: batched simplex, %d random feasible %dx%d LPs per GPU (%s), "
@@ -106,7 +126,11 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.lines.append(line.strip())
 
-    def stop(self):
+    def mark(self):
+        """Index of the next sample line: brackets the timed region inside a longer recording."""
+        return len(self.lines)
+
+    def stop(self, lo=0, hi=None):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -117,7 +141,10 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons, power = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        window = self.lines[lo:hi] if hi is not None and hi > lo else self.lines[lo:]
+        if not window:
+            window = self.lines
+        for ln in window:
             parts = [p.strip() for p in ln.split(",")]
             if len(parts) < 7:
                 continue
@@ -263,22 +290,27 @@ def ours_arm(args):
                                                  d_st.data_ptr(), d_x.data_ptr(), d_obj.data_ptr(),
                                                  d_np.data_ptr(), None, 0, stream))
 
+    # nvidia-smi is started BEFORE the warm-up (its NVML start-up can stall a launch by a few ms)
+    # and keeps sampling through the timed region; only the samples inside it are reported
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     for _ in range(max(args.warmup, 3)):
         step()
     torch.cuda.synchronize()
-    sampler = ClockSampler(local_rank)
     K = args.steps
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
     barrier()
     torch.cuda.synchronize()
-    sampler.start()
+    lo = sampler.mark()
     evs[0].record()
     for k in range(K):
         step()
         evs[k + 1].record()
     torch.cuda.synchronize()
+    time.sleep(0.12)
+    hi = sampler.mark()
     barrier()
-    clocks = sampler.stop()
+    clocks = sampler.stop(lo, hi)
     total_ms = max_over_ranks(evs[0].elapsed_time(evs[K]))
     kern_ms = [evs[k].elapsed_time(evs[k + 1]) for k in range(K)]
     pivots_step = int(d_np.sum().item())
@@ -288,9 +320,10 @@ def ours_arm(args):
     alg_bytes = 16.0 * (n + 1) * (m + 1) * pivots_step
     achieved = alg_bytes / avg_kern_s / 1e9
     input_bytes = B * (n * m + n + m) * 8 + B * (m * 8 + 16)
+    traffic, traffic_src = ncu_traffic(args, B)
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": None, "kernel": "simplex_batched_kernel", "launch_ms": avg_kern_s * 1e3,
+        "traffic": traffic, "traffic_source": traffic_src, "kernel": "simplex_batched_kernel", "launch_ms": avg_kern_s * 1e3, "launch_ms_each": [round(v, 3) for v in kern_ms],
         "algorithmic_bytes_per_launch": alg_bytes, "pivots_per_launch": pivots_step,
         "peak_source": peak_src,
         "note": "tableau is shared-memory resident: 'achieved' is EFFECTIVE GB/s (16*(n+1)*(m+1) B per pivot, "
