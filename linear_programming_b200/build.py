@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "liblp_b200.so")
 SOURCES = ["lp_api.cu", "simplex_batched.cu", "simplex_single.cu", "gauss_jordan_batched.cu"]
-HEADERS = ["lp_common.cuh", "lp_host.h", os.path.join("..", "..", "include", "lp_b200.h")]
+HEADERS = ["lp_common.cuh", "lp_host.h", "simplex_batched_impl.cuh", os.path.join("..", "..", "include", "lp_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

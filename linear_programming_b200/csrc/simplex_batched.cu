@@ -38,793 +38,28 @@
 #include "lp_common.cuh"
 #include "lp_host.h"
 
-namespace lpb {
 
-#ifndef LPB_SWEEP_WARPS
+// ---- kernel variants (same source, different parameters) ----
+#define LPB_NS smem8
 #define LPB_SWEEP_WARPS 8
-#endif
-constexpr int kSweepWarps = LPB_SWEEP_WARPS;
-constexpr int kSweepThreads = kSweepWarps * 32;  // 256
-constexpr int kThreads = kSweepThreads + 32;     // + bookkeeping warp
-constexpr int kRowChunk = 4;                     // rows per unrolled sweep step
+#define LPB_REG_ROWS 0
+#define LPB_MIN_BLOCKS 2
+#include "simplex_batched_impl.cuh"
+#undef LPB_NS
+#undef LPB_SWEEP_WARPS
+#undef LPB_REG_ROWS
+#undef LPB_MIN_BLOCKS
 
-typedef int16_t tab_t;
+#define LPB_NS reg15
+#define LPB_SWEEP_WARPS 15
+#define LPB_REG_ROWS 12
+#define LPB_MIN_BLOCKS 1
+#include "simplex_batched_impl.cuh"
+#undef LPB_NS
+#undef LPB_SWEEP_WARPS
+#undef LPB_REG_ROWS
+#undef LPB_MIN_BLOCKS
 
-// Shared-memory carve-up, computed on the host and passed by value.
-struct BatchShape {
-    int n, m;
-    int S;        // tableau row stride in doubles (even): 1 constant + m + 1 auxiliary, rounded up
-    int cx;       // lanes across column pairs in the sweep (<= 64)
-    int groups;   // row groups = 256 / cx
-    int rpg;      // physical rows per row group (multiple of kRowChunk)
-    int nfc;      // doubles in fc[] (groups * rpg + one chunk of zero padding)
-    int size_i0;  // initial table size of `independent` (phase 2: m keys / phase 1: m+1 keys)
-    int size_i1;
-    int size_d0;  // initial table size of `dependent` (n keys)
-    int cap_i, cap_d, cap_s;
-    // byte offsets from the (16-byte aligned) dynamic smem base
-    int off_T, off_nr, off_fc, off_pinvs, off_redkey, off_rowvar, off_nonecol, off_untouched, off_rowslot,
-        off_colvar, off_colslot, off_varpos, off_basis0, off_redvar, off_redu32, off_misc,
-        off_tab_i, off_tab_d, off_tab_s;
-    int bytes;
-};
-
-static inline int align_up(int v, int a) { return (v + a - 1) / a * a; }
-
-static BatchShape make_batch_shape(int n, int m)
-{
-    BatchShape s;
-    s.n = n;
-    s.m = m;
-    s.S = align_up(m + 2, 2);
-    const int npairs = s.S / 2;
-    const int passes = (npairs + 63) / 64;          // column pairs per lane (wide tableaus loop)
-    s.cx = (npairs + passes - 1) / passes;           // lanes across column pairs: 51 at m = 100
-    const int nphys = n + 2;  // n basic rows + objective row + one spare slot
-    s.groups = kSweepThreads / s.cx;                 // row groups: 5 at m = 100 (255 of 256 threads busy)
-    s.rpg = align_up((nphys + s.groups - 1) / s.groups, kRowChunk);
-    s.nfc = s.groups * s.rpg + kRowChunk;
-    s.size_i0 = pyset_initial_size(m);
-    s.size_i1 = pyset_initial_size(m + 1);
-    s.size_d0 = pyset_initial_size(n);
-    s.cap_i = pyset_capacity(m + 1);
-    s.cap_d = pyset_capacity(n);
-    s.cap_s = s.cap_i > s.cap_d ? s.cap_i : s.cap_d;
-    const int nv = n + m + 1;
-    int o = 0;
-    s.off_T = o;          o += nphys * s.S * 8;
-    s.off_nr = o;         o += s.S * 8;
-    s.off_fc = o;         o += s.nfc * 8;
-    s.off_pinvs = o;      o += s.nfc * 8;
-    s.off_redkey = o;     o += kSweepWarps * 16;
-    s.off_rowvar = o;     o += align_up(nphys, 4) * 4;
-    s.off_nonecol = o;    o += align_up(nphys, 4) * 4;
-    s.off_untouched = o;  o += align_up(nphys, 4) * 4;
-    s.off_rowslot = o;    o += align_up(nphys, 4) * 4;
-    s.off_colvar = o;     o += align_up(m + 1, 4) * 4;
-    s.off_colslot = o;    o += align_up(m + 1, 4) * 4;
-    s.off_varpos = o;     o += align_up(nv, 4) * 4;
-    s.off_basis0 = o;     o += align_up((nv + 31) / 32, 4) * 4;
-    s.off_redvar = o;     o += kSweepWarps * 4;
-    s.off_redu32 = o;     o += (kSweepWarps + 4) * 4;
-    s.off_misc = o;       o += 16 * 4;
-    s.off_tab_i = o;      o += align_up(s.cap_i * (int)sizeof(tab_t), 16);
-    s.off_tab_d = o;      o += align_up(s.cap_d * (int)sizeof(tab_t), 16);
-    s.off_tab_s = o;      o += align_up(s.cap_s * (int)sizeof(tab_t), 16);
-    s.bytes = align_up(o, 16);
-    return s;
-}
-
-struct BatchArgs {
-    int B;
-    const double *A, *b, *c;
-    double tol;
-    int max_pivots;
-    int32_t *status;
-    double *x, *objective;
-    int32_t *npivots;
-    int32_t *pivot_log;
-    int log_cap;
-    unsigned int *work_counter;
-    unsigned long long *timing;  // debug (LPB_DEBUG_TIMING): per-phase cycle counters, else null
-};
-
-// misc[] slots
-enum { MI_LP = 0, MI_ISIZE, MI_IFILL, MI_IUSED, MI_DSIZE, MI_DFILL, MI_DUSED, MI_NLIST, MI_RESELECT };
-
-// Per-CTA view of the carved shared memory (pointers live in registers).
-struct Ctx {
-    double *T, *nr, *fc, *pinvs;
-    unsigned long long *redkey;
-    int *rowvar, *nonecol, *untouched, *rowslot, *colvar, *colslot, *varpos;
-    unsigned *basis0;
-    int *redvar;
-    unsigned *redu32;
-    int *misc;
-    tab_t *tab_i, *tab_d, *tab_s;
-    int n, m, S, cx, rpg;
-    int cxi, row0, row1;  // this thread's column-pair lane and physical row block [row0, row1)
-    int spare;  // physical row slot currently unused (uniform across the CTA)
-    double tol;
-    bool track_dep;  // the `dependent` set order only matters when phase 1 runs (:538)
-    unsigned long long *timing;
-};
-
-// ---- entering column: first positive objective coefficient in set-slot order (:390-392) ----
-// Stand-alone pass (loop entry, and after a set-table rebuild).  Returns the column position,
-// or -1 when no coefficient is > tol (loop ends, :447).
-__device__ __forceinline__ int select_entering(const Ctx &c, int ncols)
-{
-    const int tid = threadIdx.x;
-    if (tid < kSweepThreads) {
-        unsigned key = 0xffffffffu;
-        const double *obj = c.T + (size_t)c.n * c.S + 1;
-        for (int k = tid; k < ncols; k += kSweepThreads)
-            if (obj[k] > c.tol) key = min(key, ((unsigned)c.colslot[k] << 16) | (unsigned)k);
-        key = __reduce_min_sync(0xffffffffu, key);
-        if ((tid & 31) == 0) c.redu32[tid >> 5] = key;
-    }
-    __syncthreads();
-    unsigned best = c.redu32[0];
-#pragma unroll
-    for (int w = 1; w < kSweepWarps; ++w) best = min(best, c.redu32[w]);
-    __syncthreads();  // redu32 is rewritten by the next sweep
-    return best == 0xffffffffu ? -1 : (int)(best & 0xffffu);
-}
-
-// ---- step 1: stage the pivot column, min-ratio test with the reference's degenerate skip (:394-436) ----
-// One thread per physical row: fc[i] = snapped T[i][1+p]; the entry is zeroed in place (the
-// column now belongs to the leaving variable, whose coefficient starts from None, :187 opt).
-// Every candidate row also leaves its scaled reciprocal pivot in pinvs[i] (:328-330), so the
-// sweep starts without a division on its critical path.
-// Returns (leaving VARIABLE id << 16 | its physical row), -1 if unbounded, -2 if the reference
-// would raise TypeError.  The row travels with the id through the reduction because varpos[]
-// is rewritten by the bookkeeping lane as soon as the barrier below is passed.
-struct __align__(16) RatioPartial {
-    unsigned long long key;
-    int id;
-    int pad;
-};
-
-__device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool forced)
-{
-    const int tid = threadIdx.x;
-    const int nphys = c.n + 2;
-    int crash = 0;
-    // only the warps that own rows take part (4 of 8 at n = 100)
-    const int nsw = min(kSweepWarps, (nphys + 31) >> 5);
-    RatioPartial *part = reinterpret_cast<RatioPartial *>(c.redkey);
-    if (tid < nsw * 32) {
-        unsigned long long key = kKeyNone;
-        int var = 0x7fffffff;
-        const bool e_in_basis0 = (c.basis0[e >> 5] >> (e & 31)) & 1u;
-        const bool e_is_slack = e < c.n;
-        for (int i = tid; i < nphys; i += nsw * 32) {
-            const int v = c.rowvar[i];
-            double f = 0.0;
-            if (v >= 0 || i == c.n) {
-                double *q = c.T + (size_t)i * c.S + 1 + p;
-                f = *q;
-                *q = 0.0;
-                if (fabs(f) <= c.tol) f = 0.0;  // substitute() returns the row unchanged (:203-205)
-            }
-            c.fc[i] = f;
-            if (v >= 0) {
-                const int nc = c.nonecol[i];
-                crash |= (nc == kNoneInitial && e_is_slack) || (nc == e) || (c.untouched[i] && e_in_basis0);
-                if (f != 0.0) {  // row is rewritten by this pivot: its only None is column e
-                    c.nonecol[i] = e;
-                    c.untouched[i] = 0;
-                }
-                const double coeff = -f;
-                const bool cand = coeff > c.tol;
-                if (cand || (forced && f != 0.0)) c.pinvs[i] = pivot_inverse(f, c.tol);
-                if (cand) {
-                    const double ratio = snap(__ddiv_rn(c.T[(size_t)i * c.S], coeff), c.tol);
-                    if (ratio != 0.0) {  // zero ratios count as +inf in min_index (:161)
-                        const unsigned long long k = order_key(ratio);
-                        const int vi = (v << 16) | i;  // ties -> lowest variable id (rows are unique per id)
-                        if (k < key || (k == key && vi < var)) {
-                            key = k;
-                            var = vi;
-                        }
-                    }
-                }
-            }
-        }
-        // lexicographic (key, id) minimum across the warp with three redux.sync steps
-        const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
-        const unsigned mh = __reduce_min_sync(0xffffffffu, hi);
-        const unsigned ml = __reduce_min_sync(0xffffffffu, hi == mh ? lo : 0xffffffffu);
-        const unsigned mi = __reduce_min_sync(0xffffffffu, (hi == mh && lo == ml) ? (unsigned)var : 0x7fffffffu);
-        if ((tid & 31) == 0) {
-            RatioPartial r;
-            r.key = ((unsigned long long)mh << 32) | ml;
-            r.id = (int)mi;
-            r.pad = 0;
-            part[tid >> 5] = r;
-        }
-    }
-    if (forced) crash = 0;
-    if (__syncthreads_or(crash)) return -2;
-    RatioPartial best = part[0];
-    for (int w = 1; w < nsw; ++w) {
-        const RatioPartial r = part[w];
-        if (r.key < best.key || (r.key == best.key && r.id < best.id)) best = r;
-    }
-    return best.key == kKeyNone ? -1 : best.id;
-}
-
-// ---- set bookkeeping by one lane of the 9th warp, overlapped with the sweep (:369-381) ----
-// e sat at column position p; l owned physical row `src`; the new row of e is written to `dest`.
-// Also publishes the entering-key candidate of column p (now variable l) for the next pivot.
-__device__ __forceinline__ void bookkeeping(const Ctx &c, int p, int src, int dest, int e, int l, double pinv)
-{
-    const int eslot = c.colslot[p];
-    const int lrowslot = c.rowslot[src];
-    c.rowvar[src] = -1;  // becomes the spare slot
-    c.rowvar[dest] = e;
-    c.nonecol[dest] = e;
-    c.untouched[dest] = 0;
-    c.colvar[p] = l;
-    c.varpos[e] = ~dest;
-    c.varpos[l] = p;
-    bool rebuild;
-    int reselect = 0;
-    if (c.track_dep) {  // dependent.remove(l); dependent.add(e)
-        PySet d = {c.misc[MI_DSIZE], c.misc[MI_DFILL], c.misc[MI_DUSED]};
-        pyset_remove_slot(c.tab_d, d, lrowslot);
-        c.rowslot[dest] = pyset_add(c.tab_d, d, e, &rebuild);
-        if (rebuild) {
-            pyset_rebuild(c.tab_d, c.tab_s, d);
-            for (int s = 0; s < d.size; ++s) {
-                const int v = (int)c.tab_d[s];
-                if (v >= 0) c.rowslot[~c.varpos[v]] = s;
-            }
-        }
-        c.misc[MI_DSIZE] = d.size;
-        c.misc[MI_DFILL] = d.fill;
-        c.misc[MI_DUSED] = d.used;
-    }
-    {  // independent.remove(e); independent.add(l)
-        PySet s = {c.misc[MI_ISIZE], c.misc[MI_IFILL], c.misc[MI_IUSED]};
-        pyset_remove_slot(c.tab_i, s, eslot);
-        c.colslot[p] = pyset_add(c.tab_i, s, l, &rebuild);
-        if (rebuild) {  // every slot moved: the keys computed by the sweep lanes are stale
-            pyset_rebuild(c.tab_i, c.tab_s, s);
-            for (int t = 0; t < s.size; ++t) {
-                const int v = (int)c.tab_i[t];
-                if (v >= 0) c.colslot[c.varpos[v]] = t;
-            }
-            reselect = 1;
-        }
-        c.misc[MI_ISIZE] = s.size;
-        c.misc[MI_IFILL] = s.fill;
-        c.misc[MI_IUSED] = s.used;
-    }
-    // new objective coefficient of column p: snap(None + c_e * (1/pivot)) (:314-318, :343-344)
-    unsigned key = 0xffffffffu;
-    const double fobj = c.fc[c.n];
-    if (fobj != 0.0) {
-        const double v = axpy_snap(0.0, fobj, snap(-pinv, c.tol), c.tol);
-        if (v > c.tol) key = ((unsigned)c.colslot[p] << 16) | (unsigned)p;
-    }
-    c.redu32[kSweepWarps] = key;
-    c.redu32[kSweepWarps + 1] = (unsigned)reselect;
-}
-
-// ---- shared-memory helpers for the sweep (32-bit shared addresses, explicit instruction forms) ----
-__device__ __forceinline__ void lds_f64x2(uint32_t addr, double &x, double &y)
-{
-    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(addr) : "memory");
-}
-__device__ __forceinline__ void sts_f64x2(uint32_t addr, double x, double y)
-{
-    asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(addr), "d"(x), "d"(y) : "memory");
-}
-// snap-to-zero as a predicated 8-byte store of +0.0 over a value already stored (|v| <= tol is
-// rare; this replaces a compare + two selects + register shuffling per element by compare + store)
-__device__ __forceinline__ void sts_zero_if_snapped(uint32_t addr, double v, double tol)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        ".reg .f64 t;\n"
-        "abs.f64 t, %1;\n"
-        "setp.le.f64 p, t, %2;\n"
-        "@p st.shared.u64 [%0], 0;\n"
-        "}\n" ::"r"(addr), "d"(v), "d"(tol) : "memory");
-}
-
-// ---- step 2: SlackForm.pivot(e, l) (:348-385) as one sweep ----
-// e sits at column position p, l owns physical row src, c.spare receives the new row of e.
-__device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, int l, int32_t *log,
-                                      int log_cap, int npiv, long long *t_own = nullptr)
-{
-    const int tid = threadIdx.x;
-    const int n = c.n, S = c.S;
-    const int nphys = n + 2;
-    const int dest = c.spare;
-    const double tol = c.tol;
-    const double pinv = c.pinvs[src];  // snap(-1 * (1.0 / pivot)), left by the row's own thread in step 1
-    if (tid < kSweepThreads) {
-        unsigned mykey = 0xffffffffu;
-        if (c.row0 < c.row1) {
-            const int npairs = S >> 1;
-            const double2 *Tsrc = reinterpret_cast<const double2 *>(c.T + (size_t)src * S);
-            const uint32_t tbase = (uint32_t)__cvta_generic_to_shared(c.T);
-            const uint32_t rsb = (uint32_t)S * 8u;  // row stride in bytes
-            const int src4 = src & ~(kRowChunk - 1), dest4 = dest & ~(kRowChunk - 1),
-                      n4 = n & ~(kRowChunk - 1);
-            for (int cp = c.cxi; cp < npairs; cp += c.cx) {
-                // this lane's two entries of the scaled pivot row (make_pivot_constraint :325-345)
-                double2 r2 = Tsrc[cp];
-                r2.x = (2 * cp == 1 + p) ? snap(-pinv, tol) : snap(__dmul_rn(pinv, r2.x), tol);
-                r2.y = (2 * cp + 1 == 1 + p) ? snap(-pinv, tol) : snap(__dmul_rn(pinv, r2.y), tol);
-                uint32_t qa = tbase + (uint32_t)c.row0 * rsb + (uint32_t)cp * 16u;
-                const double *fcp = c.fc + c.row0;
-                for (int i = c.row0; i < c.row1; i += kRowChunk, qa += kRowChunk * rsb, fcp += kRowChunk) {
-                    const double2 fa = *reinterpret_cast<const double2 *>(fcp);
-                    const double2 fb = *reinterpret_cast<const double2 *>(fcp + 2);
-                    const bool special = (i == src4) | (i == dest4) | (i == n4);
-                    if (!special && fa.x != 0.0 && fa.y != 0.0 && fb.x != 0.0 && fb.y != 0.0) {
-                        double a0x, a0y, a1x, a1y, a2x, a2y, a3x, a3y;
-                        lds_f64x2(qa, a0x, a0y);
-                        lds_f64x2(qa + rsb, a1x, a1y);
-                        lds_f64x2(qa + 2 * rsb, a2x, a2y);
-                        lds_f64x2(qa + 3 * rsb, a3x, a3y);
-                        a0x = __dadd_rn(a0x, __dmul_rn(fa.x, r2.x));
-                        a0y = __dadd_rn(a0y, __dmul_rn(fa.x, r2.y));
-                        a1x = __dadd_rn(a1x, __dmul_rn(fa.y, r2.x));
-                        a1y = __dadd_rn(a1y, __dmul_rn(fa.y, r2.y));
-                        a2x = __dadd_rn(a2x, __dmul_rn(fb.x, r2.x));
-                        a2y = __dadd_rn(a2y, __dmul_rn(fb.x, r2.y));
-                        a3x = __dadd_rn(a3x, __dmul_rn(fb.y, r2.x));
-                        a3y = __dadd_rn(a3y, __dmul_rn(fb.y, r2.y));
-                        sts_f64x2(qa, a0x, a0y);
-                        sts_f64x2(qa + rsb, a1x, a1y);
-                        sts_f64x2(qa + 2 * rsb, a2x, a2y);
-                        sts_f64x2(qa + 3 * rsb, a3x, a3y);
-                        sts_zero_if_snapped(qa, a0x, tol);
-                        sts_zero_if_snapped(qa + 8, a0y, tol);
-                        sts_zero_if_snapped(qa + rsb, a1x, tol);
-                        sts_zero_if_snapped(qa + rsb + 8, a1y, tol);
-                        sts_zero_if_snapped(qa + 2 * rsb, a2x, tol);
-                        sts_zero_if_snapped(qa + 2 * rsb + 8, a2y, tol);
-                        sts_zero_if_snapped(qa + 3 * rsb, a3x, tol);
-                        sts_zero_if_snapped(qa + 3 * rsb + 8, a3y, tol);
-                    } else {
-                        const double f4[kRowChunk] = {fa.x, fa.y, fb.x, fb.y};
-                        double2 *col = reinterpret_cast<double2 *>(c.T) + cp;
-                        const int rs = S >> 1;  // row stride in double2
-#pragma unroll
-                        for (int j = 0; j < kRowChunk; ++j) {
-                            const int ii = i + j;
-                            if (ii >= nphys || ii == src) continue;
-                            double2 *q = col + (size_t)ii * rs;
-                            if (ii == dest) {  // store(entering_idx, entering_constraint) (:352)
-                                *q = r2;
-                                continue;
-                            }
-                            double2 a = *q;
-                            const double f = f4[j];
-                            if (f != 0.0) {
-                                a.x = axpy_snap(a.x, f, r2.x, tol);
-                                a.y = axpy_snap(a.y, f, r2.y, tol);
-                                *q = a;
-                            }
-                            if (ii == n) {  // objective row: candidates for the NEXT entering column (:390-392)
-                                const int k0 = 2 * cp - 1;  // column position of a.x (-1 is the constant)
-                                if (k0 >= 0 && k0 < ncols && k0 != p && a.x > tol)
-                                    mykey = min(mykey, ((unsigned)c.colslot[k0] << 16) | (unsigned)k0);
-                                if (k0 + 1 < ncols && k0 + 1 != p && a.y > tol)
-                                    mykey = min(mykey, ((unsigned)c.colslot[k0 + 1] << 16) | (unsigned)(k0 + 1));
-                            }
-                        }
-                    }
-                }
-            }
-        }
-        mykey = __reduce_min_sync(0xffffffffu, mykey);
-        if ((tid & 31) == 0) c.redu32[tid >> 5] = mykey;
-    } else if (tid == kSweepThreads) {
-        if (log != nullptr && npiv < log_cap) {
-            log[2 * npiv] = e;
-            log[2 * npiv + 1] = l;
-        }
-        bookkeeping(c, p, src, dest, e, l, pinv);
-    }
-    c.spare = src;
-    if (t_own) *t_own = clock64();
-    __syncthreads();
-}
-
-// Next entering position after a sweep: the partial keys it left in redu32[0..8] (three
-// 128-bit loads), or a fresh pass when the set table was rebuilt and every slot moved
-// (redu32[9] != 0; redu32[10..11] stay 0xffffffff).
-__device__ __forceinline__ int next_entering(const Ctx &c, int ncols)
-{
-    constexpr int kVec = (kSweepWarps + 4) / 4;
-    static_assert((kSweepWarps & 3) == 0, "redu32[] is read as uint4");
-    uint4 k[kVec];
-#pragma unroll
-    for (int q = 0; q < kVec; ++q) k[q] = reinterpret_cast<const uint4 *>(c.redu32)[q];
-    if (k[kVec - 1].y != 0u) {
-        __syncthreads();  // everyone has read the flag before the bookkeeping lane can rewrite it
-        return select_entering(c, ncols);
-    }
-    unsigned best = k[kVec - 1].x;
-#pragma unroll
-    for (int q = 0; q < kVec - 1; ++q) best = min(best, min(min(k[q].x, k[q].y), min(k[q].z, k[q].w)));
-    return best == 0xffffffffu ? -1 : (int)(best & 0xffffu);
-}
-
-// SlackForm.solve loop (:442-466).  Returns 0 when optimal, else a terminal status code.
-// forced_row >= 0: the first pivot is the forced one of phase 1 (:524) -- x_aux (column
-// position m) enters, the basic variable of row forced_row leaves -- then the loop runs.
-__device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pivots, int32_t *log,
-                                        int log_cap, int forced_row)
-{
-    bool forced = forced_row >= 0;
-    int p = forced ? c.m : select_entering(c, ncols);
-#ifdef LPB_TIMING
-    const bool tm = (c.timing != nullptr) && ((threadIdx.x & 31) == 0);
-    unsigned long long acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
-#endif
-    int status = 0;
-    for (;;) {
-        if (p < 0) break;
-#ifdef LPB_TIMING
-        long long t0 = clock64(), t1, t2 = 0, t3;
-#endif
-        const int e = c.colvar[p];
-        int lr = stage_and_ratio(c, p, e, forced);
-#ifdef LPB_TIMING
-        t1 = clock64();
-#endif
-        if (forced) lr = (forced_row << 16) | forced_row;  // rows still hold their own slack variable
-        if (lr == -2) { status = LPB200_STATUS_REF_TYPE_ERROR; break; }
-        if (lr < 0) { status = LPB200_STATUS_INFINITY; break; }
-        if (npiv >= max_pivots) { status = LPB200_STATUS_ITERATION_LIMIT; break; }
-        const int l = lr >> 16, src = lr & 0xffff;
-#ifdef LPB_TIMING
-        sweep(c, ncols, p, src, e, l, log, log_cap, npiv, &t2);
-        t3 = clock64();
-        if (tm) { acc0 += t1 - t0; acc1 += t2 - t1; acc2 += t3 - t1; acc3 += 1; }
-#else
-        sweep(c, ncols, p, src, e, l, log, log_cap, npiv);
-#endif
-        ++npiv;
-        if (forced) {
-            forced = false;
-            p = select_entering(c, ncols);
-        } else {
-            p = next_entering(c, ncols);
-        }
-    }
-#ifdef LPB_TIMING
-    // [warp][0]=stage incl. barrier, [1]=own sweep work, [2]=sweep incl. barrier, [3]=pivots
-    if (tm && acc3) {
-        unsigned long long *t = c.timing + (threadIdx.x >> 5) * 4;
-        atomicAdd(t + 0, acc0); atomicAdd(t + 1, acc1); atomicAdd(t + 2, acc2); atomicAdd(t + 3, acc3);
-    }
-#endif
-    return status;
-}
-
-__global__ void __launch_bounds__(kThreads, 2)
-simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
-{
-    extern __shared__ __align__(16) unsigned char smem[];
-    const int tid = threadIdx.x;
-    const int n = sh.n, m = sh.m, S = sh.S;
-    const int nv = n + m + 1;
-    const int nphys = n + 2;
-    Ctx c;
-    c.T = reinterpret_cast<double *>(smem + sh.off_T);
-    c.nr = reinterpret_cast<double *>(smem + sh.off_nr);
-    c.fc = reinterpret_cast<double *>(smem + sh.off_fc);
-    c.pinvs = reinterpret_cast<double *>(smem + sh.off_pinvs);
-    c.redkey = reinterpret_cast<unsigned long long *>(smem + sh.off_redkey);
-    c.rowvar = reinterpret_cast<int *>(smem + sh.off_rowvar);
-    c.nonecol = reinterpret_cast<int *>(smem + sh.off_nonecol);
-    c.untouched = reinterpret_cast<int *>(smem + sh.off_untouched);
-    c.rowslot = reinterpret_cast<int *>(smem + sh.off_rowslot);
-    c.colvar = reinterpret_cast<int *>(smem + sh.off_colvar);
-    c.colslot = reinterpret_cast<int *>(smem + sh.off_colslot);
-    c.varpos = reinterpret_cast<int *>(smem + sh.off_varpos);
-    c.basis0 = reinterpret_cast<unsigned *>(smem + sh.off_basis0);
-    c.redvar = reinterpret_cast<int *>(smem + sh.off_redvar);
-    c.redu32 = reinterpret_cast<unsigned *>(smem + sh.off_redu32);
-    c.misc = reinterpret_cast<int *>(smem + sh.off_misc);
-    c.tab_i = reinterpret_cast<tab_t *>(smem + sh.off_tab_i);
-    c.tab_d = reinterpret_cast<tab_t *>(smem + sh.off_tab_d);
-    c.tab_s = reinterpret_cast<tab_t *>(smem + sh.off_tab_s);
-    c.n = n;
-    c.m = m;
-    c.S = S;
-    c.cx = sh.cx;
-    c.rpg = sh.rpg;
-    c.tol = a.tol;
-    c.timing = a.timing;
-    const double tol = a.tol;
-    const int nfc = sh.nfc;
-    {
-        const int ry = tid / sh.cx;
-        c.cxi = tid - ry * sh.cx;
-        c.row0 = ry * sh.rpg;
-        c.row1 = min(c.row0 + sh.rpg, (nphys + kRowChunk - 1) / kRowChunk * kRowChunk);
-        if (ry >= sh.groups) c.row1 = c.row0;  // leftover threads (256 - groups*cx) have no block
-    }
-
-    for (;;) {
-        // ---- next problem off the device work queue ----
-        __syncthreads();
-        if (tid == 0) c.misc[MI_LP] = (int)atomicAdd(a.work_counter, 1u);
-        __syncthreads();
-        const int lp = c.misc[MI_LP];
-        if (lp >= a.B) break;
-        if (tid >= kSweepThreads) {
-            // The 9th warp pulls the inputs of problem lp + gridDim.x into L2: with the queue
-            // handing out indices in order, that is the problem some CTA (usually this one) sets
-            // up one solve from now, which then reads A at L2 rather than HBM latency.
-            const long long nxt = (long long)lp + gridDim.x;
-            if (nxt < a.B) {
-                const char *pa = reinterpret_cast<const char *>(a.A + (size_t)nxt * n * m);
-                const size_t bytes = (size_t)n * m * 8;
-                for (size_t o = (size_t)(tid - kSweepThreads) * 128; o < bytes; o += 32 * 128)
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pa + o));
-            }
-        }
-        const double *gA = a.A + (size_t)lp * n * m;
-        const double *gb = a.b + (size_t)lp * n;
-        const double *gc = a.c + (size_t)lp * m;
-        int32_t *log = a.pivot_log ? a.pivot_log + (size_t)lp * a.log_cap * 2 : nullptr;
-
-        // ---- min_constant, idx = min_index(b): zeros count as +inf, first minimum wins (:591) ----
-        if (tid < kSweepThreads) {
-            unsigned long long key = kKeyNone;
-            int idx = 0x7fffffff;
-            for (int i = tid; i < n; i += kSweepThreads) {
-                const double bi = gb[i];
-                const unsigned long long k = order_key(bi != 0.0 ? bi : CUDART_INF);
-                if (k < key || (k == key && i < idx)) {
-                    key = k;
-                    idx = i;
-                }
-            }
-            warp_argmin(key, idx);
-            if ((tid & 31) == 0) {
-                c.redkey[tid >> 5] = key;
-                c.redvar[tid >> 5] = idx;
-            }
-        }
-        __syncthreads();
-        int idx0 = c.redvar[0];
-        {
-            unsigned long long key = c.redkey[0];
-#pragma unroll
-            for (int w = 1; w < kSweepWarps; ++w) {
-                const unsigned long long k = c.redkey[w];
-                const int v = c.redvar[w];
-                if (k < key || (k == key && v < idx0)) {
-                    key = k;
-                    idx0 = v;
-                }
-            }
-        }
-        const double min_c = gb[idx0];
-        const bool phase1 = (min_c < 0.0);
-        int status = 0;
-        int npiv = 0;
-        int ncols = phase1 ? m + 1 : m;
-        if (!phase1 && !(min_c > tol)) status = LPB200_STATUS_REF_ATTRIBUTE_ERROR;  // :626
-        c.track_dep = phase1;
-        c.spare = n + 1;
-
-        if (status == 0) {
-            // ---- SlackForm.__init__ (:230-302) (+ the x_aux column of :632-660 in phase 1) ----
-            if (tid < kSweepThreads) {
-                const int warp = tid >> 5, lane = tid & 31;
-                if ((m & 1) == 0 && ((reinterpret_cast<uintptr_t>(gA) & 15) == 0)) {
-                    // A as a flat stream of 128-bit loads, four in flight per thread; element pairs
-                    // never straddle a row because m is even
-                    const double2 *g2 = reinterpret_cast<const double2 *>(gA);
-                    const int total = (n * m) >> 1, hm = m >> 1;
-                    for (int base = tid; base < total; base += 4 * kSweepThreads) {
-                        double2 v[4];
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            const int idx = base + u * kSweepThreads;
-                            if (idx < total) v[u] = __ldcs(g2 + idx);
-                        }
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            const int idx = base + u * kSweepThreads;
-                            if (idx < total) {
-                                const int i = idx / hm, j = (idx - i * hm) * 2;
-                                double *Ti = c.T + (size_t)i * S + 1 + j;
-                                Ti[0] = -v[u].x;
-                                Ti[1] = -v[u].y;
-                            }
-                        }
-                    }
-                } else {
-                    for (int i = warp; i < n; i += kSweepWarps) {
-                        double *Ti = c.T + (size_t)i * S;
-                        const double *Ai = gA + (size_t)i * m;
-                        for (int j = lane; j < m; j += 32) Ti[1 + j] = -Ai[j];
-                    }
-                }
-                for (int i = tid; i < n; i += kSweepThreads) {
-                    double *Ti = c.T + (size_t)i * S;
-                    Ti[0] = gb[i];
-                    Ti[1 + m] = phase1 ? 1.0 : 0.0;  // -(-1), :659 then :262
-                    for (int k = m + 2; k < S; ++k) Ti[k] = 0.0;
-                }
-                double *obj = c.T + (size_t)n * S;
-                for (int k = tid; k < S; k += kSweepThreads) {
-                    double v = 0.0;
-                    if (k >= 1 && k <= m) v = phase1 ? 0.0 : gc[k - 1];
-                    if (k == 1 + m && phase1) v = -1.0;  // objective -x_aux (:644-645)
-                    obj[k] = v;
-                    obj[S + k] = 0.0;  // the spare slot
-                    c.nr[k] = 0.0;
-                }
-                for (int i = tid; i < nfc; i += kSweepThreads) c.fc[i] = 0.0;
-                for (int i = tid; i < nphys; i += kSweepThreads) {
-                    c.rowvar[i] = (i < n) ? i : -1;
-                    c.nonecol[i] = kNoneInitial;
-                    c.untouched[i] = 0;
-                    c.rowslot[i] = i & (sh.size_d0 - 1);
-                    if (i < n) c.varpos[i] = ~i;
-                }
-                const int isize = phase1 ? sh.size_i1 : sh.size_i0;
-                for (int k = tid; k <= m; k += kSweepThreads) {
-                    c.colvar[k] = n + k;
-                    c.varpos[n + k] = k;
-                    c.colslot[k] = (n + k) & (isize - 1);
-                }
-                for (int w = tid; w < (nv + 31) / 32; w += kSweepThreads) c.basis0[w] = 0u;
-            } else {
-                // set(range(n, n+ncols)) and set(range(0, n)) (:289-292), built by the 9th warp
-                const int lane = tid - kSweepThreads;
-                const int isize = phase1 ? sh.size_i1 : sh.size_i0;
-                for (int s = lane; s < isize; s += 32) c.tab_i[s] = (tab_t)kSetUnused;
-                __syncwarp();
-                for (int k = n + lane; k < n + ncols; k += 32) c.tab_i[k & (isize - 1)] = (tab_t)k;
-                if (phase1) {
-                    for (int s = lane; s < sh.size_d0; s += 32) c.tab_d[s] = (tab_t)kSetUnused;
-                    __syncwarp();
-                    for (int k = lane; k < n; k += 32) c.tab_d[k & (sh.size_d0 - 1)] = (tab_t)k;
-                }
-                if (lane == 0) {
-                    c.misc[MI_ISIZE] = isize;
-                    c.misc[MI_IFILL] = ncols;
-                    c.misc[MI_IUSED] = ncols;
-                    c.misc[MI_DSIZE] = sh.size_d0;
-                    c.misc[MI_DFILL] = n;
-                    c.misc[MI_DUSED] = n;
-                    c.redu32[kSweepWarps + 1] = 0u;
-                    c.redu32[kSweepWarps + 2] = 0xffffffffu;
-                    c.redu32[kSweepWarps + 3] = 0xffffffffu;
-                }
-            }
-            __syncthreads();
-
-            // One instance of the pivot loop serves phase 1 (:526, entered through the forced
-            // pivot), phase 2 after it (:599) and phase 2 alone (:619).
-            int forced_row = phase1 ? idx0 : -1;
-            for (;;) {
-                status = run_loop(c, ncols, npiv, a.max_pivots, log, a.log_cap, forced_row);
-                if (forced_row < 0) break;  // phase 2 is done
-                forced_row = -1;
-                const int aux = n + m;
-                if (status == 0) {
-                    if (!(fabs(c.T[(size_t)n * S]) <= tol)) status = LPB200_STATUS_NO_SOLUTION;  // :528-530
-                    else if (c.varpos[aux] < 0) status = LPB200_STATUS_REF_INDEX_ERROR;  // :541 -> :183
-                }
-                if (status != 0) break;
-                {
-                    // ---- rebuild the original objective (:537-541) ----
-                    // basic ORIGINAL variables in iteration order of the `dependent` set
-                    // (slack rows have objective coefficient None: skipped, :203)
-                    int *list = reinterpret_cast<int *>(c.fc);
-                    if (tid < 32) {
-                        const int dsize = c.misc[MI_DSIZE];
-                        int cnt = 0;
-                        for (int s0 = 0; s0 < dsize; s0 += 32) {
-                            const int s = s0 + tid;
-                            const int v = (s < dsize) ? (int)c.tab_d[s] : -1;
-                            const unsigned msk = __ballot_sync(0xffffffffu, v >= n);
-                            if (v >= n) list[cnt + __popc(msk & ((1u << tid) - 1u))] = v;
-                            cnt += __popc(msk);
-                        }
-                        if (tid == 0) c.misc[MI_NLIST] = cnt;
-                    }
-                    // stage c in nr[], start from (v, c) = (0, [None]*n + float(c)) (:516, :537)
-                    if (tid < kSweepThreads) {
-                        for (int j = tid; j < m; j += kSweepThreads) c.nr[j] = gc[j];
-                    }
-                    __syncthreads();
-                    const int kaux = c.varpos[aux];
-                    if (tid < kSweepThreads) {
-                        double *obj = c.T + (size_t)n * S;
-                        const int nlist = c.misc[MI_NLIST];
-                        for (int k = tid; k < 1 + ncols; k += kSweepThreads) {
-                            if (k == 1 + kaux) continue;  // zip() truncates the x_aux column (:190)
-                            double o = 0.0;
-                            if (k >= 1) {
-                                const int w = c.colvar[k - 1];
-                                o = (w >= n) ? c.nr[w - n] : 0.0;
-                            }
-                            for (int t = 0; t < nlist; ++t) {
-                                const int v = list[t];
-                                const double f = c.nr[v - n];
-                                if (fabs(f) <= tol) continue;
-                                o = axpy_snap(o, f, c.T[(size_t)(~c.varpos[v]) * S + k], tol);
-                            }
-                            obj[k] = o;
-                        }
-                    }
-                    __syncthreads();
-                    // ---- clean-up (:547-575): None out basic columns, drop x_aux, same sets live on ----
-                    const int last = ncols - 1;
-                    if (tid < kSweepThreads) {
-                        for (int w = tid; w < (nv + 31) / 32; w += kSweepThreads) {
-                            unsigned bits = 0u;
-                            for (int bb = 0; bb < 32; ++bb) {
-                                const int v = w * 32 + bb;
-                                if (v < nv && c.varpos[v] < 0) bits |= 1u << bb;
-                            }
-                            c.basis0[w] = bits;
-                        }
-                        for (int i = tid; i < nphys; i += kSweepThreads) c.untouched[i] = 1;
-                        for (int i = tid; i < nphys; i += kSweepThreads) {
-                            double *Ti = c.T + (size_t)i * S;
-                            if (kaux != last) Ti[1 + kaux] = Ti[1 + last];
-                            Ti[1 + last] = 0.0;
-                        }
-                        for (int k = tid; k < S; k += kSweepThreads) c.nr[k] = 0.0;
-                        for (int i = tid; i < nfc; i += kSweepThreads) c.fc[i] = 0.0;  // list[] lived here
-                    } else if (tid == kSweepThreads) {
-                        PySet s = {c.misc[MI_ISIZE], c.misc[MI_IFILL], c.misc[MI_IUSED]};
-                        pyset_remove_slot(c.tab_i, s, c.colslot[kaux]);  // independent.remove(nvars) (:574)
-                        c.misc[MI_IUSED] = s.used;
-                        if (kaux != last) {
-                            const int w = c.colvar[last];
-                            c.colvar[kaux] = w;
-                            c.colslot[kaux] = c.colslot[last];
-                            c.varpos[w] = kaux;
-                        }
-                    }
-                    ncols = m;
-                    __syncthreads();
-                }
-            }
-        }
-
-        // ---- results (:473-491, 603, 622) ----
-        if (tid < kSweepThreads) {
-            double *gx = a.x + (size_t)lp * m;
-            for (int j = tid; j < m; j += kSweepThreads) {
-                double v = 0.0;
-                if (status == 0) {
-                    const int pos = c.varpos[n + j];
-                    if (pos < 0) v = c.T[(size_t)(~pos) * S];
-                }
-                gx[j] = v;
-            }
-            if (tid == 0) {
-                a.status[lp] = status;
-                a.npivots[lp] = npiv;
-                a.objective[lp] = (status == 0) ? c.T[(size_t)n * S] : 0.0;
-            }
-        }
-    }
-}
-
-}  // namespace lpb
 
 // ======================================================================================
 // Host side: C ABI
@@ -847,7 +82,21 @@ static int check_batch_args(int B, int n, int m, double tol, int max_pivots, int
 extern "C" int64_t lpb200_simplex_batch_smem_bytes(int n, int m)
 {
     if (n < 1 || m < 1 || n + m + 1 >= 32000) return INT64_MAX;
-    return (int64_t)make_batch_shape(n, m).bytes;
+    return (int64_t)smem8::make_batch_shape(n, m).bytes;
+}
+
+// Which kernel variant serves a shape: the register-resident one when it is eligible (one
+// column-pair pass, at most LPB_REG_ROWS rows per thread) and fits, else the shared-memory one.
+// LPB_BATCH_KERNEL=smem|reg overrides the choice (A/B measurements, tests).
+// The shared-memory kernel is the product path.  The register-resident variant is bit-exact but
+// slower on B200 (32 M vs 81 M pivots/s on Config 4 D2: with one CTA per SM nothing overlaps the
+// serial stage/ratio chain); LPB_BATCH_KERNEL=reg selects it for experiments.
+static int pick_variant(int n, int m, const DeviceInfo &di)
+{
+    const char *force = getenv("LPB_BATCH_KERNEL");
+    if (force && force[0] == 'r')
+        return reg15::eligible(n, m) && reg15::make_batch_shape(n, m).bytes <= di.max_smem_optin ? 1 : 0;
+    return 0;
 }
 
 extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A, const double *b,
@@ -862,59 +111,11 @@ extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A,
     DeviceInfo di;
     rc = get_device_info(&di);
     if (rc) return rc;
-    const BatchShape sh = make_batch_shape(n, m);
-    if (sh.bytes > di.max_smem_optin) {
-        set_error("lpb200_simplex_batch: tableau does not fit shared memory (" + std::to_string(sh.bytes) +
-                  " > " + std::to_string(di.max_smem_optin) + " bytes); use lpb200_simplex_single");
-        return LPB200_E_TOO_LARGE;
-    }
-    int dyn_smem = sh.bytes;
-    if (const char *g = getenv("LPB_DEBUG_PAD")) dyn_smem += atoi(g);
-    LPB_CUDA(cudaFuncSetAttribute(simplex_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
-    int per_sm = 0;
-    LPB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_batched_kernel, kThreads, dyn_smem));
-    if (per_sm < 1) per_sm = 1;
-    long long grid = (long long)di.sm_count * per_sm;
-    if (const char *g = getenv("LPB_DEBUG_GRID")) grid = atoi(g);
-    if (grid > B) grid = B;
-    unsigned int *counter = nullptr;
-    LPB_CUDA(cudaMallocAsync((void **)&counter, sizeof(unsigned int), stream));
-    LPB_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned int), stream));
-    BatchArgs a;
-    a.B = B;
-    a.A = A;
-    a.b = b;
-    a.c = c;
-    a.tol = tol;
-    a.max_pivots = max_pivots;
-    a.status = status;
-    a.x = x;
-    a.objective = objective;
-    a.npivots = npivots;
-    a.pivot_log = pivot_log;
-    a.log_cap = log_cap;
-    a.work_counter = counter;
-    a.timing = nullptr;
-    const bool dbg_timing = getenv("LPB_DEBUG_TIMING") != nullptr;
-    if (dbg_timing) {
-        LPB_CUDA(cudaMalloc((void **)&a.timing, 32 * 4 * 8));
-        LPB_CUDA(cudaMemset(a.timing, 0, 32 * 4 * 8));
-    }
-    simplex_batched_kernel<<<(unsigned)grid, kThreads, dyn_smem, stream>>>(sh, a);
-    LPB_CUDA(cudaGetLastError());
-    LPB_CUDA(cudaFreeAsync(counter, stream));
-    if (dbg_timing) {  // debug only: synchronises
-        unsigned long long h[32 * 4];
-        LPB_CUDA(cudaStreamSynchronize(stream));
-        LPB_CUDA(cudaMemcpy(h, a.timing, sizeof(h), cudaMemcpyDeviceToHost));
-        for (int w = 0; w <= kSweepWarps; ++w)
-            if (h[w * 4 + 3])
-                fprintf(stderr, "[lpb timing] warp %d: stage+bar %.0f  own sweep %.0f  sweep+bar %.0f cycles/pivot (%llu pivots)\n",
-                        w, (double)h[w * 4] / h[w * 4 + 3], (double)h[w * 4 + 1] / h[w * 4 + 3],
-                        (double)h[w * 4 + 2] / h[w * 4 + 3], h[w * 4 + 3]);
-        cudaFree(a.timing);
-    }
-    return 0;
+    if (pick_variant(n, m, di) == 1)
+        return reg15::launch(di, B, n, m, A, b, c, tol, max_pivots, status, x, objective, npivots, pivot_log,
+                             log_cap, stream);
+    return smem8::launch(di, B, n, m, A, b, c, tol, max_pivots, status, x, objective, npivots, pivot_log, log_cap,
+                         stream);
 }
 
 // Host-pointer entry point: the batch is cut into chunks that are copied in, solved and
