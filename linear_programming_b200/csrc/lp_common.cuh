@@ -32,6 +32,37 @@ __device__ __forceinline__ double pivot_inverse(double piv, double tol)
     return snap(-__ddiv_rn(1.0, piv), tol);
 }
 
+// Typed constraint matrices (include/lp_b200.h LPB200_DTYPE_*): element k, or elements 4q..4q+3
+// with one streaming load (base + 4q elements must be aligned to four elements), widened to
+// fp64 -- exact for every supported type.  Dtype codes are spelled out to keep this header free
+// of the public one: F32 = 1, I32 = 2, I16 = 3, I8 = 4.
+__device__ __forceinline__ double load_typed1(const char *base, int dtype, size_t k)
+{
+    switch (dtype) {
+    case 1: return (double)__ldcs(reinterpret_cast<const float *>(base) + k);
+    case 2: return (double)__ldcs(reinterpret_cast<const int *>(base) + k);
+    case 3: return (double)__ldcs(reinterpret_cast<const short *>(base) + k);
+    default: return (double)__ldcs(reinterpret_cast<const signed char *>(base) + k);
+    }
+}
+
+__device__ __forceinline__ void load_typed4(const char *base, int dtype, size_t q, double v[4])
+{
+    if (dtype == 1) {
+        const float4 t = __ldcs(reinterpret_cast<const float4 *>(base) + q);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else if (dtype == 2) {
+        const int4 t = __ldcs(reinterpret_cast<const int4 *>(base) + q);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else if (dtype == 3) {
+        const short4 t = __ldcs(reinterpret_cast<const short4 *>(base) + q);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else {
+        const char4 t = __ldcs(reinterpret_cast<const char4 *>(base) + q);
+        v[0] = (signed char)t.x; v[1] = (signed char)t.y; v[2] = (signed char)t.z; v[3] = (signed char)t.w;
+    }
+}
+
 // order-preserving map double -> uint64 (no NaNs expected; -0.0 never reaches here: snapped)
 __device__ __forceinline__ unsigned long long order_key(double v)
 {

@@ -43,6 +43,19 @@ inline int pyset_capacity(int cnt)
     return ns > init ? ns : init;
 }
 
+// Bytes per element of an LPB200_DTYPE_* code; 0 = not a dtype.
+inline int dtype_bytes(int dtype)
+{
+    switch (dtype) {
+    case LPB200_DTYPE_F64: return 8;
+    case LPB200_DTYPE_F32: return 4;
+    case LPB200_DTYPE_I32: return 4;
+    case LPB200_DTYPE_I16: return 2;
+    case LPB200_DTYPE_I8: return 1;
+    default: return 0;
+    }
+}
+
 struct DeviceInfo {
     int device;
     int sm_count;

@@ -99,47 +99,106 @@ static int pick_variant(int n, int m, const DeviceInfo &di)
     return 0;
 }
 
-extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A, const double *b,
-                                           const double *c, double tol, int max_pivots, int32_t *status,
-                                           double *x, double *objective, int32_t *npivots,
-                                           int32_t *pivot_log, int log_cap, void *stream_v)
+extern "C" int lpb200_simplex_batch_typed_device(int B, int n, int m, const void *A, int a_dtype,
+                                                 const double *b, const double *c, double tol, int max_pivots,
+                                                 int32_t *status, double *x, double *objective,
+                                                 int32_t *npivots, int32_t *pivot_log, int log_cap,
+                                                 void *stream_v)
 {
     int rc = check_batch_args(B, n, m, tol, max_pivots, log_cap);
     if (rc) return rc;
+    if (dtype_bytes(a_dtype) == 0) {
+        set_error("lpb200_simplex_batch: a_dtype must be one of LPB200_DTYPE_*");
+        return LPB200_E_INVALID;
+    }
     if (B == 0) return 0;
     cudaStream_t stream = (cudaStream_t)stream_v;
     DeviceInfo di;
     rc = get_device_info(&di);
     if (rc) return rc;
     if (pick_variant(n, m, di) == 1)
-        return reg15::launch(di, B, n, m, A, b, c, tol, max_pivots, status, x, objective, npivots, pivot_log,
-                             log_cap, stream);
-    return smem8::launch(di, B, n, m, A, b, c, tol, max_pivots, status, x, objective, npivots, pivot_log, log_cap,
-                         stream);
+        return reg15::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots,
+                             pivot_log, log_cap, stream);
+    return smem8::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots, pivot_log,
+                         log_cap, stream);
 }
+
+extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A, const double *b,
+                                           const double *c, double tol, int max_pivots, int32_t *status,
+                                           double *x, double *objective, int32_t *npivots,
+                                           int32_t *pivot_log, int log_cap, void *stream_v)
+{
+    return lpb200_simplex_batch_typed_device(B, n, m, A, LPB200_DTYPE_F64, b, c, tol, max_pivots, status, x,
+                                             objective, npivots, pivot_log, log_cap, stream_v);
+}
+
+// Device scratch of the host-pointer entry point: two buffer sets and two streams, owned by the
+// calling thread and kept between calls (cudaMalloc/cudaFree of ~200 MB cost more than solving a
+// few thousand LPs); grown on demand, released when the thread exits.
+struct HostArena {
+    int device = -1;
+    size_t cap = 0;
+    char *mem[2] = {nullptr, nullptr};
+    cudaStream_t stream[2] = {nullptr, nullptr};
+
+    void release()
+    {
+        for (int s = 0; s < 2; ++s) {
+            if (mem[s]) cudaFree(mem[s]);
+            if (stream[s]) cudaStreamDestroy(stream[s]);
+            mem[s] = nullptr;
+            stream[s] = nullptr;
+        }
+        cap = 0;
+        device = -1;
+    }
+    int ensure(int dev, int nset, size_t bytes)
+    {
+        if (dev != device || bytes > cap) {
+            release();
+            device = dev;
+            cap = bytes;
+        }
+        for (int s = 0; s < nset; ++s) {
+            if (!stream[s]) LPB_CUDA(cudaStreamCreateWithFlags(&stream[s], cudaStreamNonBlocking));
+            if (!mem[s]) LPB_CUDA(cudaMalloc((void **)&mem[s], cap));
+        }
+        return 0;
+    }
+    ~HostArena() { release(); }
+};
+static thread_local HostArena g_arena;
 
 // Host-pointer entry point: the batch is cut into chunks that are copied in, solved and
 // copied out on two alternating streams, so the PCIe copy of chunk k+1 overlaps the solve of
 // chunk k and device memory stays bounded (two chunk-sized buffer sets).
-extern "C" int lpb200_simplex_batch(int B, int n, int m, const double *A, const double *b, const double *c,
-                                    double tol, int max_pivots, int32_t *status, double *x,
-                                    double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap)
+extern "C" int lpb200_simplex_batch_typed(int B, int n, int m, const void *A_v, int a_dtype, const double *b,
+                                          const double *c, double tol, int max_pivots, int32_t *status,
+                                          double *x, double *objective, int32_t *npivots, int32_t *pivot_log,
+                                          int log_cap)
 {
     int rc = check_batch_args(B, n, m, tol, max_pivots, log_cap);
     if (rc) return rc;
+    const size_t esz = (size_t)dtype_bytes(a_dtype);
+    if (esz == 0) {
+        set_error("lpb200_simplex_batch: a_dtype must be one of LPB200_DTYPE_*");
+        return LPB200_E_INVALID;
+    }
     if (B == 0) return 0;
+    const char *A = static_cast<const char *>(A_v);
     DeviceInfo di;
     rc = get_device_info(&di);
     if (rc) return rc;
     const size_t lpA = (size_t)n * m, lpb = (size_t)n, lpc = (size_t)m;
     const size_t lplog = pivot_log ? (size_t)log_cap * 2 : 0;
-    const size_t lp_bytes = (lpA + lpb + 2 * lpc + 1) * 8 + 8 + lplog * 4;
+    const size_t lp_bytes = lpA * esz + (lpb + 2 * lpc + 1) * 8 + 8 + lplog * 4;
     long long chunk = (long long)((size_t)(96u << 20) / lp_bytes);  // ~96 MB per chunk
     if (chunk < 1) chunk = 1;
     if (chunk > B) chunk = B;
     const int nset = (chunk < B) ? 2 : 1;
     struct Set {
-        double *A, *b, *c, *x, *obj;
+        char *A;
+        double *b, *c, *x, *obj;
         int32_t *st, *np, *log;
         cudaStream_t stream;
     } set[2] = {};
@@ -149,28 +208,40 @@ extern "C" int lpb200_simplex_batch(int B, int n, int m, const double *A, const 
         cudaError_t _e = (call);                                      \
         if (_e != cudaSuccess && rc == 0) rc = cuda_fail(_e, #call);  \
     } while (0)
+    // one device arena per buffer set, kept by the calling thread between calls (see HostArena)
+    size_t off[9];
+    {
+        const size_t sizes[8] = {(size_t)chunk * lpA * esz, (size_t)chunk * lpb * 8, (size_t)chunk * lpc * 8,
+                                 (size_t)chunk * lpc * 8,   (size_t)chunk * 8,       (size_t)chunk * 4,
+                                 (size_t)chunk * 4,         (size_t)chunk * lplog * 4};
+        off[0] = 0;
+        for (int i = 0; i < 8; ++i) off[i + 1] = off[i] + (sizes[i] + 255) / 256 * 256;
+    }
+    rc = g_arena.ensure(di.device, nset, off[8]);
+    if (rc) return rc;
     for (int s = 0; s < nset; ++s) {
-        LPB_TRY(cudaStreamCreateWithFlags(&set[s].stream, cudaStreamNonBlocking));
-        LPB_TRY(cudaMalloc((void **)&set[s].A, chunk * lpA * 8));
-        LPB_TRY(cudaMalloc((void **)&set[s].b, chunk * lpb * 8));
-        LPB_TRY(cudaMalloc((void **)&set[s].c, chunk * lpc * 8));
-        LPB_TRY(cudaMalloc((void **)&set[s].x, chunk * lpc * 8));
-        LPB_TRY(cudaMalloc((void **)&set[s].obj, chunk * 8));
-        LPB_TRY(cudaMalloc((void **)&set[s].st, chunk * 4));
-        LPB_TRY(cudaMalloc((void **)&set[s].np, chunk * 4));
-        if (lplog) LPB_TRY(cudaMalloc((void **)&set[s].log, chunk * lplog * 4));
+        char *base = g_arena.mem[s];
+        set[s].A = base + off[0];
+        set[s].b = reinterpret_cast<double *>(base + off[1]);
+        set[s].c = reinterpret_cast<double *>(base + off[2]);
+        set[s].x = reinterpret_cast<double *>(base + off[3]);
+        set[s].obj = reinterpret_cast<double *>(base + off[4]);
+        set[s].st = reinterpret_cast<int32_t *>(base + off[5]);
+        set[s].np = reinterpret_cast<int32_t *>(base + off[6]);
+        set[s].log = lplog ? reinterpret_cast<int32_t *>(base + off[7]) : nullptr;
+        set[s].stream = g_arena.stream[s];
     }
     int k = 0;
     for (long long lo = 0; lo < B && rc == 0; lo += chunk, ++k) {
         const long long cnt = (B - lo < chunk) ? (B - lo) : chunk;
         Set &q = set[k % nset];
-        LPB_TRY(cudaMemcpyAsync(q.A, A + lo * lpA, cnt * lpA * 8, cudaMemcpyHostToDevice, q.stream));
+        LPB_TRY(cudaMemcpyAsync(q.A, A + lo * lpA * esz, cnt * lpA * esz, cudaMemcpyHostToDevice, q.stream));
         LPB_TRY(cudaMemcpyAsync(q.b, b + lo * lpb, cnt * lpb * 8, cudaMemcpyHostToDevice, q.stream));
         LPB_TRY(cudaMemcpyAsync(q.c, c + lo * lpc, cnt * lpc * 8, cudaMemcpyHostToDevice, q.stream));
         if (lplog) LPB_TRY(cudaMemsetAsync(q.log, 0xff, cnt * lplog * 4, q.stream));
         if (rc == 0)
-            rc = lpb200_simplex_batch_device((int)cnt, n, m, q.A, q.b, q.c, tol, max_pivots, q.st, q.x, q.obj,
-                                             q.np, q.log, log_cap, q.stream);
+            rc = lpb200_simplex_batch_typed_device((int)cnt, n, m, q.A, a_dtype, q.b, q.c, tol, max_pivots, q.st,
+                                                   q.x, q.obj, q.np, q.log, log_cap, q.stream);
         LPB_TRY(cudaMemcpyAsync(status + lo, q.st, cnt * 4, cudaMemcpyDeviceToHost, q.stream));
         LPB_TRY(cudaMemcpyAsync(x + lo * lpc, q.x, cnt * lpc * 8, cudaMemcpyDeviceToHost, q.stream));
         LPB_TRY(cudaMemcpyAsync(objective + lo, q.obj, cnt * 8, cudaMemcpyDeviceToHost, q.stream));
@@ -185,10 +256,13 @@ extern "C" int lpb200_simplex_batch(int B, int n, int m, const double *A, const 
         }
     }
 #undef LPB_TRY
-    for (int s = 0; s < nset; ++s) {
-        cudaFree(set[s].A); cudaFree(set[s].b); cudaFree(set[s].c); cudaFree(set[s].x); cudaFree(set[s].obj);
-        cudaFree(set[s].st); cudaFree(set[s].np); cudaFree(set[s].log);
-        if (set[s].stream) cudaStreamDestroy(set[s].stream);
-    }
     return rc;
+}
+
+extern "C" int lpb200_simplex_batch(int B, int n, int m, const double *A, const double *b, const double *c,
+                                    double tol, int max_pivots, int32_t *status, double *x,
+                                    double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap)
+{
+    return lpb200_simplex_batch_typed(B, n, m, A, LPB200_DTYPE_F64, b, c, tol, max_pivots, status, x, objective,
+                                      npivots, pivot_log, log_cap);
 }

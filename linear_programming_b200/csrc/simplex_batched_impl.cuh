@@ -89,7 +89,9 @@ static BatchShape make_batch_shape(int n, int m)
 
 struct BatchArgs {
     int B;
-    const double *A, *b, *c;
+    const void *A;  // [B][n][m] elements of a_dtype (LPB200_DTYPE_*), a_esz bytes each
+    int a_dtype, a_esz;
+    const double *b, *c;
     double tol;
     int max_pivots;
     int32_t *status;
@@ -715,6 +717,79 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
 }
 #endif  // LPB_REG_ROWS
 
+// -A into the tableau body (SlackForm.__init__, simplex.py:262: A'[i][n+j] = -A[i][j]).  Kept out
+// of line: the pivot loop's register allocation should not depend on this once-per-LP code.
+#ifndef LPB_SETUP_ATTR
+#define LPB_SETUP_ATTR __noinline__
+#endif
+__device__ LPB_SETUP_ATTR void load_constraints(double *T, int S, const char *gAraw, int a_dtype, int a_esz,
+                                                int n, int m)
+{
+    const int tid = threadIdx.x;
+    const double *gA = reinterpret_cast<const double *>(gAraw);  // valid when a_dtype is F64
+    const int warp = tid >> 5, lane = tid & 31;
+    if (a_dtype != LPB200_DTYPE_F64) {
+        // typed A: widened to fp64 here, exactly (ints and float32 are subsets of fp64)
+        if ((m & 3) == 0 && ((reinterpret_cast<uintptr_t>(gAraw) & (uintptr_t)(4 * a_esz - 1)) == 0)) {
+            // four consecutive elements per load (never straddling a row), four loads in flight
+            const int total = (n * m) >> 2, qm = m >> 2;
+            for (int base = tid; base < total; base += 4 * kSweepThreads) {
+                double v[4][4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int idx = base + u * kSweepThreads;
+                    if (idx < total) load_typed4(gAraw, a_dtype, idx, v[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int idx = base + u * kSweepThreads;
+                    if (idx < total) {
+                        const int i = idx / qm, j = (idx - i * qm) * 4;
+                        double *Ti = T + (size_t)i * S + 1 + j;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) Ti[q] = -v[u][q];
+                    }
+                }
+            }
+        } else {
+            for (int i = warp; i < n; i += kSweepWarps) {
+                double *Ti = T + (size_t)i * S;
+                for (int j = lane; j < m; j += 32)
+                    Ti[1 + j] = -load_typed1(gAraw, a_dtype, (size_t)i * m + j);
+            }
+        }
+    } else if ((m & 1) == 0 && ((reinterpret_cast<uintptr_t>(gA) & 15) == 0)) {
+        // A as a flat stream of 128-bit loads, four in flight per thread; element pairs
+        // never straddle a row because m is even
+        const double2 *g2 = reinterpret_cast<const double2 *>(gA);
+        const int total = (n * m) >> 1, hm = m >> 1;
+        for (int base = tid; base < total; base += 4 * kSweepThreads) {
+            double2 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int idx = base + u * kSweepThreads;
+                if (idx < total) v[u] = __ldcs(g2 + idx);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int idx = base + u * kSweepThreads;
+                if (idx < total) {
+                    const int i = idx / hm, j = (idx - i * hm) * 2;
+                    double *Ti = T + (size_t)i * S + 1 + j;
+                    Ti[0] = -v[u].x;
+                    Ti[1] = -v[u].y;
+                }
+            }
+        }
+    } else {
+        for (int i = warp; i < n; i += kSweepWarps) {
+            double *Ti = T + (size_t)i * S;
+            const double *Ai = gA + (size_t)i * m;
+            for (int j = lane; j < m; j += 32) Ti[1 + j] = -Ai[j];
+        }
+    }
+}
+
 #if LPB_REG_ROWS > 0
 // 16 warps (15 sweep + 1 bookkeeping) x 128 registers = the SM's whole register file: one CTA per
 // SM, the tableau block of every thread (2 x LPB_REG_ROWS doubles) stays in registers
@@ -786,13 +861,13 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
             // up one solve from now, which then reads A at L2 rather than HBM latency.
             const long long nxt = (long long)lp + gridDim.x;
             if (nxt < a.B) {
-                const char *pa = reinterpret_cast<const char *>(a.A + (size_t)nxt * n * m);
-                const size_t bytes = (size_t)n * m * 8;
+                const size_t bytes = (size_t)n * m * a.a_esz;
+                const char *pa = reinterpret_cast<const char *>(a.A) + (size_t)nxt * bytes;
                 for (size_t o = (size_t)(tid - kSweepThreads) * 128; o < bytes; o += 32 * 128)
                     asm volatile("prefetch.global.L2 [%0];" ::"l"(pa + o));
             }
         }
-        const double *gA = a.A + (size_t)lp * n * m;
+        const char *gAraw = reinterpret_cast<const char *>(a.A) + (size_t)lp * n * m * a.a_esz;
         const double *gb = a.b + (size_t)lp * n;
         const double *gc = a.c + (size_t)lp * m;
         int32_t *log = a.pivot_log ? a.pivot_log + (size_t)lp * a.log_cap * 2 : nullptr;
@@ -841,37 +916,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
         if (status == 0) {
             // ---- SlackForm.__init__ (:230-302) (+ the x_aux column of :632-660 in phase 1) ----
             if (tid < kSweepThreads) {
-                const int warp = tid >> 5, lane = tid & 31;
-                if ((m & 1) == 0 && ((reinterpret_cast<uintptr_t>(gA) & 15) == 0)) {
-                    // A as a flat stream of 128-bit loads, four in flight per thread; element pairs
-                    // never straddle a row because m is even
-                    const double2 *g2 = reinterpret_cast<const double2 *>(gA);
-                    const int total = (n * m) >> 1, hm = m >> 1;
-                    for (int base = tid; base < total; base += 4 * kSweepThreads) {
-                        double2 v[4];
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            const int idx = base + u * kSweepThreads;
-                            if (idx < total) v[u] = __ldcs(g2 + idx);
-                        }
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            const int idx = base + u * kSweepThreads;
-                            if (idx < total) {
-                                const int i = idx / hm, j = (idx - i * hm) * 2;
-                                double *Ti = c.T + (size_t)i * S + 1 + j;
-                                Ti[0] = -v[u].x;
-                                Ti[1] = -v[u].y;
-                            }
-                        }
-                    }
-                } else {
-                    for (int i = warp; i < n; i += kSweepWarps) {
-                        double *Ti = c.T + (size_t)i * S;
-                        const double *Ai = gA + (size_t)i * m;
-                        for (int j = lane; j < m; j += 32) Ti[1 + j] = -Ai[j];
-                    }
-                }
+                load_constraints(c.T, S, gAraw, a.a_dtype, a.a_esz, n, m);
                 for (int i = tid; i < n; i += kSweepThreads) {
                     double *Ti = c.T + (size_t)i * S;
                     Ti[0] = gb[i];
@@ -1040,7 +1085,8 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
 
 
 // ---- host side of this variant ----
-static int launch(const DeviceInfo &di, int B, int n, int m, const double *A, const double *b, const double *c,
+static int launch(const DeviceInfo &di, int B, int n, int m, const void *A, int a_dtype, const double *b,
+                  const double *c,
                   double tol, int max_pivots, int32_t *status, double *x, double *objective, int32_t *npivots,
                   int32_t *pivot_log, int log_cap, cudaStream_t stream)
 {
@@ -1065,6 +1111,8 @@ static int launch(const DeviceInfo &di, int B, int n, int m, const double *A, co
     BatchArgs a;
     a.B = B;
     a.A = A;
+    a.a_dtype = a_dtype;
+    a.a_esz = dtype_bytes(a_dtype);
     a.b = b;
     a.c = c;
     a.tol = tol;

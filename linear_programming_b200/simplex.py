@@ -75,19 +75,35 @@ def _vp(arr) -> ctypes.c_void_p:
     return ctypes.c_void_p(arr.ctypes.data)
 
 
+# Element types the batched kernel takes for A (include/lp_b200.h LPB200_DTYPE_*).  The reference
+# parses integers (simplex.py:712-717); an integer or float32 A is widened to fp64 on the GPU,
+# exactly, so the answers are those of the float64 call at 1/8 .. 1/2 of the input bytes.
+DTYPE_F64, DTYPE_F32, DTYPE_I32, DTYPE_I16, DTYPE_I8 = 0, 1, 2, 3, 4
+_TYPED_A = {"float64": DTYPE_F64, "float32": DTYPE_F32, "int32": DTYPE_I32, "int16": DTYPE_I16, "int8": DTYPE_I8}
+
+
+def _a_dtype_code(dtype) -> int | None:
+    """LPB200_DTYPE_* of a numpy / torch dtype, None when A has to be converted to float64."""
+    return _TYPED_A.get(str(dtype).replace("torch.", ""))
+
+
 def solve_batch(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None = None,
                 log_cap: int = 0, mode: str = "auto") -> BatchResult:
     """Solve B independent LPs  max c.x  s.t. A x <= b, x >= 0  with the reference's semantics.
 
     A[B,n,m], b[B,n], c[B,m]: numpy / nested lists (host path: copies in and out) or CUDA
     float64 torch tensors (zero-copy, enqueued on the current stream, results stay on the GPU).
+    A may also be int8 / int16 / int32 / float32 (numpy array or CUDA tensor): the batch kernel
+    reads it as is and widens on the GPU -- same answers, a fraction of the bytes over PCIe.
     mode: "batch" (one CTA per LP, tableau in shared memory), "single" (grid-wide kernel, one
     LP after the other), "auto" (batch when the tableau fits shared memory).
     """
     L = _lib.lib()
     if _is_torch_cuda(A):
         return _solve_batch_torch(L, A, b, c, tol, max_pivots, log_cap, mode)
-    A = np.ascontiguousarray(A, dtype=np.float64)
+    a_code = _a_dtype_code(getattr(A, "dtype", None))
+    A = np.ascontiguousarray(A) if a_code is not None else np.ascontiguousarray(A, dtype=np.float64)
+    a_code = a_code or DTYPE_F64
     b = np.ascontiguousarray(b, dtype=np.float64)
     c = np.ascontiguousarray(c, dtype=np.float64)
     if A.ndim != 3 or b.ndim != 2 or c.ndim != 2:
@@ -105,10 +121,12 @@ def solve_batch(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None 
     if mode == "auto":
         mode = "batch" if fits_batch_kernel(n, m) else "single"
     if mode == "batch":
-        _lib.check(L.lpb200_simplex_batch(B, n, m, _vp(A), _vp(b), _vp(c), tol, max_pivots, _vp(status),
-                                          _vp(x), _vp(obj), _vp(npiv),
-                                          _vp(log) if log is not None else None, log_cap))
+        _lib.check(L.lpb200_simplex_batch_typed(B, n, m, _vp(A), a_code, _vp(b), _vp(c), tol, max_pivots,
+                                                _vp(status), _vp(x), _vp(obj), _vp(npiv),
+                                                _vp(log) if log is not None else None, log_cap))
     elif mode == "single":
+        if a_code != DTYPE_F64:
+            A = A.astype(np.float64)
         for p in range(B):
             lp = log[p] if log is not None else None
             _lib.check(L.lpb200_simplex_single(n, m, _vp(A[p]), _vp(b[p]), _vp(c[p]), tol, max_pivots,
@@ -122,9 +140,12 @@ def solve_batch(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None 
 
 def _solve_batch_torch(L, A, b, c, tol, max_pivots, log_cap, mode):
     import torch
-    for t in (A, b, c):
+    a_code = _a_dtype_code(A.dtype)
+    if a_code is None or not A.is_contiguous():
+        raise ValueError("CUDA A must be a contiguous float64/float32/int32/int16/int8 tensor")
+    for t in (b, c):
         if not (_is_torch_cuda(t) and t.dtype == torch.float64 and t.is_contiguous() and t.device == A.device):
-            raise ValueError("CUDA inputs must be contiguous float64 tensors on one device")
+            raise ValueError("CUDA b and c must be contiguous float64 tensors on the device of A")
     B, n, m = A.shape
     if tuple(b.shape) != (B, n) or tuple(c.shape) != (B, m):
         raise ValueError("shape mismatch")
@@ -142,10 +163,13 @@ def _solve_batch_torch(L, A, b, c, tol, max_pivots, log_cap, mode):
         if mode == "auto":
             mode = "batch" if fits_batch_kernel(n, m) else "single"
         if mode == "batch":
-            _lib.check(L.lpb200_simplex_batch_device(B, n, m, A.data_ptr(), b.data_ptr(), c.data_ptr(), tol,
-                                                     max_pivots, status.data_ptr(), x.data_ptr(),
-                                                     obj.data_ptr(), npiv.data_ptr(), logp, log_cap, stream))
+            _lib.check(L.lpb200_simplex_batch_typed_device(B, n, m, A.data_ptr(), a_code, b.data_ptr(),
+                                                           c.data_ptr(), tol, max_pivots, status.data_ptr(),
+                                                           x.data_ptr(), obj.data_ptr(), npiv.data_ptr(), logp,
+                                                           log_cap, stream))
         elif mode == "single":
+            if a_code != DTYPE_F64:
+                A = A.to(torch.float64)
             wsb = int(L.lpb200_simplex_single_workspace_bytes(n, m))
             ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
             for p in range(B):

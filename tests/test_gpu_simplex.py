@@ -179,3 +179,55 @@ def test_full_gpu_two_ctas_per_sm_vs_oracle(oracle_lib):
             assert np.array_equal(res.npivots, npiv)
             assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
             assert np.array_equal(res.objective.view(np.int64), obj.view(np.int64))
+
+
+@pytest.mark.parametrize("dtype", ["int8", "int16", "int32", "float32"])
+@pytest.mark.parametrize("dist,n,m,count", [("D1", 100, 100, 64), ("D2", 100, 100, 16), ("D2", 37, 61, 48),
+                                            ("D3", 30, 22, 48)])
+def test_typed_constraint_matrix_matches_float64_and_oracle(oracle_lib, dtype, dist, n, m, count):
+    """lpb200_simplex_batch_typed: an integer / float32 A (what a caller that parsed the reference's
+    input with int(), simplex.py:712-717, holds) gives the answers of the float64 call bit for bit
+    -- m % 4 == 0 takes the vector loads, the other shapes the element loads."""
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    A, b, c = workloads.simplex_batch(dist, count, n, m, seed=5)
+    At = A.astype(dtype)
+    assert np.array_equal(At.astype(np.float64), A)  # the distributions are integers in [-100, 100]
+    cap = 20000
+    res = lp.solve_batch(At, b, c, log_cap=0, max_pivots=cap)
+    st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=cap)
+    assert np.array_equal(res.status, st)
+    assert np.array_equal(res.npivots, npiv)
+    assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
+    assert np.array_equal(res.objective.view(np.int64), obj.view(np.int64))
+
+
+def test_typed_device_tensor_and_golden_cases(simplex_golden):
+    """Typed A as a CUDA int16 tensor (zero-copy), and every golden fixture of the reference whose
+    coefficients fit int16 through the typed host call: same status, pivots, x as the fp64 goldens."""
+    import torch
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    A, b, c = workloads.simplex_batch("D1", 200, 100, 100, seed=6)
+    ref = lp.solve_batch(A, b, c)
+    res = lp.solve_batch(torch.from_numpy(A.astype(np.int16)).cuda(), torch.from_numpy(b).cuda(),
+                         torch.from_numpy(c).cuda())
+    torch.cuda.synchronize()
+    assert np.array_equal(res.status.cpu().numpy(), ref.status)
+    assert np.array_equal(res.x.cpu().numpy().view(np.int64), ref.x.view(np.int64))
+    groups = {}
+    for case in simplex_golden["cases"]:
+        Af = _case_arrays(case)[0]
+        if np.array_equal(Af.astype(np.int16).astype(np.float64), Af):
+            groups.setdefault((case["n"], case["m"]), []).append(case)
+    checked = 0
+    for (n, m), cases in sorted(groups.items()):
+        A = np.stack([_case_arrays(k)[0] for k in cases]).astype(np.int16)
+        b = np.stack([_case_arrays(k)[1] for k in cases])
+        c_ = np.stack([_case_arrays(k)[2] for k in cases])
+        cap = max(k["npivots"] for k in cases) + 8
+        res = lp.solve_batch(A, b, c_, log_cap=cap, max_pivots=cap, mode="batch")
+        for p, case in enumerate(cases):
+            _check_against_case(res, p, case)
+            checked += 1
+    assert checked >= 400
