@@ -391,8 +391,8 @@ def ours_arm(args):
         c_np = torch.empty(B, dtype=torch.int32).pin_memory()
 
         def compact_step():
-            _lib.check(L.lpb200_simplex_batch_typed(B, n, m, hA8.data_ptr(), 4, hb.data_ptr(), hc.data_ptr(), tol,
-                                                    cap, c_st.data_ptr(), c_x.data_ptr(), c_obj.data_ptr(),
+            _lib.check(L.lpb200_simplex_batch_ex(B, n, m, hA8.data_ptr(), 4, hb.data_ptr(), hc.data_ptr(), tol,
+                                                 cap, 0, c_st.data_ptr(), c_x.data_ptr(), c_obj.data_ptr(),
                                                     c_np.data_ptr(), None, 0))
         compact_step()
         barrier()
@@ -409,7 +409,7 @@ def ours_arm(args):
                        "h2d_bytes_per_step": int(B * (n * m + (n + m) * 8)),
                        "d2h_bytes_per_step": int(B * (m * 8 + 8 + 4 + 4)), "steps": Ke,
                        "ms_per_step": dtc / Ke * 1e3, "matches_fp64_call": same_c,
-                       "api": "lpb200_simplex_batch_typed (LPB200_DTYPE_I8 A; b, c fp64; host pointers, pinned)"}
+                       "api": "lpb200_simplex_batch_ex (LPB200_DTYPE_I8 A; b, c fp64; host pointers, pinned)"}
         del hA8
 
     # ---- extra: pivot-heavy distribution D2 on a smaller batch (pivots/s), rank 0 only, untimed region ----

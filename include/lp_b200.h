@@ -75,25 +75,38 @@ int lpb200_simplex_batch(int B, int n, int m, const double *A, const double *b, 
                          int32_t *npivots, int32_t *pivot_log, int log_cap);
 
 /*
- * The same two calls with a typed constraint matrix.  The reference reads its input with int()
- * (simplex.py:712-717) and the course bounds the coefficients to |A[i][j]| <= 100, so a caller
- * that parsed a problem holds small integers: handing them over as int8/int16/int32 (or float32)
- * cuts the PCIe/HBM bytes of A, which is 98 % of a problem, by 8x/4x/2x.  Elements are widened
- * to fp64 exactly when the tableau is built (SlackForm.__init__, simplex.py:230-302); from
- * there on everything is bit-identical to the fp64 call on the same values.  b and c stay fp64.
+ * The same two calls, extended: a typed constraint matrix and a choice of pivoting rule.
+ *
+ * a_dtype -- the reference reads its input with int() (simplex.py:712-717) and the course bounds
+ * the coefficients to |A[i][j]| <= 100, so a caller that parsed a problem holds small integers:
+ * handing them over as int8/int16/int32 (or float32) cuts the PCIe/HBM bytes of A, which is 98 %
+ * of a problem, by 8x/4x/2x.  Elements are widened to fp64 exactly when the tableau is built
+ * (SlackForm.__init__, simplex.py:230-302); from there on everything is bit-identical to the
+ * fp64 call on the same values.  b and c stay fp64.
+ *
+ * rule -- LPB200_RULE_REFERENCE is the reference's behaviour, bugs included (this is what every
+ * other entry point does).  LPB200_RULE_BLAND is the corrected mode (NOT
+ * reference behaviour -- the bugs it removes are catalogued in SURVEY Appendix A.8): entering =
+ * lowest variable id with a positive coefficient (Bland, terminates), ratio test that keeps
+ * zero ratios (ties -> lowest id), phase dispatch on the true minimum of b (no AttributeError
+ * class, simplex.py:626), x_aux pivoted out of the basis after phase 1 instead of IndexError
+ * (simplex.py:541), no None-tracking (TypeError, simplex.py:409).  Same tableau arithmetic
+ * (two roundings, snap to zero at tol).  status is then one of 0, -1, 1, 2.
  */
 #define LPB200_DTYPE_F64 0
 #define LPB200_DTYPE_F32 1
 #define LPB200_DTYPE_I32 2
 #define LPB200_DTYPE_I16 3
 #define LPB200_DTYPE_I8 4
-int lpb200_simplex_batch_typed_device(int B, int n, int m, const void *A, int a_dtype, const double *b,
-                                      const double *c, double tol, int max_pivots, int32_t *status,
-                                      double *x, double *objective, int32_t *npivots, int32_t *pivot_log,
-                                      int log_cap, void *stream);
-int lpb200_simplex_batch_typed(int B, int n, int m, const void *A, int a_dtype, const double *b,
-                               const double *c, double tol, int max_pivots, int32_t *status, double *x,
-                               double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap);
+#define LPB200_RULE_REFERENCE 0
+#define LPB200_RULE_BLAND 1
+int lpb200_simplex_batch_ex_device(int B, int n, int m, const void *A, int a_dtype, const double *b,
+                                   const double *c, double tol, int max_pivots, int rule, int32_t *status,
+                                   double *x, double *objective, int32_t *npivots, int32_t *pivot_log,
+                                   int log_cap, void *stream);
+int lpb200_simplex_batch_ex(int B, int n, int m, const void *A, int a_dtype, const double *b, const double *c,
+                            double tol, int max_pivots, int rule, int32_t *status, double *x,
+                            double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap);
 
 /*
  * Single large LP, grid-wide: the condensed tableau lives in HBM and every pivot is one

@@ -28,12 +28,13 @@ SIGNATURES = {
     "lpb200_simplex_batch": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp,
                                             ctypes.c_double, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp,
                                             ctypes.c_int]),
-    "lpb200_simplex_batch_typed_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp,
-                                                         ctypes.c_int, c_vp, c_vp, ctypes.c_double, ctypes.c_int,
-                                                         c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.c_int, c_vp]),
-    "lpb200_simplex_batch_typed": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp, ctypes.c_int,
-                                                  c_vp, c_vp, ctypes.c_double, ctypes.c_int, c_vp, c_vp, c_vp,
-                                                  c_vp, c_vp, ctypes.c_int]),
+    "lpb200_simplex_batch_ex_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp,
+                                                      ctypes.c_int, c_vp, c_vp, ctypes.c_double, ctypes.c_int,
+                                                      ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.c_int,
+                                                      c_vp]),
+    "lpb200_simplex_batch_ex": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp, ctypes.c_int,
+                                               c_vp, c_vp, ctypes.c_double, ctypes.c_int, ctypes.c_int, c_vp,
+                                               c_vp, c_vp, c_vp, c_vp, ctypes.c_int]),
     "lpb200_simplex_single_workspace_bytes": (ctypes.c_int64, [ctypes.c_int, ctypes.c_int]),
     "lpb200_simplex_single_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, ctypes.c_double,
                                                     ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.c_int,

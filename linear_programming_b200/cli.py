@@ -19,6 +19,9 @@ reference process dies prints the exception class name on a line of its own
 ("AttributeError" / "IndexError" / "TypeError", or "IterationLimit") and the stream goes on,
 so `stress.py`-style drivers (week-2/diet/stress.py:30) can pipe a whole run through one
 process instead of one subprocess per LP.
+
+``--rule=bland`` (LP programs only) answers with the corrected mode instead of the reference's
+behaviour (include/lp_b200.h LPB200_RULE_BLAND): no crash classes, Bland's anti-cycling rule.
 """
 from __future__ import annotations
 
@@ -92,9 +95,9 @@ def iter_equations(text: str):
         pos += 1 + need
 
 
-def _solve_lp_batch(A, b, c):
+def _solve_lp_batch(A, b, c, rule="reference"):
     """One shape group on the engine; separated out so CPU tests can substitute the checker."""
-    r = _simplex.solve_batch(A, b, c)
+    r = _simplex.solve_batch(A, b, c, rule=rule)
     return r.status, r.x
 
 
@@ -102,7 +105,7 @@ def _solve_eq_batch(a, b):
     return gauss_jordan.solve_equation_batch(a, b)
 
 
-def solve_lp_stream(text: str, integer: bool) -> str:
+def solve_lp_stream(text: str, integer: bool, rule: str = "reference") -> str:
     problems = list(iter_lp_problems(text, integer))
     groups = {}
     for idx, (n, m, _, _, _) in enumerate(problems):
@@ -112,7 +115,7 @@ def solve_lp_stream(text: str, integer: bool) -> str:
         A = np.stack([problems[i][2] for i in idxs])
         b = np.stack([problems[i][3] for i in idxs])
         c = np.stack([problems[i][4] for i in idxs])
-        status, x = _solve_lp_batch(A, b, c)
+        status, x = _solve_lp_batch(A, b, c, rule) if rule != "reference" else _solve_lp_batch(A, b, c)
         for k, i in enumerate(idxs):
             st = int(status[k])
             if st in (-1, 0, 1):
@@ -144,7 +147,8 @@ def solve_equation_stream(text: str) -> str:
 def main(argv=None) -> int:
     argv = list(sys.argv[1:] if argv is None else argv)
     stream = "--stream" in argv
-    argv = [t for t in argv if t != "--stream"]
+    rule = "bland" if "--rule=bland" in argv else "reference"
+    argv = [t for t in argv if t != "--stream" and not t.startswith("--rule=")]
     prog = argv[0] if argv else "simplex"
     if prog not in ("simplex", "ad_allocation", "diet", "energy_values"):
         sys.stderr.write("unknown program %r\n" % prog)
@@ -154,15 +158,18 @@ def main(argv=None) -> int:
         if prog == "energy_values":
             sys.stdout.write(solve_equation_stream(text))
         else:
-            sys.stdout.write(solve_lp_stream(text, integer=(prog == "simplex")))
+            sys.stdout.write(solve_lp_stream(text, integer=(prog == "simplex"), rule=rule))
         return 0
     if prog == "simplex":
         s = Simplex.parse(sys.stdin)
+        s.rule = rule
         anst, ansx = s.solve()
         sys.stdout.write(format_answer(anst, ansx))
     elif prog in ("ad_allocation", "diet"):
         n, m, A, b, c = parse_lp_floats(sys.stdin.read())
-        anst, ansx = Simplex(A, b, c, n, m).solve()
+        s = Simplex(A, b, c, n, m)
+        s.rule = rule
+        anst, ansx = s.solve()
         sys.stdout.write(format_answer(anst, ansx))
     else:
         a, b = gauss_jordan.read_equation(sys.stdin.read())

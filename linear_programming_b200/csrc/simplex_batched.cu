@@ -44,21 +44,38 @@
 #define LPB_SWEEP_WARPS 8
 #define LPB_REG_ROWS 0
 #define LPB_MIN_BLOCKS 2
+#define LPB_RULE_BLAND 0
 #include "simplex_batched_impl.cuh"
 #undef LPB_NS
 #undef LPB_SWEEP_WARPS
 #undef LPB_REG_ROWS
 #undef LPB_MIN_BLOCKS
+#undef LPB_RULE_BLAND
 
 #define LPB_NS reg15
 #define LPB_SWEEP_WARPS 15
 #define LPB_REG_ROWS 12
 #define LPB_MIN_BLOCKS 1
+#define LPB_RULE_BLAND 0
 #include "simplex_batched_impl.cuh"
 #undef LPB_NS
 #undef LPB_SWEEP_WARPS
 #undef LPB_REG_ROWS
 #undef LPB_MIN_BLOCKS
+#undef LPB_RULE_BLAND
+
+// the corrected (non-reference) mode, LPB200_RULE_BLAND: same kernel, other pivoting decisions
+#define LPB_NS bland8
+#define LPB_SWEEP_WARPS 8
+#define LPB_REG_ROWS 0
+#define LPB_MIN_BLOCKS 2
+#define LPB_RULE_BLAND 1
+#include "simplex_batched_impl.cuh"
+#undef LPB_NS
+#undef LPB_SWEEP_WARPS
+#undef LPB_REG_ROWS
+#undef LPB_MIN_BLOCKS
+#undef LPB_RULE_BLAND
 
 
 // ======================================================================================
@@ -99,11 +116,10 @@ static int pick_variant(int n, int m, const DeviceInfo &di)
     return 0;
 }
 
-extern "C" int lpb200_simplex_batch_typed_device(int B, int n, int m, const void *A, int a_dtype,
-                                                 const double *b, const double *c, double tol, int max_pivots,
-                                                 int32_t *status, double *x, double *objective,
-                                                 int32_t *npivots, int32_t *pivot_log, int log_cap,
-                                                 void *stream_v)
+extern "C" int lpb200_simplex_batch_ex_device(int B, int n, int m, const void *A, int a_dtype, const double *b,
+                                              const double *c, double tol, int max_pivots, int rule,
+                                              int32_t *status, double *x, double *objective, int32_t *npivots,
+                                              int32_t *pivot_log, int log_cap, void *stream_v)
 {
     int rc = check_batch_args(B, n, m, tol, max_pivots, log_cap);
     if (rc) return rc;
@@ -111,11 +127,18 @@ extern "C" int lpb200_simplex_batch_typed_device(int B, int n, int m, const void
         set_error("lpb200_simplex_batch: a_dtype must be one of LPB200_DTYPE_*");
         return LPB200_E_INVALID;
     }
+    if (rule != LPB200_RULE_REFERENCE && rule != LPB200_RULE_BLAND) {
+        set_error("lpb200_simplex_batch: rule must be LPB200_RULE_REFERENCE or LPB200_RULE_BLAND");
+        return LPB200_E_INVALID;
+    }
     if (B == 0) return 0;
     cudaStream_t stream = (cudaStream_t)stream_v;
     DeviceInfo di;
     rc = get_device_info(&di);
     if (rc) return rc;
+    if (rule == LPB200_RULE_BLAND)
+        return bland8::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots,
+                              pivot_log, log_cap, stream);
     if (pick_variant(n, m, di) == 1)
         return reg15::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots,
                              pivot_log, log_cap, stream);
@@ -128,8 +151,9 @@ extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A,
                                            double *x, double *objective, int32_t *npivots,
                                            int32_t *pivot_log, int log_cap, void *stream_v)
 {
-    return lpb200_simplex_batch_typed_device(B, n, m, A, LPB200_DTYPE_F64, b, c, tol, max_pivots, status, x,
-                                             objective, npivots, pivot_log, log_cap, stream_v);
+    return lpb200_simplex_batch_ex_device(B, n, m, A, LPB200_DTYPE_F64, b, c, tol, max_pivots,
+                                          LPB200_RULE_REFERENCE, status, x, objective, npivots, pivot_log, log_cap,
+                                          stream_v);
 }
 
 // Device scratch of the host-pointer entry point: two buffer sets and two streams, owned by the
@@ -172,10 +196,10 @@ static thread_local HostArena g_arena;
 // Host-pointer entry point: the batch is cut into chunks that are copied in, solved and
 // copied out on two alternating streams, so the PCIe copy of chunk k+1 overlaps the solve of
 // chunk k and device memory stays bounded (two chunk-sized buffer sets).
-extern "C" int lpb200_simplex_batch_typed(int B, int n, int m, const void *A_v, int a_dtype, const double *b,
-                                          const double *c, double tol, int max_pivots, int32_t *status,
-                                          double *x, double *objective, int32_t *npivots, int32_t *pivot_log,
-                                          int log_cap)
+extern "C" int lpb200_simplex_batch_ex(int B, int n, int m, const void *A_v, int a_dtype, const double *b,
+                                       const double *c, double tol, int max_pivots, int rule, int32_t *status,
+                                       double *x, double *objective, int32_t *npivots, int32_t *pivot_log,
+                                       int log_cap)
 {
     int rc = check_batch_args(B, n, m, tol, max_pivots, log_cap);
     if (rc) return rc;
@@ -240,8 +264,8 @@ extern "C" int lpb200_simplex_batch_typed(int B, int n, int m, const void *A_v, 
         LPB_TRY(cudaMemcpyAsync(q.c, c + lo * lpc, cnt * lpc * 8, cudaMemcpyHostToDevice, q.stream));
         if (lplog) LPB_TRY(cudaMemsetAsync(q.log, 0xff, cnt * lplog * 4, q.stream));
         if (rc == 0)
-            rc = lpb200_simplex_batch_typed_device((int)cnt, n, m, q.A, a_dtype, q.b, q.c, tol, max_pivots, q.st,
-                                                   q.x, q.obj, q.np, q.log, log_cap, q.stream);
+            rc = lpb200_simplex_batch_ex_device((int)cnt, n, m, q.A, a_dtype, q.b, q.c, tol, max_pivots, rule, q.st,
+                                                q.x, q.obj, q.np, q.log, log_cap, q.stream);
         LPB_TRY(cudaMemcpyAsync(status + lo, q.st, cnt * 4, cudaMemcpyDeviceToHost, q.stream));
         LPB_TRY(cudaMemcpyAsync(x + lo * lpc, q.x, cnt * lpc * 8, cudaMemcpyDeviceToHost, q.stream));
         LPB_TRY(cudaMemcpyAsync(objective + lo, q.obj, cnt * 8, cudaMemcpyDeviceToHost, q.stream));
@@ -263,6 +287,6 @@ extern "C" int lpb200_simplex_batch(int B, int n, int m, const double *A, const 
                                     double tol, int max_pivots, int32_t *status, double *x,
                                     double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap)
 {
-    return lpb200_simplex_batch_typed(B, n, m, A, LPB200_DTYPE_F64, b, c, tol, max_pivots, status, x, objective,
-                                      npivots, pivot_log, log_cap);
+    return lpb200_simplex_batch_ex(B, n, m, A, LPB200_DTYPE_F64, b, c, tol, max_pivots, LPB200_RULE_REFERENCE,
+                                   status, x, objective, npivots, pivot_log, log_cap);
 }

@@ -124,6 +124,29 @@ struct Ctx {
     unsigned long long *timing;
 };
 
+#if LPB_RULE_BLAND
+// Column to pivot a still-basic x_aux out on after phase 1: the non-basic variable with the lowest
+// id whose entry in physical row r is non-zero; -1 when the row is all zero.
+__device__ __forceinline__ int driveout_column(const Ctx &c, int ncols, int r)
+{
+    const int tid = threadIdx.x;
+    if (tid < kSweepThreads) {
+        unsigned key = 0xffffffffu;
+        const double *row = c.T + (size_t)r * c.S + 1;
+        for (int k = tid; k < ncols; k += kSweepThreads)
+            if (fabs(row[k]) > c.tol) key = min(key, ((unsigned)c.colvar[k] << 16) | (unsigned)k);
+        key = __reduce_min_sync(0xffffffffu, key);
+        if ((tid & 31) == 0) c.redu32[tid >> 5] = key;
+    }
+    __syncthreads();
+    unsigned best = c.redu32[0];
+#pragma unroll
+    for (int w = 1; w < kSweepWarps; ++w) best = min(best, c.redu32[w]);
+    __syncthreads();
+    return best == 0xffffffffu ? -1 : (int)(best & 0xffffu);
+}
+#endif
+
 // ---- entering column: first positive objective coefficient in set-slot order (:390-392) ----
 // Stand-alone pass (loop entry, and after a set-table rebuild).  Returns the column position,
 // or -1 when no coefficient is > tol (loop ends, :447).
@@ -185,7 +208,9 @@ __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool 
             c.fc[i] = f;
             if (v >= 0) {
                 const int nc = c.nonecol[i];
+#if !LPB_RULE_BLAND
                 crash |= (nc == kNoneInitial && e_is_slack) || (nc == e) || (c.untouched[i] && e_in_basis0);
+#endif
                 if (f != 0.0) {  // row is rewritten by this pivot: its only None is column e
                     c.nonecol[i] = e;
                     c.untouched[i] = 0;
@@ -195,7 +220,7 @@ __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool 
                 if (cand || (forced && f != 0.0)) c.pinvs[i] = pivot_inverse(f, c.tol);
                 if (cand) {
                     const double ratio = snap(__ddiv_rn(c.T[(size_t)i * c.S], coeff), c.tol);
-                    if (ratio != 0.0) {  // zero ratios count as +inf in min_index (:161)
+                    if (ratio != 0.0 || LPB_RULE_BLAND) {  // zero ratios count as +inf in min_index (:161)
                         const unsigned long long k = order_key(ratio);
                         const int vi = (v << 16) | i;  // ties -> lowest variable id (rows are unique per id)
                         if (k < key || (k == key && vi < var)) {
@@ -260,6 +285,10 @@ __device__ __forceinline__ void bookkeeping(const Ctx &c, int p, int src, int de
         c.misc[MI_DFILL] = d.fill;
         c.misc[MI_DUSED] = d.used;
     }
+#if LPB_RULE_BLAND
+    (void)eslot;
+    c.colslot[p] = l;  // Bland: the entering priority of a column is the id of its variable
+#else
     {  // independent.remove(e); independent.add(l)
         PySet s = {c.misc[MI_ISIZE], c.misc[MI_IFILL], c.misc[MI_IUSED]};
         pyset_remove_slot(c.tab_i, s, eslot);
@@ -276,6 +305,7 @@ __device__ __forceinline__ void bookkeeping(const Ctx &c, int p, int src, int de
         c.misc[MI_IFILL] = s.fill;
         c.misc[MI_IUSED] = s.used;
     }
+#endif
     // new objective coefficient of column p: snap(None + c_e * (1/pivot)) (:314-318, :343-344)
     unsigned key = 0xffffffffu;
     const double fobj = c.fc[c.n];
@@ -475,7 +505,9 @@ __device__ __forceinline__ int ratio_staged(const Ctx &c, int e, bool forced)
             }
             if (v >= 0) {
                 const int nc = c.nonecol[i];
+#if !LPB_RULE_BLAND
                 crash |= (nc == kNoneInitial && e_is_slack) || (nc == e) || (c.untouched[i] && e_in_basis0);
+#endif
                 if (f != 0.0) {
                     c.nonecol[i] = e;
                     c.untouched[i] = 0;
@@ -485,7 +517,7 @@ __device__ __forceinline__ int ratio_staged(const Ctx &c, int e, bool forced)
                 if (cand || (forced && f != 0.0)) c.pinvs[i] = pivot_inverse(f, c.tol);
                 if (cand) {
                     const double ratio = snap(__ddiv_rn(c.bcol[i], coeff), c.tol);
-                    if (ratio != 0.0) {
+                    if (ratio != 0.0 || LPB_RULE_BLAND) {
                         const unsigned long long k = order_key(ratio);
                         const int vi = (v << 16) | i;
                         if (k < key || (k == key && vi < var)) {
@@ -519,7 +551,7 @@ __device__ __forceinline__ int ratio_staged(const Ctx &c, int e, bool forced)
 }
 
 __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pivots, int32_t *log,
-                                        int log_cap, int forced_row)
+                                        int log_cap, int forced_p, int forced_lr)
 {
     constexpr int R = LPB_REG_ROWS;
     const int tid = threadIdx.x;
@@ -539,8 +571,8 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
         a[j] = (active && j < c.rpt && row < nphys) ? T2[(size_t)row * rs + cxi] : make_double2(0.0, 0.0);
     }
 
-    bool forced = forced_row >= 0;
-    int p = forced ? c.m : select_entering(c, ncols);
+    bool forced = forced_lr >= 0;
+    int p = forced ? forced_p : select_entering(c, ncols);
     int status = 0;
 #ifdef LPB_TIMING
     const bool tm = (c.timing != nullptr) && ((threadIdx.x & 31) == 0);
@@ -575,7 +607,7 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
         __syncthreads();
         // ---- step 2: min-ratio test (:394-436) ----
         int lr = ratio_staged(c, e, forced);
-        if (forced) lr = (forced_row << 16) | forced_row;  // rows still hold their own slack variable
+        if (forced) lr = forced_lr;
         if (lr == -2) { status = LPB200_STATUS_REF_TYPE_ERROR; break; }
         if (lr < 0) { status = LPB200_STATUS_INFINITY; break; }
         if (npiv >= max_pivots) { status = LPB200_STATUS_ITERATION_LIMIT; break; }
@@ -664,13 +696,14 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
 }
 #else
 // SlackForm.solve loop (:442-466).  Returns 0 when optimal, else a terminal status code.
-// forced_row >= 0: the first pivot is the forced one of phase 1 (:524) -- x_aux (column
-// position m) enters, the basic variable of row forced_row leaves -- then the loop runs.
+// forced_lr >= 0: the first pivot is forced -- the variable at column position forced_p enters,
+// the basic variable forced_lr >> 16 in physical row forced_lr & 0xffff leaves (phase 1, :524:
+// x_aux enters, the row of min b leaves) -- then the loop runs.
 __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pivots, int32_t *log,
-                                        int log_cap, int forced_row)
+                                        int log_cap, int forced_p, int forced_lr)
 {
-    bool forced = forced_row >= 0;
-    int p = forced ? c.m : select_entering(c, ncols);
+    bool forced = forced_lr >= 0;
+    int p = forced ? forced_p : select_entering(c, ncols);
 #ifdef LPB_TIMING
     const bool tm = (c.timing != nullptr) && ((threadIdx.x & 31) == 0);
     unsigned long long acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
@@ -686,7 +719,7 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
 #ifdef LPB_TIMING
         t1 = clock64();
 #endif
-        if (forced) lr = (forced_row << 16) | forced_row;  // rows still hold their own slack variable
+        if (forced) lr = forced_lr;
         if (lr == -2) { status = LPB200_STATUS_REF_TYPE_ERROR; break; }
         if (lr < 0) { status = LPB200_STATUS_INFINITY; break; }
         if (npiv >= max_pivots) { status = LPB200_STATUS_ITERATION_LIMIT; break; }
@@ -878,7 +911,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
             int idx = 0x7fffffff;
             for (int i = tid; i < n; i += kSweepThreads) {
                 const double bi = gb[i];
-                const unsigned long long k = order_key(bi != 0.0 ? bi : CUDART_INF);
+                const unsigned long long k = order_key((bi != 0.0 || LPB_RULE_BLAND) ? bi : CUDART_INF);
                 if (k < key || (k == key && i < idx)) {
                     key = k;
                     idx = i;
@@ -909,7 +942,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
         int status = 0;
         int npiv = 0;
         int ncols = phase1 ? m + 1 : m;
-        if (!phase1 && !(min_c > tol)) status = LPB200_STATUS_REF_ATTRIBUTE_ERROR;  // :626
+        if (!LPB_RULE_BLAND && !phase1 && !(min_c > tol)) status = LPB200_STATUS_REF_ATTRIBUTE_ERROR;  // :626
         c.track_dep = phase1;
         c.spare = n + 1;
 
@@ -944,7 +977,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                 for (int k = tid; k <= m; k += kSweepThreads) {
                     c.colvar[k] = n + k;
                     c.varpos[n + k] = k;
-                    c.colslot[k] = (n + k) & (isize - 1);
+                    c.colslot[k] = LPB_RULE_BLAND ? (n + k) : ((n + k) & (isize - 1));
                 }
                 for (int w = tid; w < (nv + 31) / 32; w += kSweepThreads) c.basis0[w] = 0u;
             } else {
@@ -973,17 +1006,35 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
 
             // One instance of the pivot loop serves phase 1 (:526, entered through the forced
             // pivot), phase 2 after it (:599) and phase 2 alone (:619).
-            int forced_row = phase1 ? idx0 : -1;
+            // the forced pivot: x_aux (column position m) enters, the row of min b -- which still
+            // holds its own slack variable, id == row -- leaves (:524)
+            int forced_p = m, forced_lr = phase1 ? ((idx0 << 16) | idx0) : -1;
+            bool in_phase1 = phase1;
             for (;;) {
-                status = run_loop(c, ncols, npiv, a.max_pivots, log, a.log_cap, forced_row);
-                if (forced_row < 0) break;  // phase 2 is done
-                forced_row = -1;
+                status = run_loop(c, ncols, npiv, a.max_pivots, log, a.log_cap, forced_p, forced_lr);
+                if (!in_phase1) break;  // phase 2 is done
+                forced_lr = -1;
                 const int aux = n + m;
                 if (status == 0) {
                     if (!(fabs(c.T[(size_t)n * S]) <= tol)) status = LPB200_STATUS_NO_SOLUTION;  // :528-530
+#if LPB_RULE_BLAND
+                    else if (c.varpos[aux] < 0) {
+                        // x_aux is basic at level 0: pivot it out on the lowest-id column with a
+                        // non-zero entry in its row; an all-zero row is a redundant constraint, left inert
+                        const int r = ~c.varpos[aux];
+                        const int k = driveout_column(c, ncols, r);
+                        if (k >= 0) {
+                            forced_p = k;
+                            forced_lr = (aux << 16) | r;
+                            continue;
+                        }
+                    }
+#else
                     else if (c.varpos[aux] < 0) status = LPB200_STATUS_REF_INDEX_ERROR;  // :541 -> :183
+#endif
                 }
                 if (status != 0) break;
+                in_phase1 = false;
                 {
                     // ---- rebuild the original objective (:537-541) ----
                     // basic ORIGINAL variables in iteration order of the `dependent` set
@@ -1003,7 +1054,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                     }
                     // stage c in nr[], start from (v, c) = (0, [None]*n + float(c)) (:516, :537)
                     if (tid < kSweepThreads) {
-                        for (int j = tid; j < m; j += kSweepThreads) c.nr[j] = gc[j];
+                        for (int j = tid; j <= m; j += kSweepThreads) c.nr[j] = (j < m) ? gc[j] : 0.0;  // [m]: x_aux
                     }
                     __syncthreads();
                     const int kaux = c.varpos[aux];
@@ -1039,17 +1090,19 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                             c.basis0[w] = bits;
                         }
                         for (int i = tid; i < nphys; i += kSweepThreads) c.untouched[i] = 1;
-                        for (int i = tid; i < nphys; i += kSweepThreads) {
+                        for (int i = tid; i < nphys && kaux >= 0; i += kSweepThreads) {
                             double *Ti = c.T + (size_t)i * S;
                             if (kaux != last) Ti[1 + kaux] = Ti[1 + last];
                             Ti[1 + last] = 0.0;
                         }
                         for (int k = tid; k < S; k += kSweepThreads) c.nr[k] = 0.0;
                         for (int i = tid; i < nfc; i += kSweepThreads) c.fc[i] = 0.0;  // list[] lived here
-                    } else if (tid == kSweepThreads) {
+                    } else if (tid == kSweepThreads && kaux >= 0) {
+#if !LPB_RULE_BLAND
                         PySet s = {c.misc[MI_ISIZE], c.misc[MI_IFILL], c.misc[MI_IUSED]};
                         pyset_remove_slot(c.tab_i, s, c.colslot[kaux]);  // independent.remove(nvars) (:574)
                         c.misc[MI_IUSED] = s.used;
+#endif
                         if (kaux != last) {
                             const int w = c.colvar[last];
                             c.colvar[kaux] = w;
@@ -1057,7 +1110,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                             c.varpos[w] = kaux;
                         }
                     }
-                    ncols = m;
+                    if (kaux >= 0) ncols = m;  // (Bland only: x_aux left basic in an all-zero row keeps m+1 columns)
                     __syncthreads();
                 }
             }

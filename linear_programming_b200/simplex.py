@@ -87,20 +87,35 @@ def _a_dtype_code(dtype) -> int | None:
     return _TYPED_A.get(str(dtype).replace("torch.", ""))
 
 
+RULE_REFERENCE, RULE_BLAND = 0, 1
+_RULES = {"reference": RULE_REFERENCE, "bland": RULE_BLAND}
+
+
+def _rule_code(rule: str, mode: str) -> int:
+    if rule not in _RULES:
+        raise ValueError("rule must be 'reference' or 'bland'")
+    if rule != "reference" and mode == "single":
+        raise ValueError("rule='bland' is served by the batch kernel only (mode='batch' or 'auto')")
+    return _RULES[rule]
+
+
 def solve_batch(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None = None,
-                log_cap: int = 0, mode: str = "auto") -> BatchResult:
+                log_cap: int = 0, mode: str = "auto", rule: str = "reference") -> BatchResult:
     """Solve B independent LPs  max c.x  s.t. A x <= b, x >= 0  with the reference's semantics.
 
     A[B,n,m], b[B,n], c[B,m]: numpy / nested lists (host path: copies in and out) or CUDA
     float64 torch tensors (zero-copy, enqueued on the current stream, results stay on the GPU).
     A may also be int8 / int16 / int32 / float32 (numpy array or CUDA tensor): the batch kernel
     reads it as is and widens on the GPU -- same answers, a fraction of the bytes over PCIe.
+    rule: "reference" reproduces the reference bit for bit, bugs included; "bland" is the
+    corrected mode (include/lp_b200.h LPB200_RULE_BLAND: Bland's rule, zero ratios kept, x_aux
+    driven out, no crash classes) -- not reference behaviour, batch kernel only.
     mode: "batch" (one CTA per LP, tableau in shared memory), "single" (grid-wide kernel, one
     LP after the other), "auto" (batch when the tableau fits shared memory).
     """
     L = _lib.lib()
     if _is_torch_cuda(A):
-        return _solve_batch_torch(L, A, b, c, tol, max_pivots, log_cap, mode)
+        return _solve_batch_torch(L, A, b, c, tol, max_pivots, log_cap, mode, rule)
     a_code = _a_dtype_code(getattr(A, "dtype", None))
     A = np.ascontiguousarray(A) if a_code is not None else np.ascontiguousarray(A, dtype=np.float64)
     a_code = a_code or DTYPE_F64
@@ -120,10 +135,11 @@ def solve_batch(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None 
     log = np.full((B, log_cap, 2), -1, dtype=np.int32) if log_cap > 0 else None
     if mode == "auto":
         mode = "batch" if fits_batch_kernel(n, m) else "single"
+    r_code = _rule_code(rule, mode)
     if mode == "batch":
-        _lib.check(L.lpb200_simplex_batch_typed(B, n, m, _vp(A), a_code, _vp(b), _vp(c), tol, max_pivots,
-                                                _vp(status), _vp(x), _vp(obj), _vp(npiv),
-                                                _vp(log) if log is not None else None, log_cap))
+        _lib.check(L.lpb200_simplex_batch_ex(B, n, m, _vp(A), a_code, _vp(b), _vp(c), tol, max_pivots, r_code,
+                                             _vp(status), _vp(x), _vp(obj), _vp(npiv),
+                                             _vp(log) if log is not None else None, log_cap))
     elif mode == "single":
         if a_code != DTYPE_F64:
             A = A.astype(np.float64)
@@ -138,7 +154,7 @@ def solve_batch(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None 
     return BatchResult(status, x, obj, npiv, log)
 
 
-def _solve_batch_torch(L, A, b, c, tol, max_pivots, log_cap, mode):
+def _solve_batch_torch(L, A, b, c, tol, max_pivots, log_cap, mode, rule="reference"):
     import torch
     a_code = _a_dtype_code(A.dtype)
     if a_code is None or not A.is_contiguous():
@@ -162,11 +178,12 @@ def _solve_batch_torch(L, A, b, c, tol, max_pivots, log_cap, mode):
         logp = log.data_ptr() if log is not None else None
         if mode == "auto":
             mode = "batch" if fits_batch_kernel(n, m) else "single"
+        r_code = _rule_code(rule, mode)
         if mode == "batch":
-            _lib.check(L.lpb200_simplex_batch_typed_device(B, n, m, A.data_ptr(), a_code, b.data_ptr(),
-                                                           c.data_ptr(), tol, max_pivots, status.data_ptr(),
-                                                           x.data_ptr(), obj.data_ptr(), npiv.data_ptr(), logp,
-                                                           log_cap, stream))
+            _lib.check(L.lpb200_simplex_batch_ex_device(B, n, m, A.data_ptr(), a_code, b.data_ptr(),
+                                                        c.data_ptr(), tol, max_pivots, r_code,
+                                                        status.data_ptr(), x.data_ptr(), obj.data_ptr(),
+                                                        npiv.data_ptr(), logp, log_cap, stream))
         elif mode == "single":
             if a_code != DTYPE_F64:
                 A = A.to(torch.float64)
@@ -182,7 +199,8 @@ def _solve_batch_torch(L, A, b, c, tol, max_pivots, log_cap, mode):
     return BatchResult(status, x, obj, npiv, log)
 
 
-def solve(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None = None, mode: str = "auto"):
+def solve(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None = None, mode: str = "auto",
+          rule: str = "reference"):
     """Per-problem surface: solve(A, b, c) -> (status, x).  x is a list of m floats when
     status == 0, else None (like the reference's (anst, ansx))."""
     A = np.asarray(A, dtype=np.float64)
@@ -190,7 +208,7 @@ def solve(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None = None
     c = np.asarray(c, dtype=np.float64).reshape(-1)
     n, m = b.shape[0], c.shape[0]
     A = A.reshape(n, m)
-    r = solve_batch(A[None], b[None], c[None], tol=tol, max_pivots=max_pivots, mode=mode)
+    r = solve_batch(A[None], b[None], c[None], tol=tol, max_pivots=max_pivots, mode=mode, rule=rule)
     st = int(r.status[0])
     return st, ([float(v) for v in r.x[0]] if st == STATUS_BOUNDED else None)
 
@@ -207,6 +225,7 @@ class Simplex:
         self.m = m
         self.tolerance = DEFAULT_TOLERANCE
         self.max_pivots = None
+        self.rule = "reference"  # "bland": the corrected mode (engine-only attribute, see solve_batch)
         self.npivots = None
         self.pivots = None
 
@@ -224,7 +243,7 @@ class Simplex:
         c = np.asarray(self.c, dtype=np.float64).reshape(m)
         cap = self.max_pivots if self.max_pivots is not None else default_max_pivots(n, m)
         r = solve_batch(A[None], b[None], c[None], tol=self.tolerance, max_pivots=cap,
-                        log_cap=(cap if record_pivots else 0))
+                        log_cap=(cap if record_pivots else 0), rule=self.rule)
         st = int(r.status[0])
         self.npivots = int(r.npivots[0])
         if record_pivots:

@@ -64,6 +64,13 @@ def lib():
         L.lp_oracle_simplex_batch.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, _dp, _dp, _dp,
                                               ctypes.c_double, ctypes.c_int, _ip, _dp, _dp, _ip,
                                               ctypes.c_int]
+        L.lp_oracle_simplex_rule.restype = ctypes.c_int
+        L.lp_oracle_simplex_rule.argtypes = [ctypes.c_int, ctypes.c_int, _dp, _dp, _dp, ctypes.c_double,
+                                             ctypes.c_int, ctypes.c_int, _dp, _dp, _ip, _ip, ctypes.c_int]
+        L.lp_oracle_simplex_batch_rule.restype = ctypes.c_int
+        L.lp_oracle_simplex_batch_rule.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, _dp, _dp, _dp,
+                                                   ctypes.c_double, ctypes.c_int, ctypes.c_int, _ip, _dp, _dp,
+                                                   _ip, ctypes.c_int]
         L.lp_oracle_gauss_jordan.restype = None
         L.lp_oracle_gauss_jordan.argtypes = [ctypes.c_int, _dp, _dp, _dp, ctypes.c_int]
         L.lp_oracle_gauss_jordan_batch.restype = ctypes.c_int
@@ -83,8 +90,13 @@ def _p(a, t=_dp):
     return a.ctypes.data_as(t)
 
 
-def simplex(A, b, c, tol: float = 1e-9, max_pivots: int = 1_000_000, log_cap: int | None = None):
-    """One LP through the C restatement.  Returns dict(status, x, objective, npivots, pivots)."""
+RULES = {"reference": 0, "bland": 1}
+
+
+def simplex(A, b, c, tol: float = 1e-9, max_pivots: int = 1_000_000, log_cap: int | None = None,
+            rule: str = "reference"):
+    """One LP through the C restatement.  Returns dict(status, x, objective, npivots, pivots).
+    rule="bland" is the corrected (non-reference) mode, see simplex_oracle.c."""
     A, b, c = _d(A), _d(b), _d(c)
     n, m = b.shape[0], c.shape[0]
     assert A.shape == (n, m), (A.shape, n, m)
@@ -94,14 +106,20 @@ def simplex(A, b, c, tol: float = 1e-9, max_pivots: int = 1_000_000, log_cap: in
     obj = np.zeros(1)
     npiv = np.zeros(1, dtype=np.int32)
     log = np.zeros((max(log_cap, 1), 2), dtype=np.int32)
-    st = lib().lp_oracle_simplex(n, m, _p(A), _p(b), _p(c), tol, max_pivots, _p(x), _p(obj),
-                                 _p(npiv, _ip), _p(log, _ip), log_cap)
+    st = lib().lp_oracle_simplex_rule(n, m, _p(A), _p(b), _p(c), tol, max_pivots, RULES[rule], _p(x), _p(obj),
+                                      _p(npiv, _ip), _p(log, _ip), log_cap)
     k = int(npiv[0])
     return {"status": int(st), "x": x, "objective": float(obj[0]), "npivots": k,
             "pivots": [tuple(int(v) for v in r) for r in log[:min(k, log_cap)]]}
 
 
-def simplex_batch(A, b, c, tol: float = 1e-9, max_pivots: int = 1_000_000, threads: int = 0):
+def driveouts(reset: bool = True) -> int:
+    """x_aux drive-out pivots the rule="bland" restatement performed since the last reset."""
+    return int(lib().lp_oracle_driveouts(int(reset)))
+
+
+def simplex_batch(A, b, c, tol: float = 1e-9, max_pivots: int = 1_000_000, threads: int = 0,
+                  rule: str = "reference"):
     """Batch [B,n,m],[B,n],[B,m] on host threads.  Returns (status, x, objective, npivots, threads)."""
     A, b, c = _d(A), _d(b), _d(c)
     B, n, m = A.shape
@@ -109,8 +127,8 @@ def simplex_batch(A, b, c, tol: float = 1e-9, max_pivots: int = 1_000_000, threa
     x = np.zeros((B, m))
     obj = np.zeros(B)
     npiv = np.zeros(B, dtype=np.int32)
-    used = lib().lp_oracle_simplex_batch(B, n, m, _p(A), _p(b), _p(c), tol, max_pivots,
-                                         _p(status, _ip), _p(x), _p(obj), _p(npiv, _ip), threads)
+    used = lib().lp_oracle_simplex_batch_rule(B, n, m, _p(A), _p(b), _p(c), tol, max_pivots, RULES[rule],
+                                              _p(status, _ip), _p(x), _p(obj), _p(npiv, _ip), threads)
     return status, x, obj, npiv, int(used)
 
 

@@ -66,6 +66,19 @@ int lp_oracle_simplex(int n, int m, const double *A, const double *b, const doub
                       int max_pivots, double *x, double *objective, int32_t *npivots,
                       int32_t *pivot_log, int log_cap);
 
+/* The same with a pivoting rule: LP_RULE_REFERENCE is lp_oracle_simplex; LP_RULE_BLAND is the
+ * corrected mode described at the top of simplex_oracle.c (not reference behaviour). */
+#define LP_RULE_REFERENCE 0
+#define LP_RULE_BLAND 1
+int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const double *c, double tol,
+                           int max_pivots, int rule, double *x, double *objective, int32_t *npivots,
+                           int32_t *pivot_log, int log_cap);
+int lp_oracle_simplex_batch_rule(int B, int n, int m, const double *A, const double *b, const double *c,
+                                 double tol, int max_pivots, int rule, int32_t *status, double *x,
+                                 double *objective, int32_t *npivots, int threads);
+
+int lp_oracle_driveouts(int reset); /* LP_RULE_BLAND: x_aux drive-out pivots so far (test instrumentation) */
+
 /* Batch driver used for the timed CPU baseline: pthreads over problems
  * (threads <= 0 means all cores).  Returns the number of threads used. */
 int lp_oracle_simplex_batch(int B, int n, int m, const double *A, const double *b, const double *c,

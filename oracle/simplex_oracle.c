@@ -22,6 +22,17 @@
  *   lp_oracle_simplex()    Simplex.solve                  simplex.py:586-630
  *                          find_basic_feasible            simplex.py:514-584
  *                          make_auxiliary_form            simplex.py:632-660
+ *
+ * rule = LP_RULE_BLAND is the "corrected" mode of SURVEY 8(f) rank 3 -- NOT reference behaviour,
+ * no reference to pin it to ("parity unpinned" for this mode; tests check it against scipy
+ * HiGHS instead).  Same tableau arithmetic (two roundings, snap), different decisions:
+ *   - entering = LOWEST VARIABLE ID with c[j] > tol (Bland) instead of CPython-set order;
+ *   - ratio test keeps zero ratios (the reference skips them, Appendix A.8), ties -> lowest id;
+ *   - phase dispatch on the true minimum of b (zeros are zeros); min b >= 0 starts phase 2,
+ *     so the AttributeError class (:626) is gone; None-tracking (TypeError :409) is off;
+ *   - x_aux still basic (at level 0) after phase 1 is pivoted out on the lowest-id non-basic
+ *     variable with a non-zero coefficient in its row instead of raising IndexError (:541);
+ *     if the row is all zero it is a redundant constraint: it stays, inert, and no column is dropped.
  */
 #include <math.h>
 #include <stdlib.h>
@@ -50,10 +61,20 @@ typedef struct {
     pyset_t dep, indep;
     double tol;
     int npiv, maxpiv;
+    int rule;
     int32_t *log;
     int logcap;
     double *newrow;
 } lp_t;
+
+/* test instrumentation: x_aux drive-out pivots performed since the last reset (not thread-safe) */
+static int g_driveouts = 0;
+int lp_oracle_driveouts(int reset)
+{
+    const int v = g_driveouts;
+    if (reset) g_driveouts = 0;
+    return v;
+}
 
 static inline double snap(double v, double tol) { return fabs(v) <= tol ? 0.0 : v; }
 
@@ -125,6 +146,12 @@ static void do_pivot(lp_t *s, int e, int l)
 static int pick_entering(const lp_t *s)
 {
     const double *c = s->T + (size_t)s->n * s->stride;
+    if (s->rule == LP_RULE_BLAND) {
+        int best = -1;
+        for (int k = 0; k < s->ncols; ++k)
+            if (c[1 + k] > s->tol && (best < 0 || s->colvar[k] < best)) best = s->colvar[k];
+        return best;
+    }
     for (int i = 0; i < s->indep.size; ++i) {
         const int v = s->indep.table[i];
         if (v >= 0 && c[1 + s->varpos[v]] > s->tol) return v;
@@ -136,7 +163,8 @@ static int pick_entering(const lp_t *s)
 static int pick_leaving(const lp_t *s, int e)
 {
     const int n = s->n, S = s->stride, p = s->varpos[e];
-    for (int i = 0; i < n; ++i) { /* -1 * None at :409 */
+    const int bland = (s->rule == LP_RULE_BLAND);
+    for (int i = 0; i < n && !bland; ++i) { /* -1 * None at :409 */
         if ((s->none_col[i] == NONE_INITIAL && e < n) || s->none_col[i] == e ||
             (s->untouched[i] && s->basis0[e]))
             return -2;
@@ -148,7 +176,7 @@ static int pick_leaving(const lp_t *s, int e)
         const double coeff = -1.0 * Ti[1 + p];
         if (!(coeff > s->tol)) continue;                 /* ispositive(coeff), :413 */
         const double ratio = snap(Ti[0] / coeff, s->tol); /* :414-415 */
-        if (ratio == 0.0) continue;                      /* falsy -> key +inf in min_index, :161 */
+        if (ratio == 0.0 && !bland) continue;            /* falsy -> key +inf in min_index, :161 */
         const int v = s->rowvar[i];
         /* min() over ascending variable id keeps the first minimum */
         if (best < 0 || ratio < bestr || (ratio == bestr && v < best)) {
@@ -177,6 +205,14 @@ int lp_oracle_simplex(int n, int m, const double *A, const double *b, const doub
                       int max_pivots, double *x, double *objective, int32_t *npivots,
                       int32_t *pivot_log, int log_cap)
 {
+    return lp_oracle_simplex_rule(n, m, A, b, c, tol, max_pivots, LP_RULE_REFERENCE, x, objective, npivots,
+                                  pivot_log, log_cap);
+}
+
+int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const double *c, double tol,
+                           int max_pivots, int rule, double *x, double *objective, int32_t *npivots,
+                           int32_t *pivot_log, int log_cap)
+{
     lp_t s;
     memset(&s, 0, sizeof(s));
     const int nv = n + m + 1;
@@ -186,6 +222,7 @@ int lp_oracle_simplex(int n, int m, const double *A, const double *b, const doub
     s.stride = m + 2;
     s.tol = tol;
     s.maxpiv = max_pivots;
+    s.rule = rule;
     s.log = pivot_log;
     s.logcap = log_cap;
     s.T = (double *)calloc((size_t)(n + 1) * (size_t)s.stride, sizeof(double));
@@ -205,7 +242,7 @@ int lp_oracle_simplex(int n, int m, const double *A, const double *b, const doub
     {
         double bestkey = INFINITY;
         for (int i = 0; i < n; ++i) {
-            const double key = (b[i] != 0.0) ? b[i] : INFINITY;
+            const double key = (b[i] != 0.0 || rule == LP_RULE_BLAND) ? b[i] : INFINITY;
             if (key < bestkey) {
                 bestkey = key;
                 idx = i;
@@ -214,7 +251,7 @@ int lp_oracle_simplex(int n, int m, const double *A, const double *b, const doub
     }
     const double min_c = b[idx];
     const int phase1 = (min_c < 0.0);
-    if (!phase1 && !(min_c > tol)) { /* self.assignment undefined -> AttributeError, :626 */
+    if (!phase1 && !(min_c > tol) && rule != LP_RULE_BLAND) { /* self.assignment undefined -> AttributeError, :626 */
         status = LP_STATUS_REF_ATTRIBUTE_ERROR;
         goto done_noset;
     }
@@ -258,7 +295,19 @@ int lp_oracle_simplex(int n, int m, const double *A, const double *b, const doub
             status = LP_STATUS_NO_SOLUTION;
             goto done;
         }
-        if (s.isbasic[aux]) { /* new_obj.get_coefficient(n+m) -> IndexError, :541 -> :183 */
+        if (s.isbasic[aux] && rule == LP_RULE_BLAND) { /* drive x_aux out of the basis */
+            const double *Tr = s.T + (size_t)s.varpos[aux] * s.stride;
+            int ev = -1;
+            for (int k = 0; k < s.ncols; ++k)
+                if (fabs(Tr[1 + k]) > tol && (ev < 0 || s.colvar[k] < ev)) ev = s.colvar[k];
+            if (ev >= 0) {
+                if (s.npiv >= s.maxpiv) { status = LP_STATUS_ITERATION_LIMIT; goto done; }
+                do_pivot(&s, ev, aux);
+                ++g_driveouts;
+                status = run_loop(&s); /* the objective is -x_aux again: ends at once */
+                if (status != 0) goto done;
+            }
+        } else if (s.isbasic[aux]) { /* new_obj.get_coefficient(n+m) -> IndexError, :541 -> :183 */
             status = LP_STATUS_REF_INDEX_ERROR;
             goto done;
         }
@@ -289,7 +338,7 @@ int lp_oracle_simplex(int n, int m, const double *A, const double *b, const doub
         /* clean-up, :547-575 */
         for (int v = 0; v < nv; ++v) s.basis0[v] = s.isbasic[v];
         for (int i = 0; i < n; ++i) s.untouched[i] = 1;
-        {
+        if (!s.isbasic[aux]) {
             const int kaux = s.varpos[aux], last = s.ncols - 1;
             if (kaux != last) {
                 for (int i = 0; i <= n; ++i)
@@ -305,7 +354,7 @@ int lp_oracle_simplex(int n, int m, const double *A, const double *b, const doub
             for (int k = 0; k < s.ncols; ++k) obj[1 + k] = o[s.colvar[k]];
         }
         free(o);
-        pyset_remove(&s.indep, aux); /* :574 -- the same set objects live on into phase 2 */
+        if (!s.isbasic[aux]) pyset_remove(&s.indep, aux); /* :574 -- the same set objects live on into phase 2 */
     }
 
     status = run_loop(&s); /* :599 / :619 */
@@ -329,7 +378,7 @@ typedef struct {
     int B, n, m;
     const double *A, *b, *c;
     double tol;
-    int max_pivots;
+    int max_pivots, rule;
     int32_t *status;
     double *x, *objective;
     int32_t *npivots;
@@ -339,15 +388,23 @@ static void simplex_job(void *arg, int p)
 {
     simplex_job_t *j = (simplex_job_t *)arg;
     const int n = j->n, m = j->m;
-    j->status[p] = lp_oracle_simplex(n, m, j->A + (size_t)p * n * m, j->b + (size_t)p * n,
-                                     j->c + (size_t)p * m, j->tol, j->max_pivots, j->x + (size_t)p * m,
-                                     j->objective + p, j->npivots + p, NULL, 0);
+    j->status[p] = lp_oracle_simplex_rule(n, m, j->A + (size_t)p * n * m, j->b + (size_t)p * n,
+                                          j->c + (size_t)p * m, j->tol, j->max_pivots, j->rule,
+                                          j->x + (size_t)p * m, j->objective + p, j->npivots + p, NULL, 0);
 }
 
 int lp_oracle_simplex_batch(int B, int n, int m, const double *A, const double *b, const double *c,
                             double tol, int max_pivots, int32_t *status, double *x, double *objective,
                             int32_t *npivots, int threads)
 {
-    simplex_job_t j = {B, n, m, A, b, c, tol, max_pivots, status, x, objective, npivots};
+    return lp_oracle_simplex_batch_rule(B, n, m, A, b, c, tol, max_pivots, LP_RULE_REFERENCE, status, x,
+                                        objective, npivots, threads);
+}
+
+int lp_oracle_simplex_batch_rule(int B, int n, int m, const double *A, const double *b, const double *c,
+                                 double tol, int max_pivots, int rule, int32_t *status, double *x,
+                                 double *objective, int32_t *npivots, int threads)
+{
+    simplex_job_t j = {B, n, m, A, b, c, tol, max_pivots, rule, status, x, objective, npivots};
     return lp_oracle_parallel_for(B, threads, simplex_job, &j);
 }

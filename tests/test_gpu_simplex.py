@@ -185,7 +185,7 @@ def test_full_gpu_two_ctas_per_sm_vs_oracle(oracle_lib):
 @pytest.mark.parametrize("dist,n,m,count", [("D1", 100, 100, 64), ("D2", 100, 100, 16), ("D2", 37, 61, 48),
                                             ("D3", 30, 22, 48)])
 def test_typed_constraint_matrix_matches_float64_and_oracle(oracle_lib, dtype, dist, n, m, count):
-    """lpb200_simplex_batch_typed: an integer / float32 A (what a caller that parsed the reference's
+    """lpb200_simplex_batch_ex: an integer / float32 A (what a caller that parsed the reference's
     input with int(), simplex.py:712-717, holds) gives the answers of the float64 call bit for bit
     -- m % 4 == 0 takes the vector loads, the other shapes the element loads."""
     import linear_programming_b200 as lp
@@ -231,3 +231,45 @@ def test_typed_device_tensor_and_golden_cases(simplex_golden):
             _check_against_case(res, p, case)
             checked += 1
     assert checked >= 400
+
+
+def test_bland_rule_stress_distribution_vs_oracle(oracle_lib):
+    """LPB200_RULE_BLAND (corrected mode): status, pivot sequence and x bit-identical to the CPU
+    restatement of the same rule (itself checked against HiGHS in tests/test_oracle_bland.py),
+    on the distribution whose zeros in b crash the reference; includes x_aux drive-outs."""
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    groups = {}
+    for A, b, c in workloads.stress_batch(5000, seed=13):
+        groups.setdefault(A.shape, []).append((A, b, c))
+    seen = set()
+    oracle_lib.driveouts(reset=True)
+    for (n, m), lst in groups.items():
+        A = np.stack([q[0] for q in lst]); b = np.stack([q[1] for q in lst]); c = np.stack([q[2] for q in lst])
+        res = lp.solve_batch(A, b, c, log_cap=64, max_pivots=5000, rule="bland")
+        for p in range(len(lst)):
+            o = oracle_lib.simplex(A[p], b[p], c[p], max_pivots=5000, rule="bland")
+            assert int(res.status[p]) == o["status"]
+            assert int(res.npivots[p]) == o["npivots"]
+            assert res.pivots(p) == o["pivots"][:64]
+            assert np.array_equal(res.x[p].view(np.int64), o["x"].view(np.int64))
+            assert float(res.objective[p]).hex() == float(o["objective"]).hex()
+            seen.add(o["status"])
+    assert seen == {0, -1, 1}
+    assert oracle_lib.driveouts() > 0  # the x_aux drive-out path was exercised
+
+
+@pytest.mark.parametrize("dist,n,m,count", [("D1", 100, 100, 64), ("D2", 100, 100, 8), ("D3", 100, 100, 12),
+                                            ("D3", 37, 61, 64), ("D3", 64, 20, 64)])
+def test_bland_rule_random_batches_vs_oracle(oracle_lib, dist, n, m, count):
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    A, b, c = workloads.simplex_batch(dist, count, n, m, seed=9)
+    cap = 200000
+    res = lp.solve_batch(A.astype(np.int16), b, c, max_pivots=cap, rule="bland")
+    st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=cap, rule="bland")
+    assert np.array_equal(res.status, st)
+    assert np.array_equal(res.npivots, npiv)
+    assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
+    assert np.array_equal(res.objective.view(np.int64), obj.view(np.int64))
+    assert set(int(s) for s in st) <= {0, -1, 1}
