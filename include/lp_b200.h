@@ -174,6 +174,19 @@ int lpb200_gauss_jordan_batch_device(int B, int n, const double *a, const double
                                      void *workspace, int64_t workspace_bytes, void *stream);
 int lpb200_gauss_jordan_batch(int B, int n, const double *a, const double *b, double *x);
 
+/*
+ * The same two calls with a choice of pivot selection.  LPB200_PIVOT_REFERENCE is the reference's
+ * SelectPivotElement (energy_values.cc:85-114: the diagonal element, a row swap only on an exact
+ * zero).  LPB200_PIVOT_PARTIAL (NOT reference behaviour) pivots step k on the
+ * row i >= k with the largest |a[i][k]| (first maximum); the elimination arithmetic
+ * (ProcessPivotElement, :132-159) is unchanged.
+ */
+#define LPB200_PIVOT_REFERENCE 0
+#define LPB200_PIVOT_PARTIAL 1
+int lpb200_gauss_jordan_batch_ex_device(int B, int n, const double *a, const double *b, double *x, int pivoting,
+                                        void *workspace, int64_t workspace_bytes, void *stream);
+int lpb200_gauss_jordan_batch_ex(int B, int n, const double *a, const double *b, double *x, int pivoting);
+
 #ifdef __cplusplus
 }
 #endif

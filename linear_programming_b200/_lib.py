@@ -58,6 +58,9 @@ SIGNATURES = {
     "lpb200_gauss_jordan_batch_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp,
                                                         ctypes.c_int64, c_vp]),
     "lpb200_gauss_jordan_batch": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp]),
+    "lpb200_gauss_jordan_batch_ex_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, ctypes.c_int,
+                                                           c_vp, ctypes.c_int64, c_vp]),
+    "lpb200_gauss_jordan_batch_ex": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, ctypes.c_int]),
 }
 
 

@@ -22,6 +22,14 @@
 // touched (they are exact zeros the reference only rewrites with zeros).
 // A zero pivot met inside a panel truncates the panel there; the swap happens in global
 // memory at the start of the next panel.
+//
+// kPartial = true is the PARTIAL-PIVOTING mode (not reference behaviour:
+// energy_values.cc:100-110 only ever swaps on an exact zero).  Step k pivots on the row i >= k
+// with the largest |a[i][k]| (first maximum).  The search and the row exchange happen inside the
+// shared-memory panel -- the whole panel row moves, scales of the earlier steps included, so the
+// trailing update still sees, per row, the operations of the step-by-step algorithm in order --
+// and the K exchanges are replayed on each trailing column by the thread that owns it at the
+// start of pass 1.  No panel is ever truncated; the arithmetic per element is unchanged.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -50,12 +58,17 @@ constexpr int kGjBlockRows = LPB_GJ_BLOCK;  // rows per work item of the trailin
 #ifndef LPB_GJ_MINB
 #define LPB_GJ_MINB 2
 #endif
+template <bool kPartial>
 __global__ void __launch_bounds__(kGjThreads, LPB_GJ_MINB)
 gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restrict__ x_all)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     double *P = reinterpret_cast<double *>(smem);                 // [n][kGjPS]
     int *flag = reinterpret_cast<int *>(P + (size_t)n * kGjPS);   // [2]
+    // partial pivoting only: perm[q] = row exchanged with row k0+q at step q; per-warp argmax slots
+    int *perm = flag + 4;                                                       // [kGjK]
+    unsigned long long *wkey = reinterpret_cast<unsigned long long *>(perm + kGjK);  // [kGjThreads / 32]
+    int *widx = reinterpret_cast<int *>(wkey + kGjThreads / 32);                // [kGjThreads / 32]
     const int tid = threadIdx.x;
     double *a = a_all + (size_t)blockIdx.x * n * n;
     double *bx = x_all + (size_t)blockIdx.x * n;
@@ -63,7 +76,7 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
     for (int k0 = 0; k0 < n;) {
         const int K = min(kGjK, n - k0);
         // ---- SelectPivotElement for step k0, on the up-to-date matrix in global memory ----
-        if (tid == 0) {
+        if (!kPartial && tid == 0) {
             int sw = -1;
             if (a[(size_t)k0 * n + k0] == 0.0) {
                 sw = k0;
@@ -73,7 +86,7 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
             flag[0] = sw;
         }
         __syncthreads();
-        const int sw = flag[0];
+        const int sw = kPartial ? -1 : flag[0];
         if (sw > k0) {  // std::swap(a[k0], a[sw]); std::swap(b[k0], b[sw])  (:106-109)
             for (int j = k0 + tid; j <= n; j += kGjThreads) {
                 double *p0 = (j < n) ? &a[(size_t)k0 * n + j] : &bx[k0];
@@ -94,8 +107,55 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
         int Kp = K;
         for (int q = 0; q < K; ++q) {
             const int k = k0 + q;
+            if (kPartial) {
+                // r = first row >= k with the largest |a[i][k]|; key = (|v| bits, ~i): max wins
+                unsigned long long key = 0ull;
+                int best = k;
+                for (int i = k + tid; i < n; i += kGjThreads) {
+                    const unsigned long long m =
+                        (unsigned long long)__double_as_longlong(fabs(P[(size_t)i * kGjPS + q]));
+                    if (m > key || (m == key && i < best)) {
+                        key = m;
+                        best = i;
+                    }
+                }
+                if (k + tid >= n) best = 0x7fffffff;
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) {
+                    const unsigned long long ok = __shfl_down_sync(0xffffffffu, key, off);
+                    const int ob = __shfl_down_sync(0xffffffffu, best, off);
+                    if (ok > key || (ok == key && ob < best)) {
+                        key = ok;
+                        best = ob;
+                    }
+                }
+                if ((tid & 31) == 0) {
+                    wkey[tid >> 5] = key;
+                    widx[tid >> 5] = best;
+                }
+                __syncthreads();
+                int r = widx[0];
+                {
+                    unsigned long long bk = wkey[0];
+                    for (int w = 1; w < kGjThreads / 32; ++w) {
+                        const unsigned long long ok = wkey[w];
+                        const int ob = widx[w];
+                        if (ok > bk || (ok == bk && ob < r)) {
+                            bk = ok;
+                            r = ob;
+                        }
+                    }
+                }
+                if (tid == 0) perm[q] = r;
+                if (r != k && tid < K) {  // the whole panel row moves, earlier scales included
+                    const double t = P[(size_t)k * kGjPS + tid];
+                    P[(size_t)k * kGjPS + tid] = P[(size_t)r * kGjPS + tid];
+                    P[(size_t)r * kGjPS + tid] = t;
+                }
+                __syncthreads();
+            }
             const double value = P[(size_t)k * kGjPS + q];
-            if (q > 0 && value == 0.0) {  // needs a row swap: finish this panel at q pivots
+            if (!kPartial && q > 0 && value == 0.0) {  // needs a row swap: finish this panel at q pivots
                 Kp = q;
                 break;
             }
@@ -127,6 +187,16 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
         for (int j = jfirst + tid; j <= n; j += kGjThreads) {
             double *col = (j < n) ? (a + j) : bx;
             const size_t cs = (j < n) ? (size_t)n : 1;  // element stride down the column
+            if (kPartial) {  // replay the panel's row exchanges on this column, in order
+                for (int q = 0; q < Kp; ++q) {
+                    const int r = perm[q];
+                    if (r != k0 + q) {
+                        const double t = col[(size_t)(k0 + q) * cs];
+                        col[(size_t)(k0 + q) * cs] = col[(size_t)r * cs];
+                        col[(size_t)r * cs] = t;
+                    }
+                }
+            }
             double R[kGjK];
 #pragma unroll
             for (int q = 0; q < kGjK; ++q) {
@@ -224,30 +294,59 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
 
 using namespace lpb;
 
+static inline int gj_smem_bytes(int n) { return n * kGjPS * 8 + 288; }  // panel + flag, perm, argmax slots
+
+static int gj_launch(int B, int n, double *wa, double *x, int pivoting, const DeviceInfo &di, cudaStream_t stream)
+{
+    const int smem = gj_smem_bytes(n);
+    if (smem > di.max_smem_optin) {
+        set_error("lpb200_gauss_jordan_batch: n too large for the shared-memory panel (n <= " +
+                  std::to_string((di.max_smem_optin - 288) / (kGjPS * 8)) + ")");
+        return LPB200_E_TOO_LARGE;
+    }
+    if (pivoting == LPB200_PIVOT_PARTIAL) {
+        LPB_CUDA(cudaFuncSetAttribute(gauss_jordan_batched_kernel<true>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        gauss_jordan_batched_kernel<true><<<B, kGjThreads, smem, stream>>>(n, wa, x);
+    } else {
+        LPB_CUDA(cudaFuncSetAttribute(gauss_jordan_batched_kernel<false>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        gauss_jordan_batched_kernel<false><<<B, kGjThreads, smem, stream>>>(n, wa, x);
+    }
+    LPB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+static int gj_check(int B, int n, int pivoting)
+{
+    if (B < 0 || n < 0) {
+        set_error("lpb200_gauss_jordan_batch: need B >= 0 and n >= 0");
+        return LPB200_E_INVALID;
+    }
+    if (pivoting != LPB200_PIVOT_REFERENCE && pivoting != LPB200_PIVOT_PARTIAL) {
+        set_error("lpb200_gauss_jordan_batch: pivoting must be LPB200_PIVOT_REFERENCE or LPB200_PIVOT_PARTIAL");
+        return LPB200_E_INVALID;
+    }
+    return 0;
+}
+
 extern "C" int64_t lpb200_gauss_jordan_workspace_bytes(int B, int n)
 {
     if (B < 0 || n < 0) return 0;
     return (int64_t)B * n * n * 8;
 }
 
-extern "C" int lpb200_gauss_jordan_batch_device(int B, int n, const double *a, const double *b, double *x,
-                                                void *workspace, int64_t workspace_bytes, void *stream_v)
+extern "C" int lpb200_gauss_jordan_batch_ex_device(int B, int n, const double *a, const double *b, double *x,
+                                                   int pivoting, void *workspace, int64_t workspace_bytes,
+                                                   void *stream_v)
 {
-    if (B < 0 || n < 0) {
-        set_error("lpb200_gauss_jordan_batch: need B >= 0 and n >= 0");
-        return LPB200_E_INVALID;
-    }
+    int rc = gj_check(B, n, pivoting);
+    if (rc) return rc;
     if (B == 0 || n == 0) return 0;  // size 0 prints nothing (week-2/energy_values/tests/01)
     cudaStream_t stream = (cudaStream_t)stream_v;
     DeviceInfo di;
-    int rc = get_device_info(&di);
+    rc = get_device_info(&di);
     if (rc) return rc;
-    const int smem = n * kGjPS * 8 + 16;
-    if (smem > di.max_smem_optin) {
-        set_error("lpb200_gauss_jordan_batch: n too large for the shared-memory panel (n <= " +
-                  std::to_string((di.max_smem_optin - 16) / (kGjPS * 8)) + ")");
-        return LPB200_E_TOO_LARGE;
-    }
     if (workspace == nullptr || workspace_bytes < lpb200_gauss_jordan_workspace_bytes(B, n)) {
         set_error("lpb200_gauss_jordan_batch: workspace too small");
         return LPB200_E_INVALID;
@@ -255,21 +354,24 @@ extern "C" int lpb200_gauss_jordan_batch_device(int B, int n, const double *a, c
     double *wa = static_cast<double *>(workspace);
     LPB_CUDA(cudaMemcpyAsync(wa, a, (size_t)B * n * n * 8, cudaMemcpyDeviceToDevice, stream));
     if (x != b) LPB_CUDA(cudaMemcpyAsync(x, b, (size_t)B * n * 8, cudaMemcpyDeviceToDevice, stream));
-    LPB_CUDA(cudaFuncSetAttribute(gauss_jordan_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    gauss_jordan_batched_kernel<<<B, kGjThreads, smem, stream>>>(n, wa, x);
-    LPB_CUDA(cudaGetLastError());
-    return 0;
+    return gj_launch(B, n, wa, x, pivoting, di, stream);
 }
 
-extern "C" int lpb200_gauss_jordan_batch(int B, int n, const double *a, const double *b, double *x)
+extern "C" int lpb200_gauss_jordan_batch_device(int B, int n, const double *a, const double *b, double *x,
+                                                void *workspace, int64_t workspace_bytes, void *stream_v)
 {
-    if (B < 0 || n < 0) {
-        set_error("lpb200_gauss_jordan_batch: need B >= 0 and n >= 0");
-        return LPB200_E_INVALID;
-    }
+    return lpb200_gauss_jordan_batch_ex_device(B, n, a, b, x, LPB200_PIVOT_REFERENCE, workspace, workspace_bytes,
+                                               stream_v);
+}
+
+extern "C" int lpb200_gauss_jordan_batch_ex(int B, int n, const double *a, const double *b, double *x,
+                                            int pivoting)
+{
+    int rc = gj_check(B, n, pivoting);
+    if (rc) return rc;
     if (B == 0 || n == 0) return 0;
     DeviceInfo di;
-    int rc = get_device_info(&di);
+    rc = get_device_info(&di);
     if (rc) return rc;
     double *da = nullptr, *dx = nullptr;
     const size_t na = (size_t)B * n * n * 8, nx = (size_t)B * n * 8;
@@ -280,22 +382,14 @@ extern "C" int lpb200_gauss_jordan_batch(int B, int n, const double *a, const do
     rc = 0;
     if ((e = cudaMemcpy(da, a, na, cudaMemcpyHostToDevice)) != cudaSuccess) rc = cuda_fail(e, "cudaMemcpy(a)");
     if (!rc && (e = cudaMemcpy(dx, b, nx, cudaMemcpyHostToDevice)) != cudaSuccess) rc = cuda_fail(e, "cudaMemcpy(b)");
-    if (!rc) {
-        const int smem = n * kGjPS * 8 + 16;
-        if (smem > di.max_smem_optin) {
-            set_error("lpb200_gauss_jordan_batch: n too large for the shared-memory panel");
-            rc = LPB200_E_TOO_LARGE;
-        }
-        if (!rc && (e = cudaFuncSetAttribute(gauss_jordan_batched_kernel,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess)
-            rc = cuda_fail(e, "cudaFuncSetAttribute");
-        if (!rc) {
-            gauss_jordan_batched_kernel<<<B, kGjThreads, smem, 0>>>(n, da, dx);
-            if ((e = cudaGetLastError()) != cudaSuccess) rc = cuda_fail(e, "gauss_jordan_batched_kernel");
-        }
-    }
+    if (!rc) rc = gj_launch(B, n, da, dx, pivoting, di, 0);
     if (!rc && (e = cudaMemcpy(x, dx, nx, cudaMemcpyDeviceToHost)) != cudaSuccess) rc = cuda_fail(e, "cudaMemcpy(x)");
     cudaFree(da);
     cudaFree(dx);
     return rc;
+}
+
+extern "C" int lpb200_gauss_jordan_batch(int B, int n, const double *a, const double *b, double *x)
+{
+    return lpb200_gauss_jordan_batch_ex(B, n, a, b, x, LPB200_PIVOT_REFERENCE);
 }

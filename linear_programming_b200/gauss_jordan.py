@@ -19,9 +19,19 @@ def _is_torch_cuda(t) -> bool:
     return type(t).__module__.startswith("torch") and getattr(t, "is_cuda", False)
 
 
-def solve_equation_batch(a, b):
+PIVOT_REFERENCE, PIVOT_PARTIAL = 0, 1
+_PIVOTING = {"reference": PIVOT_REFERENCE, "partial": PIVOT_PARTIAL}
+
+
+def solve_equation_batch(a, b, pivoting: str = "reference"):
     """a[B,n,n], b[B,n] -> x[B,n].  numpy in -> numpy out (host path); CUDA float64 torch
-    tensors in -> CUDA tensor out (zero-copy, current stream).  Inputs are not modified."""
+    tensors in -> CUDA tensor out (zero-copy, current stream).  Inputs are not modified.
+    pivoting: "reference" = the reference's rule (diagonal pivot, swap on an exact zero only,
+    energy_values.cc:85-114); "partial" = largest |a[i][k]| in the column (not reference
+    behaviour; for ill-conditioned systems)."""
+    if pivoting not in _PIVOTING:
+        raise ValueError("pivoting must be 'reference' or 'partial'")
+    pv = _PIVOTING[pivoting]
     L = _lib.lib()
     if _is_torch_cuda(a):
         import torch
@@ -36,8 +46,8 @@ def solve_equation_batch(a, b):
             wsb = int(L.lpb200_gauss_jordan_workspace_bytes(B, n))
             ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=a.device)
             stream = torch.cuda.current_stream(a.device).cuda_stream
-            _lib.check(L.lpb200_gauss_jordan_batch_device(B, n, a.data_ptr(), b.data_ptr(), x.data_ptr(),
-                                                          ws.data_ptr(), wsb, stream))
+            _lib.check(L.lpb200_gauss_jordan_batch_ex_device(B, n, a.data_ptr(), b.data_ptr(), x.data_ptr(), pv,
+                                                             ws.data_ptr(), wsb, stream))
         return x
     a = np.ascontiguousarray(a, dtype=np.float64)
     b = np.ascontiguousarray(b, dtype=np.float64)
@@ -45,19 +55,19 @@ def solve_equation_batch(a, b):
         raise ValueError("expected a[B,n,n], b[B,n]")
     B, n = b.shape
     x = np.zeros((B, n), dtype=np.float64)
-    _lib.check(L.lpb200_gauss_jordan_batch(B, n, ctypes.c_void_p(a.ctypes.data), ctypes.c_void_p(b.ctypes.data),
-                                           ctypes.c_void_p(x.ctypes.data)))
+    _lib.check(L.lpb200_gauss_jordan_batch_ex(B, n, ctypes.c_void_p(a.ctypes.data), ctypes.c_void_p(b.ctypes.data),
+                                              ctypes.c_void_p(x.ctypes.data), pv))
     return x
 
 
-def solve_equation(a, b):
+def solve_equation(a, b, pivoting: str = "reference"):
     """SolveEquation (energy_values.cc:166): one square system, returns the solution column."""
     b = np.asarray(b, dtype=np.float64).reshape(-1)
     n = b.shape[0]
     if n == 0:
         return np.zeros(0, dtype=np.float64)
     a = np.asarray(a, dtype=np.float64).reshape(n, n)
-    return solve_equation_batch(a[None], b[None])[0]
+    return solve_equation_batch(a[None], b[None], pivoting=pivoting)[0]
 
 
 def read_equation(text: str):

@@ -76,6 +76,11 @@ def lib():
         L.lp_oracle_gauss_jordan_batch.restype = ctypes.c_int
         L.lp_oracle_gauss_jordan_batch.argtypes = [ctypes.c_int, ctypes.c_int, _dp, _dp, _dp,
                                                    ctypes.c_int, ctypes.c_int]
+        L.lp_oracle_gauss_jordan_pivot.restype = None
+        L.lp_oracle_gauss_jordan_pivot.argtypes = [ctypes.c_int, _dp, _dp, _dp, ctypes.c_int, ctypes.c_int]
+        L.lp_oracle_gauss_jordan_batch_pivot.restype = ctypes.c_int
+        L.lp_oracle_gauss_jordan_batch_pivot.argtypes = [ctypes.c_int, ctypes.c_int, _dp, _dp, _dp,
+                                                         ctypes.c_int, ctypes.c_int, ctypes.c_int]
         L.lp_oracle_pyset_replay.restype = ctypes.c_int
         L.lp_oracle_pyset_replay.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int, _ip, _ip, _ip]
         _lib = L
@@ -132,20 +137,24 @@ def simplex_batch(A, b, c, tol: float = 1e-9, max_pivots: int = 1_000_000, threa
     return status, x, obj, npiv, int(used)
 
 
-def gauss_jordan(a, b, full_sweep: bool = True):
+PIVOTING = {"reference": 0, "partial": 1}
+
+
+def gauss_jordan(a, b, full_sweep: bool = True, pivoting: str = "reference"):
     a, b = _d(a), _d(b)
     n = b.shape[0]
     x = np.zeros(n)
     if n:
-        lib().lp_oracle_gauss_jordan(n, _p(a), _p(b), _p(x), int(full_sweep))
+        lib().lp_oracle_gauss_jordan_pivot(n, _p(a), _p(b), _p(x), int(full_sweep), PIVOTING[pivoting])
     return x
 
 
-def gauss_jordan_batch(a, b, full_sweep: bool = False, threads: int = 0):
+def gauss_jordan_batch(a, b, full_sweep: bool = False, threads: int = 0, pivoting: str = "reference"):
     a, b = _d(a), _d(b)
     B, n = b.shape
     x = np.zeros((B, n))
-    used = lib().lp_oracle_gauss_jordan_batch(B, n, _p(a), _p(b), _p(x), int(full_sweep), threads)
+    used = lib().lp_oracle_gauss_jordan_batch_pivot(B, n, _p(a), _p(b), _p(x), int(full_sweep),
+                                                    PIVOTING[pivoting], threads)
     return x, int(used)
 
 

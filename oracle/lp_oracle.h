@@ -92,6 +92,14 @@ int lp_oracle_simplex_batch(int B, int n, int m, const double *A, const double *
 void lp_oracle_gauss_jordan(int n, const double *a, const double *b, double *x, int full_sweep);
 int lp_oracle_gauss_jordan_batch(int B, int n, const double *a, const double *b, double *x,
                                  int full_sweep, int threads);
+/* The same with a pivot rule: LP_PIVOT_REFERENCE as above, LP_PIVOT_PARTIAL = largest |a[i][k]|
+ * of the column (not reference behaviour; see gauss_jordan_oracle.c). */
+#define LP_PIVOT_REFERENCE 0
+#define LP_PIVOT_PARTIAL 1
+void lp_oracle_gauss_jordan_pivot(int n, const double *a, const double *b, double *x, int full_sweep,
+                                  int pivoting);
+int lp_oracle_gauss_jordan_batch_pivot(int B, int n, const double *a, const double *b, double *x,
+                                       int full_sweep, int pivoting, int threads);
 
 #ifdef __cplusplus
 }
