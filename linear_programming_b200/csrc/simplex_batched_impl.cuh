@@ -22,7 +22,8 @@ typedef int16_t tab_t;
 // Shared-memory carve-up, computed on the host and passed by value.
 struct BatchShape {
     int n, m;
-    int S;        // tableau row stride in doubles (even): 1 constant + m + 1 auxiliary, rounded up
+    int S;        // tableau row stride in doubles (even): 1 constant + m + 1 auxiliary, rounded up, + padding
+    int npairs;   // column pairs the sweep covers = ceil((m + 2) / 2); the padding is never touched
     int cx;       // lanes across column pairs in the sweep (<= 64)
     int groups;   // row groups = 256 / cx
     int rpg;      // physical rows per row group (multiple of kRowChunk)
@@ -46,8 +47,10 @@ static BatchShape make_batch_shape(int n, int m)
     BatchShape s;
     s.n = n;
     s.m = m;
-    s.S = align_up(m + 2, 2);
-    const int npairs = s.S / 2;
+    const int W = align_up(m + 2, 2);
+    const int npairs = W / 2;
+    s.npairs = npairs;
+    s.S = W;
     const int passes = (npairs + 63) / 64;          // column pairs per lane (wide tableaus loop)
     s.cx = (npairs + passes - 1) / passes;           // lanes across column pairs: 51 at m = 100
     const int nphys = n + 2;  // n basic rows + objective row + one spare slot
@@ -55,6 +58,7 @@ static BatchShape make_batch_shape(int n, int m)
     s.rpg = align_up((nphys + s.groups - 1) / s.groups, kRowChunk);
     s.rpt = (nphys + s.groups - 1) / s.groups;
     s.nfc = s.groups * s.rpg + kRowChunk;
+    if (const char *g = getenv("LPB_DEBUG_SPAD")) s.S = W + 2 * (atoi(g) / 2);
     s.size_i0 = pyset_initial_size(m);
     s.size_i1 = pyset_initial_size(m + 1);
     s.size_d0 = pyset_initial_size(n);
@@ -116,7 +120,7 @@ struct Ctx {
     unsigned *redu32;
     int *misc;
     tab_t *tab_i, *tab_d, *tab_s;
-    int n, m, S, cx, rpg, rpt;
+    int n, m, S, npairs, cx, rpg, rpt;
     int cxi, row0, row1;  // this thread's column-pair lane and physical row block [row0, row1)
     int spare;  // physical row slot currently unused (uniform across the CTA)
     double tol;
@@ -354,7 +358,7 @@ __device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, 
     if (tid < kSweepThreads) {
         unsigned mykey = 0xffffffffu;
         if (c.row0 < c.row1) {
-            const int npairs = S >> 1;
+            const int npairs = c.npairs;
             const double2 *Tsrc = reinterpret_cast<const double2 *>(c.T + (size_t)src * S);
             const uint32_t tbase = (uint32_t)__cvta_generic_to_shared(c.T);
             const uint32_t rsb = (uint32_t)S * 8u;  // row stride in bytes
@@ -861,6 +865,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
     c.n = n;
     c.m = m;
     c.S = S;
+    c.npairs = sh.npairs;
     c.cx = sh.cx;
     c.rpg = sh.rpg;
     c.rpt = sh.rpt;
@@ -1206,7 +1211,7 @@ static bool eligible(int n, int m)
 {
 #if LPB_REG_ROWS > 0
     const BatchShape s = make_batch_shape(n, m);
-    return (s.S / 2) <= 64 && s.rpt <= LPB_REG_ROWS;
+    return s.npairs <= 64 && s.rpt <= LPB_REG_ROWS;
 #else
     (void)n;
     (void)m;

@@ -273,3 +273,48 @@ def test_bland_rule_random_batches_vs_oracle(oracle_lib, dist, n, m, count):
     assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
     assert np.array_equal(res.objective.view(np.int64), obj.view(np.int64))
     assert set(int(s) for s in st) <= {0, -1, 1}
+
+
+@pytest.mark.parametrize("n,m,count", [(1, 1, 64), (1, 7, 64), (7, 1, 64), (2, 129, 32), (129, 2, 32), (3, 255, 16),
+                                       (160, 160, 4), (100, 250, 4), (250, 100, 4), (20, 1000, 4)])
+@pytest.mark.parametrize("rule", ["reference", "bland"])
+def test_edge_shapes_vs_oracle(oracle_lib, n, m, count, rule):
+    """Degenerate and extreme shapes of the one-CTA-per-LP kernel: a single row or column, odd widths,
+    more than 64 column pairs (lanes loop), and the largest tableaus shared memory holds (one CTA/SM)."""
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    assert lp.simplex.fits_batch_kernel(n, m)
+    A, b, c = workloads.simplex_batch("D3", count, n, m, seed=21)
+    cap = 30000
+    res = lp.solve_batch(A, b, c, max_pivots=cap, log_cap=32, mode="batch", rule=rule)
+    st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=cap, rule=rule)
+    assert np.array_equal(res.status, st)
+    assert np.array_equal(res.npivots, npiv)
+    assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
+    assert np.array_equal(res.objective.view(np.int64), obj.view(np.int64))
+
+
+def test_auto_mode_falls_back_to_the_grid_wide_kernel_when_smem_is_too_small(oracle_lib):
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    n = m = 166
+    assert not lp.simplex.fits_batch_kernel(n, m)
+    A, b, c = workloads.simplex_batch("D1", 2, n, m, seed=22)
+    res = lp.solve_batch(A, b, c, max_pivots=400)
+    st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=400)
+    assert np.array_equal(res.status, st) and np.array_equal(res.npivots, npiv)
+    assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
+    with pytest.raises(lp.EngineError):
+        lp.solve_batch(A, b, c, mode="batch")
+
+
+def test_empty_batch_and_bad_arguments():
+    import linear_programming_b200 as lp
+    res = lp.solve_batch(np.zeros((0, 3, 4)), np.zeros((0, 3)), np.zeros((0, 4)))
+    assert res.status.shape == (0,) and res.x.shape == (0, 4)
+    with pytest.raises(ValueError):
+        lp.solve_batch(np.zeros((2, 3, 4)), np.zeros((2, 4)), np.zeros((2, 4)))
+    with pytest.raises(ValueError):
+        lp.solve_batch(np.zeros((1, 3, 4)), np.zeros((1, 3)), np.zeros((1, 4)), rule="dantzig")
+    with pytest.raises(lp.EngineError):
+        lp.solve_batch(np.zeros((1, 3, 4)), np.zeros((1, 3)), np.zeros((1, 4)), tol=-1.0)
