@@ -147,7 +147,10 @@ def solve_equation_stream(text: str) -> str:
 def main(argv=None) -> int:
     argv = list(sys.argv[1:] if argv is None else argv)
     stream = "--stream" in argv
-    rule = "bland" if "--rule=bland" in argv else "reference"
+    rule = "reference"
+    for t in argv:
+        if t.startswith("--rule="):
+            rule = t.split("=", 1)[1]
     argv = [t for t in argv if t != "--stream" and not t.startswith("--rule=")]
     prog = argv[0] if argv else "simplex"
     if prog not in ("simplex", "ad_allocation", "diet", "energy_values"):

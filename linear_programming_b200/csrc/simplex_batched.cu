@@ -44,39 +44,52 @@
 #define LPB_SWEEP_WARPS 8
 #define LPB_REG_ROWS 0
 #define LPB_MIN_BLOCKS 2
-#define LPB_RULE_BLAND 0
+#define LPB_RULE 0
 #include "simplex_batched_impl.cuh"
 #undef LPB_NS
 #undef LPB_SWEEP_WARPS
 #undef LPB_REG_ROWS
 #undef LPB_MIN_BLOCKS
-#undef LPB_RULE_BLAND
+#undef LPB_RULE
 
 #define LPB_NS reg15
 #define LPB_SWEEP_WARPS 15
 #define LPB_REG_ROWS 12
 #define LPB_MIN_BLOCKS 1
-#define LPB_RULE_BLAND 0
+#define LPB_RULE 0
 #include "simplex_batched_impl.cuh"
 #undef LPB_NS
 #undef LPB_SWEEP_WARPS
 #undef LPB_REG_ROWS
 #undef LPB_MIN_BLOCKS
-#undef LPB_RULE_BLAND
+#undef LPB_RULE
 
 // the corrected (non-reference) mode, LPB200_RULE_BLAND: same kernel, other pivoting decisions
 #define LPB_NS bland8
 #define LPB_SWEEP_WARPS 8
 #define LPB_REG_ROWS 0
 #define LPB_MIN_BLOCKS 2
-#define LPB_RULE_BLAND 1
+#define LPB_RULE 1
 #include "simplex_batched_impl.cuh"
 #undef LPB_NS
 #undef LPB_SWEEP_WARPS
 #undef LPB_REG_ROWS
 #undef LPB_MIN_BLOCKS
-#undef LPB_RULE_BLAND
+#undef LPB_RULE
 
+
+// LPB200_RULE_DANTZIG: largest-coefficient pricing with a Bland fallback on degenerate streaks
+#define LPB_NS dantzig8
+#define LPB_SWEEP_WARPS 8
+#define LPB_REG_ROWS 0
+#define LPB_MIN_BLOCKS 2
+#define LPB_RULE 2
+#include "simplex_batched_impl.cuh"
+#undef LPB_NS
+#undef LPB_SWEEP_WARPS
+#undef LPB_REG_ROWS
+#undef LPB_MIN_BLOCKS
+#undef LPB_RULE
 
 // ======================================================================================
 // Host side: C ABI
@@ -127,8 +140,8 @@ extern "C" int lpb200_simplex_batch_ex_device(int B, int n, int m, const void *A
         set_error("lpb200_simplex_batch: a_dtype must be one of LPB200_DTYPE_*");
         return LPB200_E_INVALID;
     }
-    if (rule != LPB200_RULE_REFERENCE && rule != LPB200_RULE_BLAND) {
-        set_error("lpb200_simplex_batch: rule must be LPB200_RULE_REFERENCE or LPB200_RULE_BLAND");
+    if (rule != LPB200_RULE_REFERENCE && rule != LPB200_RULE_BLAND && rule != LPB200_RULE_DANTZIG) {
+        set_error("lpb200_simplex_batch: rule must be one of LPB200_RULE_*");
         return LPB200_E_INVALID;
     }
     if (B == 0) return 0;
@@ -136,6 +149,9 @@ extern "C" int lpb200_simplex_batch_ex_device(int B, int n, int m, const void *A
     DeviceInfo di;
     rc = get_device_info(&di);
     if (rc) return rc;
+    if (rule == LPB200_RULE_DANTZIG)
+        return dantzig8::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots,
+                                pivot_log, log_cap, stream);
     if (rule == LPB200_RULE_BLAND)
         return bland8::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots,
                               pivot_log, log_cap, stream);

@@ -12,6 +12,14 @@
 namespace lpb {
 namespace LPB_NS {
 
+// LPB_RULE: 0 = the reference's decisions (parity), 1 = Bland, 2 = Dantzig with Bland fallback.
+// Everything that differs from the reference is compiled in only when LPB_CORRECTED.
+#undef LPB_CORRECTED
+#define LPB_CORRECTED (LPB_RULE != 0)
+constexpr unsigned long long kKeyZeroRatio = 0x8000000000000000ull;  // order_key(+0.0)
+constexpr int kDegenerateStreak = 8;  // Dantzig: degenerate pivots in a row before Bland takes over
+
+
 constexpr int kSweepWarps = LPB_SWEEP_WARPS;
 constexpr int kSweepThreads = kSweepWarps * 32;  // 256
 constexpr int kThreads = kSweepThreads + 32;     // + bookkeeping warp
@@ -128,7 +136,7 @@ struct Ctx {
     unsigned long long *timing;
 };
 
-#if LPB_RULE_BLAND
+#if LPB_CORRECTED
 // Column to pivot a still-basic x_aux out on after phase 1: the non-basic variable with the lowest
 // id whose entry in physical row r is non-zero; -1 when the row is all zero.
 __device__ __forceinline__ int driveout_column(const Ctx &c, int ncols, int r)
@@ -173,6 +181,52 @@ __device__ __forceinline__ int select_entering(const Ctx &c, int ncols)
     return best == 0xffffffffu ? -1 : (int)(best & 0xffffu);
 }
 
+#if LPB_RULE == 2
+// Dantzig pricing: the column with the LARGEST objective coefficient > tol enters, ties -> lowest
+// variable id; with bland_now (a run of degenerate pivots) the lowest id with a positive
+// coefficient, which cannot cycle.  Stand-alone pass over the objective row after every sweep.
+__device__ __forceinline__ int select_entering_dantzig(const Ctx &c, int ncols, bool bland_now)
+{
+    const int tid = threadIdx.x;
+    if (tid < kSweepThreads) {
+        unsigned long long key = kKeyNone;
+        int id = 0x7fffffff;
+        const double *obj = c.T + (size_t)c.n * c.S + 1;
+        for (int k = tid; k < ncols; k += kSweepThreads) {
+            const double v = obj[k];
+            if (v > c.tol) {
+                // positive doubles order like their bit patterns: ~bits makes the largest the minimum
+                const unsigned long long kk = bland_now ? 0ull : ~(unsigned long long)__double_as_longlong(v);
+                const int ii = (c.colvar[k] << 16) | k;
+                if (kk < key || (kk == key && ii < id)) {
+                    key = kk;
+                    id = ii;
+                }
+            }
+        }
+        warp_argmin(key, id);
+        if ((tid & 31) == 0) {
+            c.redkey[2 * (tid >> 5)] = key;  // redkey[] is 16 bytes per warp (RatioPartial)
+            c.redvar[tid >> 5] = id;
+        }
+    }
+    __syncthreads();
+    unsigned long long best = c.redkey[0];
+    int bid = c.redvar[0];
+#pragma unroll
+    for (int w = 1; w < kSweepWarps; ++w) {
+        const unsigned long long k = c.redkey[2 * w];
+        const int v = c.redvar[w];
+        if (k < best || (k == best && v < bid)) {
+            best = k;
+            bid = v;
+        }
+    }
+    __syncthreads();  // redkey/redvar are rewritten by the next ratio test
+    return bid == 0x7fffffff ? -1 : (bid & 0xffff);
+}
+#endif
+
 // ---- step 1: stage the pivot column, min-ratio test with the reference's degenerate skip (:394-436) ----
 // One thread per physical row: fc[i] = snapped T[i][1+p]; the entry is zeroed in place (the
 // column now belongs to the leaving variable, whose coefficient starts from None, :187 opt).
@@ -187,7 +241,8 @@ struct __align__(16) RatioPartial {
     int pad;
 };
 
-__device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool forced)
+__device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool forced,
+                                               unsigned long long *best_key = nullptr)
 {
     const int tid = threadIdx.x;
     const int nphys = c.n + 2;
@@ -212,7 +267,7 @@ __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool 
             c.fc[i] = f;
             if (v >= 0) {
                 const int nc = c.nonecol[i];
-#if !LPB_RULE_BLAND
+#if !LPB_CORRECTED
                 crash |= (nc == kNoneInitial && e_is_slack) || (nc == e) || (c.untouched[i] && e_in_basis0);
 #endif
                 if (f != 0.0) {  // row is rewritten by this pivot: its only None is column e
@@ -224,7 +279,7 @@ __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool 
                 if (cand || (forced && f != 0.0)) c.pinvs[i] = pivot_inverse(f, c.tol);
                 if (cand) {
                     const double ratio = snap(__ddiv_rn(c.T[(size_t)i * c.S], coeff), c.tol);
-                    if (ratio != 0.0 || LPB_RULE_BLAND) {  // zero ratios count as +inf in min_index (:161)
+                    if (ratio != 0.0 || LPB_CORRECTED) {  // zero ratios count as +inf in min_index (:161)
                         const unsigned long long k = order_key(ratio);
                         const int vi = (v << 16) | i;  // ties -> lowest variable id (rows are unique per id)
                         if (k < key || (k == key && vi < var)) {
@@ -255,6 +310,7 @@ __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool 
         const RatioPartial r = part[w];
         if (r.key < best.key || (r.key == best.key && r.id < best.id)) best = r;
     }
+    if (best_key) *best_key = best.key;
     return best.key == kKeyNone ? -1 : best.id;
 }
 
@@ -289,7 +345,7 @@ __device__ __forceinline__ void bookkeeping(const Ctx &c, int p, int src, int de
         c.misc[MI_DFILL] = d.fill;
         c.misc[MI_DUSED] = d.used;
     }
-#if LPB_RULE_BLAND
+#if LPB_CORRECTED
     (void)eslot;
     c.colslot[p] = l;  // Bland: the entering priority of a column is the id of its variable
 #else
@@ -509,7 +565,7 @@ __device__ __forceinline__ int ratio_staged(const Ctx &c, int e, bool forced)
             }
             if (v >= 0) {
                 const int nc = c.nonecol[i];
-#if !LPB_RULE_BLAND
+#if !LPB_CORRECTED
                 crash |= (nc == kNoneInitial && e_is_slack) || (nc == e) || (c.untouched[i] && e_in_basis0);
 #endif
                 if (f != 0.0) {
@@ -521,7 +577,7 @@ __device__ __forceinline__ int ratio_staged(const Ctx &c, int e, bool forced)
                 if (cand || (forced && f != 0.0)) c.pinvs[i] = pivot_inverse(f, c.tol);
                 if (cand) {
                     const double ratio = snap(__ddiv_rn(c.bcol[i], coeff), c.tol);
-                    if (ratio != 0.0 || LPB_RULE_BLAND) {
+                    if (ratio != 0.0 || LPB_CORRECTED) {
                         const unsigned long long k = order_key(ratio);
                         const int vi = (v << 16) | i;
                         if (k < key || (k == key && vi < var)) {
@@ -707,7 +763,13 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
                                         int log_cap, int forced_p, int forced_lr)
 {
     bool forced = forced_lr >= 0;
+#if LPB_RULE == 2
+    int streak = 0;  // degenerate pivots in a row (uniform across the CTA)
+    unsigned long long best_key = 0ull;
+    int p = forced ? forced_p : select_entering_dantzig(c, ncols, false);
+#else
     int p = forced ? forced_p : select_entering(c, ncols);
+#endif
 #ifdef LPB_TIMING
     const bool tm = (c.timing != nullptr) && ((threadIdx.x & 31) == 0);
     unsigned long long acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
@@ -719,7 +781,12 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
         long long t0 = clock64(), t1, t2 = 0, t3;
 #endif
         const int e = c.colvar[p];
+#if LPB_RULE == 2
+        int lr = stage_and_ratio(c, p, e, forced, &best_key);
+        if (!forced) streak = (best_key == kKeyZeroRatio) ? streak + 1 : 0;
+#else
         int lr = stage_and_ratio(c, p, e, forced);
+#endif
 #ifdef LPB_TIMING
         t1 = clock64();
 #endif
@@ -736,12 +803,17 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
         sweep(c, ncols, p, src, e, l, log, log_cap, npiv);
 #endif
         ++npiv;
+#if LPB_RULE == 2
+        forced = false;
+        p = select_entering_dantzig(c, ncols, streak > kDegenerateStreak);
+#else
         if (forced) {
             forced = false;
             p = select_entering(c, ncols);
         } else {
             p = next_entering(c, ncols);
         }
+#endif
     }
 #ifdef LPB_TIMING
     // [warp][0]=stage incl. barrier, [1]=own sweep work, [2]=sweep incl. barrier, [3]=pivots
@@ -916,7 +988,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
             int idx = 0x7fffffff;
             for (int i = tid; i < n; i += kSweepThreads) {
                 const double bi = gb[i];
-                const unsigned long long k = order_key((bi != 0.0 || LPB_RULE_BLAND) ? bi : CUDART_INF);
+                const unsigned long long k = order_key((bi != 0.0 || LPB_CORRECTED) ? bi : CUDART_INF);
                 if (k < key || (k == key && i < idx)) {
                     key = k;
                     idx = i;
@@ -947,7 +1019,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
         int status = 0;
         int npiv = 0;
         int ncols = phase1 ? m + 1 : m;
-        if (!LPB_RULE_BLAND && !phase1 && !(min_c > tol)) status = LPB200_STATUS_REF_ATTRIBUTE_ERROR;  // :626
+        if (!LPB_CORRECTED && !phase1 && !(min_c > tol)) status = LPB200_STATUS_REF_ATTRIBUTE_ERROR;  // :626
         c.track_dep = phase1;
         c.spare = n + 1;
 
@@ -982,7 +1054,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                 for (int k = tid; k <= m; k += kSweepThreads) {
                     c.colvar[k] = n + k;
                     c.varpos[n + k] = k;
-                    c.colslot[k] = LPB_RULE_BLAND ? (n + k) : ((n + k) & (isize - 1));
+                    c.colslot[k] = LPB_CORRECTED ? (n + k) : ((n + k) & (isize - 1));
                 }
                 for (int w = tid; w < (nv + 31) / 32; w += kSweepThreads) c.basis0[w] = 0u;
             } else {
@@ -1022,7 +1094,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                 const int aux = n + m;
                 if (status == 0) {
                     if (!(fabs(c.T[(size_t)n * S]) <= tol)) status = LPB200_STATUS_NO_SOLUTION;  // :528-530
-#if LPB_RULE_BLAND
+#if LPB_CORRECTED
                     else if (c.varpos[aux] < 0) {
                         // x_aux is basic at level 0: pivot it out on the lowest-id column with a
                         // non-zero entry in its row; an all-zero row is a redundant constraint, left inert
@@ -1103,7 +1175,7 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
                         for (int k = tid; k < S; k += kSweepThreads) c.nr[k] = 0.0;
                         for (int i = tid; i < nfc; i += kSweepThreads) c.fc[i] = 0.0;  // list[] lived here
                     } else if (tid == kSweepThreads && kaux >= 0) {
-#if !LPB_RULE_BLAND
+#if !LPB_CORRECTED
                         PySet s = {c.misc[MI_ISIZE], c.misc[MI_IFILL], c.misc[MI_IUSED]};
                         pyset_remove_slot(c.tab_i, s, c.colslot[kaux]);  // independent.remove(nvars) (:574)
                         c.misc[MI_IUSED] = s.used;

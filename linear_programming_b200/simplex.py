@@ -87,15 +87,15 @@ def _a_dtype_code(dtype) -> int | None:
     return _TYPED_A.get(str(dtype).replace("torch.", ""))
 
 
-RULE_REFERENCE, RULE_BLAND = 0, 1
-_RULES = {"reference": RULE_REFERENCE, "bland": RULE_BLAND}
+RULE_REFERENCE, RULE_BLAND, RULE_DANTZIG = 0, 1, 2
+_RULES = {"reference": RULE_REFERENCE, "bland": RULE_BLAND, "dantzig": RULE_DANTZIG}
 
 
 def _rule_code(rule: str, mode: str) -> int:
     if rule not in _RULES:
-        raise ValueError("rule must be 'reference' or 'bland'")
+        raise ValueError("rule must be 'reference', 'bland' or 'dantzig'")
     if rule != "reference" and mode == "single":
-        raise ValueError("rule='bland' is served by the batch kernel only (mode='batch' or 'auto')")
+        raise ValueError("rule=%r is served by the batch kernel only (mode='batch' or 'auto')" % rule)
     return _RULES[rule]
 
 
@@ -109,7 +109,8 @@ def solve_batch(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None 
     reads it as is and widens on the GPU -- same answers, a fraction of the bytes over PCIe.
     rule: "reference" reproduces the reference bit for bit, bugs included; "bland" is the
     corrected mode (include/lp_b200.h LPB200_RULE_BLAND: Bland's rule, zero ratios kept, x_aux
-    driven out, no crash classes) -- not reference behaviour, batch kernel only.
+    driven out, no crash classes) and "dantzig" the same with largest-coefficient pricing (far
+    fewer pivots; Bland takes over on degenerate streaks) -- not reference behaviour, batch kernel only.
     mode: "batch" (one CTA per LP, tableau in shared memory), "single" (grid-wide kernel, one
     LP after the other), "auto" (batch when the tableau fits shared memory).
     """

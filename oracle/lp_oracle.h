@@ -70,6 +70,8 @@ int lp_oracle_simplex(int n, int m, const double *A, const double *b, const doub
  * corrected mode described at the top of simplex_oracle.c (not reference behaviour). */
 #define LP_RULE_REFERENCE 0
 #define LP_RULE_BLAND 1
+#define LP_RULE_DANTZIG 2 /* largest coefficient, Bland after LP_DEGENERATE_STREAK degenerate pivots in a row */
+#define LP_DEGENERATE_STREAK 8
 int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const double *c, double tol,
                            int max_pivots, int rule, double *x, double *objective, int32_t *npivots,
                            int32_t *pivot_log, int log_cap);

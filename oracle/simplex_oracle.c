@@ -33,6 +33,10 @@
  *   - x_aux still basic (at level 0) after phase 1 is pivoted out on the lowest-id non-basic
  *     variable with a non-zero coefficient in its row instead of raising IndexError (:541);
  *     if the row is all zero it is a redundant constraint: it stays, inert, and no column is dropped.
+ * rule = LP_RULE_DANTZIG is LP_RULE_BLAND with largest-coefficient pricing: entering = the column
+ * with the largest c[j] > tol (ties -> lowest id); once more than LP_DEGENERATE_STREAK pivots in a
+ * row (within one run of the loop) had a zero leaving ratio, Bland's entering choice is used until
+ * a pivot with a non-zero ratio happens.
  */
 #include <math.h>
 #include <stdlib.h>
@@ -62,6 +66,8 @@ typedef struct {
     double tol;
     int npiv, maxpiv;
     int rule;
+    int streak;     /* LP_RULE_DANTZIG: degenerate pivots in a row in the current loop */
+    int last_zero;  /* the ratio of the leaving row picked last was 0 */
     int32_t *log;
     int logcap;
     double *newrow;
@@ -146,7 +152,19 @@ static void do_pivot(lp_t *s, int e, int l)
 static int pick_entering(const lp_t *s)
 {
     const double *c = s->T + (size_t)s->n * s->stride;
-    if (s->rule == LP_RULE_BLAND) {
+    if (s->rule == LP_RULE_DANTZIG && s->streak <= LP_DEGENERATE_STREAK) {
+        int best = -1;
+        double bestv = 0.0;
+        for (int k = 0; k < s->ncols; ++k) {
+            const double v = c[1 + k];
+            if (v > s->tol && (best < 0 || v > bestv || (v == bestv && s->colvar[k] < best))) {
+                best = s->colvar[k];
+                bestv = v;
+            }
+        }
+        return best;
+    }
+    if (s->rule != LP_RULE_REFERENCE) {
         int best = -1;
         for (int k = 0; k < s->ncols; ++k)
             if (c[1 + k] > s->tol && (best < 0 || s->colvar[k] < best)) best = s->colvar[k];
@@ -160,10 +178,10 @@ static int pick_entering(const lp_t *s)
 }
 
 /* pick_leaving_idx, simplex.py:394-436.  Returns variable id, -1 = unbounded, -2 = TypeError. */
-static int pick_leaving(const lp_t *s, int e)
+static int pick_leaving(lp_t *s, int e)
 {
     const int n = s->n, S = s->stride, p = s->varpos[e];
-    const int bland = (s->rule == LP_RULE_BLAND);
+    const int bland = (s->rule != LP_RULE_REFERENCE); /* the corrected ratio test (both corrected rules) */
     for (int i = 0; i < n && !bland; ++i) { /* -1 * None at :409 */
         if ((s->none_col[i] == NONE_INITIAL && e < n) || s->none_col[i] == e ||
             (s->untouched[i] && s->basis0[e]))
@@ -184,18 +202,21 @@ static int pick_leaving(const lp_t *s, int e)
             bestr = ratio;
         }
     }
+    s->last_zero = (best >= 0 && bestr == 0.0);
     return best;
 }
 
 /* SlackForm.solve loop, simplex.py:442-466.  Returns 0 when no positive coefficient is left. */
 static int run_loop(lp_t *s)
 {
+    s->streak = 0;
     for (;;) {
         const int e = pick_entering(s);
         if (e < 0) return 0;
         const int l = pick_leaving(s, e);
         if (l == -2) return LP_STATUS_REF_TYPE_ERROR;
         if (l < 0) return LP_STATUS_INFINITY;
+        s->streak = s->last_zero ? s->streak + 1 : 0;
         if (s->npiv >= s->maxpiv) return LP_STATUS_ITERATION_LIMIT;
         do_pivot(s, e, l);
     }
@@ -242,7 +263,7 @@ int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const
     {
         double bestkey = INFINITY;
         for (int i = 0; i < n; ++i) {
-            const double key = (b[i] != 0.0 || rule == LP_RULE_BLAND) ? b[i] : INFINITY;
+            const double key = (b[i] != 0.0 || rule != LP_RULE_REFERENCE) ? b[i] : INFINITY;
             if (key < bestkey) {
                 bestkey = key;
                 idx = i;
@@ -251,7 +272,7 @@ int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const
     }
     const double min_c = b[idx];
     const int phase1 = (min_c < 0.0);
-    if (!phase1 && !(min_c > tol) && rule != LP_RULE_BLAND) { /* self.assignment undefined -> AttributeError, :626 */
+    if (!phase1 && !(min_c > tol) && rule == LP_RULE_REFERENCE) { /* self.assignment undefined -> AttributeError, :626 */
         status = LP_STATUS_REF_ATTRIBUTE_ERROR;
         goto done_noset;
     }
@@ -295,7 +316,7 @@ int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const
             status = LP_STATUS_NO_SOLUTION;
             goto done;
         }
-        if (s.isbasic[aux] && rule == LP_RULE_BLAND) { /* drive x_aux out of the basis */
+        if (s.isbasic[aux] && rule != LP_RULE_REFERENCE) { /* drive x_aux out of the basis */
             const double *Tr = s.T + (size_t)s.varpos[aux] * s.stride;
             int ev = -1;
             for (int k = 0; k < s.ncols; ++k)

@@ -233,7 +233,8 @@ def test_typed_device_tensor_and_golden_cases(simplex_golden):
     assert checked >= 400
 
 
-def test_bland_rule_stress_distribution_vs_oracle(oracle_lib):
+@pytest.mark.parametrize("rule", ["bland", "dantzig"])
+def test_bland_rule_stress_distribution_vs_oracle(oracle_lib, rule):
     """LPB200_RULE_BLAND (corrected mode): status, pivot sequence and x bit-identical to the CPU
     restatement of the same rule (itself checked against HiGHS in tests/test_oracle_bland.py),
     on the distribution whose zeros in b crash the reference; includes x_aux drive-outs."""
@@ -246,9 +247,9 @@ def test_bland_rule_stress_distribution_vs_oracle(oracle_lib):
     oracle_lib.driveouts(reset=True)
     for (n, m), lst in groups.items():
         A = np.stack([q[0] for q in lst]); b = np.stack([q[1] for q in lst]); c = np.stack([q[2] for q in lst])
-        res = lp.solve_batch(A, b, c, log_cap=64, max_pivots=5000, rule="bland")
+        res = lp.solve_batch(A, b, c, log_cap=64, max_pivots=5000, rule=rule)
         for p in range(len(lst)):
-            o = oracle_lib.simplex(A[p], b[p], c[p], max_pivots=5000, rule="bland")
+            o = oracle_lib.simplex(A[p], b[p], c[p], max_pivots=5000, rule=rule)
             assert int(res.status[p]) == o["status"]
             assert int(res.npivots[p]) == o["npivots"]
             assert res.pivots(p) == o["pivots"][:64]
@@ -261,13 +262,14 @@ def test_bland_rule_stress_distribution_vs_oracle(oracle_lib):
 
 @pytest.mark.parametrize("dist,n,m,count", [("D1", 100, 100, 64), ("D2", 100, 100, 8), ("D3", 100, 100, 12),
                                             ("D3", 37, 61, 64), ("D3", 64, 20, 64)])
-def test_bland_rule_random_batches_vs_oracle(oracle_lib, dist, n, m, count):
+@pytest.mark.parametrize("rule", ["bland", "dantzig"])
+def test_bland_rule_random_batches_vs_oracle(oracle_lib, dist, n, m, count, rule):
     import linear_programming_b200 as lp
     from linear_programming_b200 import workloads
     A, b, c = workloads.simplex_batch(dist, count, n, m, seed=9)
     cap = 200000
-    res = lp.solve_batch(A.astype(np.int16), b, c, max_pivots=cap, rule="bland")
-    st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=cap, rule="bland")
+    res = lp.solve_batch(A.astype(np.int16), b, c, max_pivots=cap, rule=rule)
+    st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=cap, rule=rule)
     assert np.array_equal(res.status, st)
     assert np.array_equal(res.npivots, npiv)
     assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
@@ -277,7 +279,7 @@ def test_bland_rule_random_batches_vs_oracle(oracle_lib, dist, n, m, count):
 
 @pytest.mark.parametrize("n,m,count", [(1, 1, 64), (1, 7, 64), (7, 1, 64), (2, 129, 32), (129, 2, 32), (3, 255, 16),
                                        (160, 160, 4), (100, 250, 4), (250, 100, 4), (20, 1000, 4)])
-@pytest.mark.parametrize("rule", ["reference", "bland"])
+@pytest.mark.parametrize("rule", ["reference", "bland", "dantzig"])
 def test_edge_shapes_vs_oracle(oracle_lib, n, m, count, rule):
     """Degenerate and extreme shapes of the one-CTA-per-LP kernel: a single row or column, odd widths,
     more than 64 column pairs (lanes loop), and the largest tableaus shared memory holds (one CTA/SM)."""
@@ -315,6 +317,23 @@ def test_empty_batch_and_bad_arguments():
     with pytest.raises(ValueError):
         lp.solve_batch(np.zeros((2, 3, 4)), np.zeros((2, 4)), np.zeros((2, 4)))
     with pytest.raises(ValueError):
-        lp.solve_batch(np.zeros((1, 3, 4)), np.zeros((1, 3)), np.zeros((1, 4)), rule="dantzig")
+        lp.solve_batch(np.zeros((1, 3, 4)), np.zeros((1, 3)), np.zeros((1, 4)), rule="steepest")
     with pytest.raises(lp.EngineError):
         lp.solve_batch(np.zeros((1, 3, 4)), np.zeros((1, 3)), np.zeros((1, 4)), tol=-1.0)
+
+
+@pytest.mark.parametrize("dist,n,m,count", [("D1", 100, 100, 320), ("D3", 100, 100, 16), ("D3", 37, 61, 64)])
+def test_register_resident_variant_vs_oracle(oracle_lib, monkeypatch, dist, n, m, count):
+    """The opt-in register-resident kernel variant (LPB_BATCH_KERNEL=reg; slower than the default
+    shared-memory kernel on B200, kept as a measured experiment -- DESIGN.md 5.1) stays bit-exact."""
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    monkeypatch.setenv("LPB_BATCH_KERNEL", "reg")
+    A, b, c = workloads.simplex_batch(dist, count, n, m, seed=23)
+    cap = 20000
+    res = lp.solve_batch(A, b, c, max_pivots=cap, log_cap=16)
+    st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=cap)
+    assert np.array_equal(res.status, st)
+    assert np.array_equal(res.npivots, npiv)
+    assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
+    assert np.array_equal(res.objective.view(np.int64), obj.view(np.int64))

@@ -30,29 +30,32 @@ def _check(A, b, c, o):
         assert abs(float(c @ x) - o["objective"]) <= 1e-6 * max(1.0, abs(opt))
 
 
-def test_bland_oracle_matches_highs_on_the_stress_distribution(oracle_lib):
+@pytest.mark.parametrize("rule", ["bland", "dantzig"])
+def test_bland_oracle_matches_highs_on_the_stress_distribution(oracle_lib, rule):
     """stress.py:23-26 distribution with zeros forced into b: every input on which the reference
     crashes (AttributeError / IndexError / TypeError) or cycles gets a proper answer here."""
     from linear_programming_b200 import workloads
     seen = set()
     for A, b, c in workloads.stress_batch(1500, seed=11):
-        o = oracle_lib.simplex(A, b, c, rule="bland", max_pivots=5000)
+        o = oracle_lib.simplex(A, b, c, rule=rule, max_pivots=5000)
         assert o["status"] in (0, -1, 1)
         _check(A, b, c, o)
         seen.add(o["status"])
     assert seen == {0, -1, 1}
 
 
+@pytest.mark.parametrize("rule", ["bland", "dantzig"])
 @pytest.mark.parametrize("dist,n,m,count", [("D3", 20, 20, 120), ("D2", 30, 40, 40), ("D3", 40, 25, 80)])
-def test_bland_oracle_matches_highs_mid_size(oracle_lib, dist, n, m, count):
+def test_bland_oracle_matches_highs_mid_size(oracle_lib, dist, n, m, count, rule):
     from linear_programming_b200 import workloads
     A, b, c = workloads.simplex_batch(dist, count, n, m, seed=7)
-    st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, rule="bland", max_pivots=200000)
+    st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, rule=rule, max_pivots=200000)
     for p in range(count):
         _check(A[p], b[p], c[p], {"status": int(st[p]), "x": x[p], "objective": float(obj[p])})
 
 
-def test_bland_answers_the_reference_crash_fixtures(oracle_lib, simplex_golden):
+@pytest.mark.parametrize("rule", ["bland", "dantzig"])
+def test_bland_answers_the_reference_crash_fixtures(oracle_lib, simplex_golden, rule):
     """Every golden case on which the reference raises (status 3/4/5) is a well-posed LP."""
     crashed = [k for k in simplex_golden["cases"] if k["status"] in (3, 4, 5)]
     assert len(crashed) >= 10
@@ -60,7 +63,24 @@ def test_bland_answers_the_reference_crash_fixtures(oracle_lib, simplex_golden):
         A = np.array(case["A"], dtype=np.float64).reshape(case["n"], case["m"])
         b = np.array(case["b"], dtype=np.float64)
         c = np.array(case["c"], dtype=np.float64)
-        _check(A, b, c, oracle_lib.simplex(A, b, c, rule="bland", max_pivots=20000))
+        _check(A, b, c, oracle_lib.simplex(A, b, c, rule=rule, max_pivots=20000))
+
+
+def test_dantzig_needs_far_fewer_pivots_and_uses_the_bland_fallback(oracle_lib):
+    from linear_programming_b200 import workloads
+    A, b, c = workloads.simplex_batch("D2", 12, 60, 60, seed=8)
+    _, _, ob, nb, _ = oracle_lib.simplex_batch(A, b, c, rule="bland", max_pivots=200000)
+    st, _, od, nd, _ = oracle_lib.simplex_batch(A, b, c, rule="dantzig", max_pivots=200000)
+    assert nd.sum() * 2 < nb.sum()
+    bounded = st == 0
+    assert np.allclose(ob[bounded], od[bounded], rtol=1e-9)
+    # a fully degenerate LP (b = 0): every pivot has ratio 0, the fallback must end it
+    rng = np.random.default_rng(3)
+    for _ in range(50):
+        A1 = rng.integers(-5, 6, size=(6, 6)).astype(np.float64)
+        o = oracle_lib.simplex(A1, np.zeros(6), rng.integers(-5, 6, size=6).astype(np.float64), rule="dantzig",
+                               max_pivots=5000)
+        assert o["status"] in (0, 1)
 
 
 def test_reference_rule_is_untouched(oracle_lib, simplex_golden):
