@@ -1,6 +1,7 @@
 // lp_api.cu -- error state, device probes and version of liblp_b200.so.
 #include <cuda_runtime.h>
 
+#include <mutex>
 #include <string>
 
 #include "lp_host.h"
@@ -30,6 +31,37 @@ int get_device_info(DeviceInfo *info)
     LPB_CUDA(cudaGetDevice(&info->device));
     LPB_CUDA(cudaDeviceGetAttribute(&info->sm_count, cudaDevAttrMultiProcessorCount, info->device));
     LPB_CUDA(cudaDeviceGetAttribute(&info->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, info->device));
+    return 0;
+}
+
+// Stream-ordered scratch (the batched kernel's 4-byte work counter) comes from a pool of our own
+// that keeps its memory across synchronisation points: the device's default pool hands unused
+// memory back at every sync (release threshold 0), which made each call issued on an idle GPU pay
+// ~240 us for a fresh physical allocation.
+int scratch_alloc(void **ptr, size_t bytes, int device, cudaStream_t stream)
+{
+    static std::mutex mu;
+    static cudaMemPool_t pools[64] = {};
+    if (device < 0 || device >= 64) {
+        set_error("scratch_alloc: unsupported device ordinal");
+        return LPB200_E_INVALID;
+    }
+    cudaMemPool_t pool;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!pools[device]) {
+            cudaMemPoolProps props = {};
+            props.allocType = cudaMemAllocationTypePinned;
+            props.handleTypes = cudaMemHandleTypeNone;
+            props.location.type = cudaMemLocationTypeDevice;
+            props.location.id = device;
+            LPB_CUDA(cudaMemPoolCreate(&pools[device], &props));
+            unsigned long long keep = ~0ull;
+            LPB_CUDA(cudaMemPoolSetAttribute(pools[device], cudaMemPoolAttrReleaseThreshold, &keep));
+        }
+        pool = pools[device];
+    }
+    LPB_CUDA(cudaMallocFromPoolAsync(ptr, bytes, pool, stream));
     return 0;
 }
 

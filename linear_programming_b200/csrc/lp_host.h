@@ -62,5 +62,7 @@ struct DeviceInfo {
     int max_smem_optin;
 };
 int get_device_info(DeviceInfo *info);
+// stream-ordered scratch from the library's own retaining pool; release with cudaFreeAsync
+int scratch_alloc(void **ptr, size_t bytes, int device, cudaStream_t stream);
 
 }  // namespace lpb

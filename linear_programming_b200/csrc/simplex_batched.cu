@@ -32,6 +32,7 @@
 #include <cuda_runtime.h>
 #include <math_constants.h>
 #include <stdint.h>
+#include <string.h>
 #include <stdio.h>
 #include <stdlib.h>
 
@@ -175,34 +176,53 @@ extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A,
 // Device scratch of the host-pointer entry point: two buffer sets and two streams, owned by the
 // calling thread and kept between calls (cudaMalloc/cudaFree of ~200 MB cost more than solving a
 // few thousand LPs); grown on demand, released when the thread exits.
+constexpr size_t kStageBytes = (size_t)4 << 20;  // calls smaller than this go through one pinned staging buffer
+
 struct HostArena {
     int device = -1;
     size_t cap = 0;
     char *mem[2] = {nullptr, nullptr};
     cudaStream_t stream[2] = {nullptr, nullptr};
+    char *stage = nullptr;  // pinned host mirror of a small call's buffer set (one copy in, one copy out)
 
-    void release()
+    void release_memory()
     {
         for (int s = 0; s < 2; ++s) {
             if (mem[s]) cudaFree(mem[s]);
-            if (stream[s]) cudaStreamDestroy(stream[s]);
             mem[s] = nullptr;
-            stream[s] = nullptr;
         }
         cap = 0;
+    }
+    void release()
+    {
+        release_memory();
+        for (int s = 0; s < 2; ++s) {
+            if (stream[s]) cudaStreamDestroy(stream[s]);
+            stream[s] = nullptr;
+        }
+        if (stage) cudaFreeHost(stage);
+        stage = nullptr;
         device = -1;
     }
     int ensure(int dev, int nset, size_t bytes)
     {
-        if (dev != device || bytes > cap) {
+        if (dev != device) {
             release();
             device = dev;
-            cap = bytes;
+        }
+        if (bytes > cap) {  // grow geometrically (at least 8 MB): a run of slightly larger batches reallocates once
+            size_t want = cap * 2 > bytes ? cap * 2 : bytes;
+            if (want < ((size_t)8 << 20)) want = (size_t)8 << 20;
+            for (int s = 0; s < 2; ++s)
+                if (stream[s]) LPB_CUDA(cudaStreamSynchronize(stream[s]));
+            release_memory();
+            cap = want;
         }
         for (int s = 0; s < nset; ++s) {
             if (!stream[s]) LPB_CUDA(cudaStreamCreateWithFlags(&stream[s], cudaStreamNonBlocking));
             if (!mem[s]) LPB_CUDA(cudaMalloc((void **)&mem[s], cap));
         }
+        if (!stage && bytes <= kStageBytes) LPB_CUDA(cudaMallocHost((void **)&stage, kStageBytes));
         return 0;
     }
     ~HostArena() { release(); }
@@ -271,6 +291,37 @@ extern "C" int lpb200_simplex_batch_ex(int B, int n, int m, const void *A_v, int
         set[s].log = lplog ? reinterpret_cast<int32_t *>(base + off[7]) : nullptr;
         set[s].stream = g_arena.stream[s];
     }
+    if (nset == 1 && off[8] <= kStageBytes) {
+        // small call: the inputs are gathered in the pinned mirror of the buffer set and go over in ONE
+        // copy, the outputs come back in one -- 2 driver copies instead of 8 pageable ones
+        Set &q = set[0];
+        char *h = g_arena.stage;
+        memcpy(h + off[0], A, (size_t)B * lpA * esz);
+        memcpy(h + off[1], b, (size_t)B * lpb * 8);
+        memcpy(h + off[2], c, (size_t)B * lpc * 8);
+        LPB_TRY(cudaMemcpyAsync(g_arena.mem[0], h, off[3], cudaMemcpyHostToDevice, q.stream));
+        if (lplog) LPB_TRY(cudaMemsetAsync(q.log, 0xff, (size_t)B * lplog * 4, q.stream));
+        if (rc == 0)
+            rc = lpb200_simplex_batch_ex_device(B, n, m, q.A, a_dtype, q.b, q.c, tol, max_pivots, rule, q.st, q.x,
+                                                q.obj, q.np, q.log, log_cap, q.stream);
+        LPB_TRY(cudaMemcpyAsync(h + off[3], g_arena.mem[0] + off[3], off[8] - off[3], cudaMemcpyDeviceToHost,
+                                q.stream));
+        LPB_TRY(cudaStreamSynchronize(q.stream));
+        if (rc == 0) {
+            memcpy(x, h + off[3], (size_t)B * lpc * 8);
+            memcpy(objective, h + off[4], (size_t)B * 8);
+            memcpy(status, h + off[5], (size_t)B * 4);
+            memcpy(npivots, h + off[6], (size_t)B * 4);
+            if (lplog) memcpy(pivot_log, h + off[7], (size_t)B * lplog * 4);
+        }
+#undef LPB_TRY
+        return rc;
+    }
+#define LPB_TRY(call)                                                 \
+    do {                                                              \
+        cudaError_t _e = (call);                                      \
+        if (_e != cudaSuccess && rc == 0) rc = cuda_fail(_e, #call);  \
+    } while (0)
     int k = 0;
     for (long long lo = 0; lo < B && rc == 0; lo += chunk, ++k) {
         const long long cnt = (B - lo < chunk) ? (B - lo) : chunk;

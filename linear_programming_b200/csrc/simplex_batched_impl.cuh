@@ -1236,7 +1236,10 @@ static int launch(const DeviceInfo &di, int B, int n, int m, const void *A, int 
     if (const char *g = getenv("LPB_DEBUG_GRID")) grid = atoi(g);
     if (grid > B) grid = B;
     unsigned int *counter = nullptr;
-    LPB_CUDA(cudaMallocAsync((void **)&counter, sizeof(unsigned int), stream));
+    {
+        const int rc = scratch_alloc((void **)&counter, sizeof(unsigned int), di.device, stream);
+        if (rc) return rc;
+    }
     LPB_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned int), stream));
     BatchArgs a;
     a.B = B;
