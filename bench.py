@@ -67,7 +67,7 @@ def measured_peak():
 
 def ncu_traffic(args, batch):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from the
-    committed ncu --set full capture of this very command (profiles/, see tools/gpu/profile_r1g.sh).
+    committed ncu --set full capture of this very command (profiles/, see tools/gpu/profile.sh).
     Only valid for the configuration that was captured; anything else reports null."""
     path = os.path.join(ROOT, "profiles", "r1g_batched_ncu_summary.csv")
     if not (batch == 65536 and args.dist == "D1" and args.n == 100 and args.m == 100 and os.path.exists(path)):
@@ -440,6 +440,18 @@ def ours_arm(args):
                  "D2_effective_GBps": 16.0 * (n + 1) * (m + 1) * piv2 / (ms2 * 1e-3) / 1e9}
 
     if rank == 0:
+        # the unmodified Python reference cannot run on this box; its timing on samples of these very
+        # inputs was recorded where it exists (tools/time_reference_batch.py) and is quoted, labelled
+        try:
+            with open(os.path.join(ROOT, "tests", "golden", "reference_batch_times.json")) as f:
+                rt = json.load(f)
+            key = "config4_" + args.dist
+            if key in rt and n == 100 and m == 100:
+                extra["python_reference_recorded"] = {
+                    "lps_per_s_per_core": rt[key]["lps_per_s_per_core"], "ms_per_pivot": rt[key]["ms_per_pivot"],
+                    "sample_lps": rt[key]["lps"], "where": rt["note"]}
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(args.warmup, 3),
             "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
