@@ -411,6 +411,11 @@ __device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, 
     const int dest = c.spare;
     const double tol = c.tol;
     const double pinv = c.pinvs[src];  // snap(-1 * (1.0 / pivot)), left by the row's own thread in step 1
+#ifdef LPB_TIMING
+    const long long ts_in = clock64();
+    long long ts_pro = ts_in, ts_slow = 0;
+    int n_slow = 0;
+#endif
     if (tid < kSweepThreads) {
         unsigned mykey = 0xffffffffu;
         if (c.row0 < c.row1) {
@@ -427,6 +432,9 @@ __device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, 
                 r2.y = (2 * cp + 1 == 1 + p) ? snap(-pinv, tol) : snap(__dmul_rn(pinv, r2.y), tol);
                 uint32_t qa = tbase + (uint32_t)c.row0 * rsb + (uint32_t)cp * 16u;
                 const double *fcp = c.fc + c.row0;
+#ifdef LPB_TIMING
+                ts_pro = clock64();
+#endif
                 for (int i = c.row0; i < c.row1; i += kRowChunk, qa += kRowChunk * rsb, fcp += kRowChunk) {
                     const double2 fa = *reinterpret_cast<const double2 *>(fcp);
                     const double2 fb = *reinterpret_cast<const double2 *>(fcp + 2);
@@ -458,6 +466,10 @@ __device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, 
                         sts_zero_if_snapped(qa + 3 * rsb, a3x, tol);
                         sts_zero_if_snapped(qa + 3 * rsb + 8, a3y, tol);
                     } else {
+#ifdef LPB_TIMING
+                        const long long ts0 = clock64();
+                        ++n_slow;
+#endif
                         const double f4[kRowChunk] = {fa.x, fa.y, fb.x, fb.y};
                         double2 *col = reinterpret_cast<double2 *>(c.T) + cp;
                         const int rs = S >> 1;  // row stride in double2
@@ -485,6 +497,9 @@ __device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, 
                                     mykey = min(mykey, ((unsigned)c.colslot[k0 + 1] << 16) | (unsigned)(k0 + 1));
                             }
                         }
+#ifdef LPB_TIMING
+                        ts_slow += clock64() - ts0;
+#endif
                     }
                 }
             }
@@ -500,6 +515,14 @@ __device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, 
     }
     c.spare = src;
     if (t_own) *t_own = clock64();
+#ifdef LPB_TIMING
+    if (c.timing != nullptr && (tid & 31) == 0 && tid < kSweepThreads) {
+        unsigned long long *t = c.timing + 32 * 4 + (tid >> 5) * 4;  // [prologue, general-path cycles, general-path chunks, -]
+        atomicAdd(t + 0, (unsigned long long)(ts_pro - ts_in));
+        atomicAdd(t + 1, (unsigned long long)ts_slow);
+        atomicAdd(t + 2, (unsigned long long)n_slow);
+    }
+#endif
     __syncthreads();
 }
 
@@ -1260,14 +1283,14 @@ static int launch(const DeviceInfo &di, int B, int n, int m, const void *A, int 
     a.timing = nullptr;
     const bool dbg_timing = getenv("LPB_DEBUG_TIMING") != nullptr;
     if (dbg_timing) {
-        LPB_CUDA(cudaMalloc((void **)&a.timing, 32 * 4 * 8));
-        LPB_CUDA(cudaMemset(a.timing, 0, 32 * 4 * 8));
+        LPB_CUDA(cudaMalloc((void **)&a.timing, 64 * 4 * 8));
+        LPB_CUDA(cudaMemset(a.timing, 0, 64 * 4 * 8));
     }
     simplex_batched_kernel<<<(unsigned)grid, kThreads, dyn_smem, stream>>>(sh, a);
     LPB_CUDA(cudaGetLastError());
     LPB_CUDA(cudaFreeAsync(counter, stream));
     if (dbg_timing) {  // debug only: synchronises
-        unsigned long long h[32 * 4];
+        unsigned long long h[64 * 4];
         LPB_CUDA(cudaStreamSynchronize(stream));
         LPB_CUDA(cudaMemcpy(h, a.timing, sizeof(h), cudaMemcpyDeviceToHost));
         for (int w = 0; w <= kSweepWarps; ++w)
@@ -1275,6 +1298,11 @@ static int launch(const DeviceInfo &di, int B, int n, int m, const void *A, int 
                 fprintf(stderr, "[lpb timing] warp %d: stage+bar %.0f  own sweep %.0f  sweep+bar %.0f cycles/pivot (%llu pivots)\n",
                         w, (double)h[w * 4] / h[w * 4 + 3], (double)h[w * 4 + 1] / h[w * 4 + 3],
                         (double)h[w * 4 + 2] / h[w * 4 + 3], h[w * 4 + 3]);
+        for (int w = 0; w < kSweepWarps; ++w)
+            if (h[w * 4 + 3])
+                fprintf(stderr, "[lpb timing] warp %d sweep: prologue %.0f  general path %.0f cycles/pivot in %.2f chunks/pivot\n", w,
+                        (double)h[128 + w * 4] / h[w * 4 + 3], (double)h[128 + w * 4 + 1] / h[w * 4 + 3],
+                        (double)h[128 + w * 4 + 2] / h[w * 4 + 3]);
         cudaFree(a.timing);
     }
     return 0;
