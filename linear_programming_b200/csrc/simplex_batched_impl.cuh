@@ -253,8 +253,10 @@ __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool 
     if (tid < nsw * 32) {
         unsigned long long key = kKeyNone;
         int var = 0x7fffffff;
+#if !LPB_CORRECTED
         const bool e_in_basis0 = (c.basis0[e >> 5] >> (e & 31)) & 1u;
         const bool e_is_slack = e < c.n;
+#endif
         for (int i = tid; i < nphys; i += nsw * 32) {
             const int v = c.rowvar[i];
             double f = 0.0;
@@ -266,8 +268,8 @@ __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool 
             }
             c.fc[i] = f;
             if (v >= 0) {
-                const int nc = c.nonecol[i];
 #if !LPB_CORRECTED
+                const int nc = c.nonecol[i];
                 crash |= (nc == kNoneInitial && e_is_slack) || (nc == e) || (c.untouched[i] && e_in_basis0);
 #endif
                 if (f != 0.0) {  // row is rewritten by this pivot: its only None is column e
@@ -577,8 +579,10 @@ __device__ __forceinline__ int ratio_staged(const Ctx &c, int e, bool forced)
     if (tid < nsw * 32) {
         unsigned long long key = kKeyNone;
         int var = 0x7fffffff;
+#if !LPB_CORRECTED
         const bool e_in_basis0 = (c.basis0[e >> 5] >> (e & 31)) & 1u;
         const bool e_is_slack = e < c.n;
+#endif
         for (int i = tid; i < nphys; i += nsw * 32) {
             const int v = c.rowvar[i];
             double f = c.fc[i];
@@ -587,8 +591,8 @@ __device__ __forceinline__ int ratio_staged(const Ctx &c, int e, bool forced)
                 c.fc[i] = 0.0;
             }
             if (v >= 0) {
-                const int nc = c.nonecol[i];
 #if !LPB_CORRECTED
+                const int nc = c.nonecol[i];
                 crash |= (nc == kNoneInitial && e_is_slack) || (nc == e) || (c.untouched[i] && e_in_basis0);
 #endif
                 if (f != 0.0) {
@@ -1310,7 +1314,7 @@ static int launch(const DeviceInfo &di, int B, int n, int m, const void *A, int 
 
 // Shapes this variant can serve (register-resident variants need one column-pair pass and at
 // most LPB_REG_ROWS rows per thread; the shared-memory variant takes anything that fits).
-static bool eligible(int n, int m)
+[[maybe_unused]] static bool eligible(int n, int m)
 {
 #if LPB_REG_ROWS > 0
     const BatchShape s = make_batch_shape(n, m);

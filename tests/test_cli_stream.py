@@ -91,3 +91,27 @@ def test_single_problem_cli_is_byte_compatible(monkeypatch, capsys, simplex_gold
         monkeypatch.setattr(sys, "stdin", io.StringIO(case["stdin"]))
         assert cli.main(["simplex"]) == 0
         assert capsys.readouterr().out == _expected_stdout(case)
+
+
+def test_rule_flag_reaches_the_batch_call(monkeypatch, oracle_lib):
+    """`--rule=bland|dantzig` (corrected modes) is handed to the batch solve; the default stays the
+    reference's behaviour, on an input where the two differ (all-zero b: AttributeError class)."""
+    from linear_programming_b200 import cli
+    seen = []
+
+    def checker(A, b, c, rule="reference"):
+        seen.append(rule)
+        st, x, _, _, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=100000, rule=rule)
+        return st, x
+    monkeypatch.setattr(cli, "_solve_lp_batch", checker)
+    text = "2 2\n1 1\n1 -1\n0 0\n1 1\n"          # b == 0: the reference raises (simplex.py:626)
+    assert cli.solve_lp_stream(text, integer=True) == "AttributeError\n"
+    out = cli.solve_lp_stream(text, integer=True, rule="bland")
+    assert out.startswith("Bounded solution\n") or out == "Infinity\n"
+    assert cli.solve_lp_stream(text, integer=True, rule="dantzig") == out
+    assert seen == ["reference", "bland", "dantzig"]
+    monkeypatch.setattr(sys, "stdin", io.StringIO(text))
+    buf = io.StringIO()
+    monkeypatch.setattr(sys, "stdout", buf)
+    assert cli.main(["simplex", "--stream", "--rule=dantzig"]) == 0
+    assert buf.getvalue() == out
