@@ -41,8 +41,11 @@
 
 
 // ---- kernel variants (same source, different parameters) ----
+#ifndef LPB_SMEM_WARPS
+#define LPB_SMEM_WARPS 8  // sweep warps of the product kernel (A/B knob: 10 gives six row groups, measured slower)
+#endif
 #define LPB_NS smem8
-#define LPB_SWEEP_WARPS 8
+#define LPB_SWEEP_WARPS LPB_SMEM_WARPS
 #define LPB_REG_ROWS 0
 #define LPB_MIN_BLOCKS 2
 #define LPB_RULE 0
