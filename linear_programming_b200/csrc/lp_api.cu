@@ -31,6 +31,7 @@ int get_device_info(DeviceInfo *info)
     LPB_CUDA(cudaGetDevice(&info->device));
     LPB_CUDA(cudaDeviceGetAttribute(&info->sm_count, cudaDevAttrMultiProcessorCount, info->device));
     LPB_CUDA(cudaDeviceGetAttribute(&info->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, info->device));
+    LPB_CUDA(cudaDeviceGetAttribute(&info->max_smem_per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, info->device));
     return 0;
 }
 

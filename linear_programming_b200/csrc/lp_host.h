@@ -59,7 +59,8 @@ inline int dtype_bytes(int dtype)
 struct DeviceInfo {
     int device;
     int sm_count;
-    int max_smem_optin;
+    int max_smem_optin;   // per CTA (opt-in)
+    int max_smem_per_sm;  // per SM
 };
 int get_device_info(DeviceInfo *info);
 // stream-ordered scratch from the library's own retaining pool; release with cudaFreeAsync

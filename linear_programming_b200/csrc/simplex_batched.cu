@@ -68,6 +68,48 @@
 #undef LPB_MIN_BLOCKS
 #undef LPB_RULE
 
+// Small problems: one sweep warp + the bookkeeping warp per LP.  A 64-thread CTA needs a fraction of
+// the registers of the 288-thread one, so 8-16 LPs are resident per SM instead of 2 (measured on
+// B200, tools/gpu/variant_grid.py: 3x the pivots/s at 30x30, 1.8x at 50x50).  Two register budgets:
+// tiny1 (64 registers, 16 CTAs/SM) for diet-size problems, small1 (120 registers, 8 CTAs/SM) where
+// shared memory limits the residency anyway.
+#define LPB_NS tiny1
+#define LPB_SWEEP_WARPS 1
+#define LPB_REG_ROWS 0
+#define LPB_MIN_BLOCKS 16
+#define LPB_RULE 0
+#include "simplex_batched_impl.cuh"
+#undef LPB_NS
+#undef LPB_SWEEP_WARPS
+#undef LPB_REG_ROWS
+#undef LPB_MIN_BLOCKS
+#undef LPB_RULE
+
+#define LPB_NS small1
+#define LPB_SWEEP_WARPS 1
+#define LPB_REG_ROWS 0
+#define LPB_MIN_BLOCKS 8
+#define LPB_RULE 0
+#include "simplex_batched_impl.cuh"
+#undef LPB_NS
+#undef LPB_SWEEP_WARPS
+#undef LPB_REG_ROWS
+#undef LPB_MIN_BLOCKS
+#undef LPB_RULE
+
+// course-size problems (ad_allocation: up to 50 x 100): four sweep warps + the bookkeeping warp
+#define LPB_NS mid4
+#define LPB_SWEEP_WARPS 4
+#define LPB_REG_ROWS 0
+#define LPB_MIN_BLOCKS 4
+#define LPB_RULE 0
+#include "simplex_batched_impl.cuh"
+#undef LPB_NS
+#undef LPB_SWEEP_WARPS
+#undef LPB_REG_ROWS
+#undef LPB_MIN_BLOCKS
+#undef LPB_RULE
+
 // the corrected (non-reference) mode, LPB200_RULE_BLAND: same kernel, other pivoting decisions
 #define LPB_NS bland8
 #define LPB_SWEEP_WARPS 8
@@ -122,15 +164,36 @@ extern "C" int64_t lpb200_simplex_batch_smem_bytes(int n, int m)
 // Which kernel variant serves a shape: the register-resident one when it is eligible (one
 // column-pair pass, at most LPB_REG_ROWS rows per thread) and fits, else the shared-memory one.
 // LPB_BATCH_KERNEL=smem|reg overrides the choice (A/B measurements, tests).
-// The shared-memory kernel is the product path.  The register-resident variant is bit-exact but
-// slower on B200 (32 M vs 81 M pivots/s on Config 4 D2: with one CTA per SM nothing overlaps the
-// serial stage/ratio chain); LPB_BATCH_KERNEL=reg selects it for experiments.
-static int pick_variant(int n, int m, const DeviceInfo &di)
+// Kernel variant for a shape (reference rule).  smem8 (8+1 warps, 2 CTAs/SM) is the kernel the
+// headline 100x100 batch runs on; smaller problems get smaller CTAs so that more of them are resident:
+//   tiny1   n, m <= 30                                   1+1 warps, 16 CTAs/SM
+//   small1  (n+2) * ceil((m+2)/2) <= 1500, m <= 62        1+1 warps,  8 CTAs/SM
+//   mid4    three or more tableaus fit one SM's shared memory   4+1 warps
+// (small1 and mid4 only when the batch has more than 2 LPs per SM: see below)
+// LPB_BATCH_KERNEL=smem|tiny|small|mid|reg forces one (A/B measurements, tests); reg is the
+// register-resident experiment: bit-exact but slower on B200 (32 M vs 81 M pivots/s on Config 4 D2:
+// with one CTA per SM nothing overlaps the serial stage/ratio chain).
+enum { V_SMEM8 = 0, V_REG15, V_TINY1, V_SMALL1, V_MID4 };
+static int pick_variant(int B, int n, int m, const DeviceInfo &di)
 {
-    const char *force = getenv("LPB_BATCH_KERNEL");
-    if (force && force[0] == 'r')
-        return reg15::eligible(n, m) && reg15::make_batch_shape(n, m).bytes <= di.max_smem_optin ? 1 : 0;
-    return 0;
+    const int npairs = (m + 3) / 2, nphys = n + 2;
+    const bool one_warp_ok = npairs <= 32;
+    if (const char *force = getenv("LPB_BATCH_KERNEL")) {
+        switch (force[0]) {
+        case 'r': return reg15::eligible(n, m) && reg15::make_batch_shape(n, m).bytes <= di.max_smem_optin ? V_REG15 : V_SMEM8;
+        case 't': return one_warp_ok ? V_TINY1 : V_SMEM8;
+        case 'm': return V_MID4;
+        case 's': return force[1] == 'm' && force[2] == 'a' ? (one_warp_ok ? V_SMALL1 : V_SMEM8) : V_SMEM8;
+        default: break;
+        }
+    }
+    if (n <= 30 && m <= 30) return V_TINY1;
+    // a batch that cannot even fill the SMs is a latency problem: all eight sweep warps on each LP
+    // (a lone 50x50 LP: 2.7 us per pivot on smem8, 3.7 on small1)
+    if (B <= 2 * di.sm_count) return V_SMEM8;
+    if (one_warp_ok && nphys * npairs <= 1500) return V_SMALL1;
+    if ((long long)mid4::make_batch_shape(n, m).bytes * 3 + 3 * 1024 <= (long long)di.max_smem_per_sm) return V_MID4;
+    return V_SMEM8;
 }
 
 extern "C" int lpb200_simplex_batch_ex_device(int B, int n, int m, const void *A, int a_dtype, const double *b,
@@ -159,9 +222,16 @@ extern "C" int lpb200_simplex_batch_ex_device(int B, int n, int m, const void *A
     if (rule == LPB200_RULE_BLAND)
         return bland8::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots,
                               pivot_log, log_cap, stream);
-    if (pick_variant(n, m, di) == 1)
-        return reg15::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots,
-                             pivot_log, log_cap, stream);
+#define LPB_LAUNCH(ns) \
+    ns::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots, pivot_log, log_cap, stream)
+    switch (pick_variant(B, n, m, di)) {
+    case V_TINY1: return LPB_LAUNCH(tiny1);
+    case V_SMALL1: return LPB_LAUNCH(small1);
+    case V_MID4: return LPB_LAUNCH(mid4);
+    case V_REG15: return LPB_LAUNCH(reg15);
+    default: break;
+    }
+#undef LPB_LAUNCH
     return smem8::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots, pivot_log,
                          log_cap, stream);
 }

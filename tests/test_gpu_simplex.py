@@ -337,3 +337,49 @@ def test_register_resident_variant_vs_oracle(oracle_lib, monkeypatch, dist, n, m
     assert np.array_equal(res.npivots, npiv)
     assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
     assert np.array_equal(res.objective.view(np.int64), obj.view(np.int64))
+
+
+@pytest.mark.parametrize("variant", ["tiny", "small", "mid", "smem"])
+def test_every_kernel_variant_is_bit_exact(oracle_lib, simplex_golden, monkeypatch, variant):
+    """The library picks a CTA size per shape and batch size (1+1 warps for small problems, 4+1 for
+    course-size ones, 8+1 for the 100x100 batch); every variant, forced through LPB_BATCH_KERNEL, gives
+    the reference's answers on the golden fixtures and the oracle's on random batches."""
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    monkeypatch.setenv("LPB_BATCH_KERNEL", variant)
+    groups = {}
+    for case in simplex_golden["cases"]:
+        groups.setdefault((case["n"], case["m"]), []).append(case)
+    checked = 0
+    for (n, m), cases in sorted(groups.items()):
+        A = np.stack([_case_arrays(k)[0] for k in cases])
+        b = np.stack([_case_arrays(k)[1] for k in cases])
+        c_ = np.stack([_case_arrays(k)[2] for k in cases])
+        cap = max(k["npivots"] for k in cases) + 8
+        res = lp.solve_batch(A, b, c_, log_cap=cap, max_pivots=cap, mode="batch")
+        for p, case in enumerate(cases):
+            _check_against_case(res, p, case)
+            checked += 1
+    assert checked >= 430
+    for dist, n, m, count in (("D3", 37, 61, 600), ("D3", 50, 50, 600), ("D2", 20, 28, 600), ("D3", 62, 30, 600),
+                              ("D1", 100, 100, 600)):
+        A, b, c = workloads.simplex_batch(dist, count, n, m, seed=31)
+        res = lp.solve_batch(A.astype(np.int16), b, c, max_pivots=20000)
+        st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=20000)
+        assert np.array_equal(res.status, st)
+        assert np.array_equal(res.npivots, npiv)
+        assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
+        assert np.array_equal(res.objective.view(np.int64), obj.view(np.int64))
+
+
+def test_automatic_variant_choice_large_batches_vs_oracle(oracle_lib):
+    """Batches large enough (> 2 LPs per SM) for the throughput variants to be picked automatically."""
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    for dist, n, m, count in (("D3", 7, 5, 3000), ("D3", 40, 40, 700), ("D3", 50, 100, 500), ("D2", 80, 80, 400)):
+        A, b, c = workloads.simplex_batch(dist, count, n, m, seed=32)
+        res = lp.solve_batch(A, b, c, max_pivots=30000)
+        st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=30000)
+        assert np.array_equal(res.status, st)
+        assert np.array_equal(res.npivots, npiv)
+        assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
