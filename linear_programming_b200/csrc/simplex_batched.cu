@@ -137,6 +137,31 @@
 #undef LPB_MIN_BLOCKS
 #undef LPB_RULE
 
+// the corrected rules on diet-size problems (n, m <= 30): the two-warp CTA
+#define LPB_NS bland_tiny1
+#define LPB_SWEEP_WARPS 1
+#define LPB_REG_ROWS 0
+#define LPB_MIN_BLOCKS 16
+#define LPB_RULE 1
+#include "simplex_batched_impl.cuh"
+#undef LPB_NS
+#undef LPB_SWEEP_WARPS
+#undef LPB_REG_ROWS
+#undef LPB_MIN_BLOCKS
+#undef LPB_RULE
+
+#define LPB_NS dantzig_tiny1
+#define LPB_SWEEP_WARPS 1
+#define LPB_REG_ROWS 0
+#define LPB_MIN_BLOCKS 16
+#define LPB_RULE 2
+#include "simplex_batched_impl.cuh"
+#undef LPB_NS
+#undef LPB_SWEEP_WARPS
+#undef LPB_REG_ROWS
+#undef LPB_MIN_BLOCKS
+#undef LPB_RULE
+
 // ======================================================================================
 // Host side: C ABI
 // ======================================================================================
@@ -216,14 +241,14 @@ extern "C" int lpb200_simplex_batch_ex_device(int B, int n, int m, const void *A
     DeviceInfo di;
     rc = get_device_info(&di);
     if (rc) return rc;
-    if (rule == LPB200_RULE_DANTZIG)
-        return dantzig8::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots,
-                                pivot_log, log_cap, stream);
-    if (rule == LPB200_RULE_BLAND)
-        return bland8::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots,
-                              pivot_log, log_cap, stream);
 #define LPB_LAUNCH(ns) \
     ns::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots, pivot_log, log_cap, stream)
+    if (rule != LPB200_RULE_REFERENCE) {  // corrected modes: the two-warp CTA for diet-size problems, else 8+1 warps
+        const char *force = getenv("LPB_BATCH_KERNEL");
+        const bool tiny = (n <= 30 && m <= 30 && !(force && force[0] == 's' && force[1] == 'm' && force[2] == 'e'));
+        if (rule == LPB200_RULE_DANTZIG) return tiny ? LPB_LAUNCH(dantzig_tiny1) : LPB_LAUNCH(dantzig8);
+        return tiny ? LPB_LAUNCH(bland_tiny1) : LPB_LAUNCH(bland8);
+    }
     switch (pick_variant(B, n, m, di)) {
     case V_TINY1: return LPB_LAUNCH(tiny1);
     case V_SMALL1: return LPB_LAUNCH(small1);
