@@ -40,7 +40,7 @@ namespace lpb {
 
 constexpr int kGjK = 16;            // pivots per panel
 constexpr int kGjPS = kGjK + 2;     // panel row stride in shared memory (16-byte aligned rows)
-constexpr int kGjThreads = 512;
+constexpr int kGjMaxThreads = 512;  // CTA size for large systems; small ones get 64 or 128 threads (more systems per SM)
 #ifndef LPB_GJ_ROWS
 #define LPB_GJ_ROWS 2
 #endif
@@ -58,8 +58,8 @@ constexpr int kGjBlockRows = LPB_GJ_BLOCK;  // rows per work item of the trailin
 #ifndef LPB_GJ_MINB
 #define LPB_GJ_MINB 2
 #endif
-template <bool kPartial>
-__global__ void __launch_bounds__(kGjThreads, LPB_GJ_MINB)
+template <bool kPartial, int kGjThreads>
+__global__ void __launch_bounds__(kGjThreads, (kGjThreads == kGjMaxThreads ? LPB_GJ_MINB : 1024 / kGjThreads))
 gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restrict__ x_all)
 {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -304,15 +304,25 @@ static int gj_launch(int B, int n, double *wa, double *x, int pivoting, const De
                   std::to_string((di.max_smem_optin - 288) / (kGjPS * 8)) + ")");
         return LPB200_E_TOO_LARGE;
     }
-    if (pivoting == LPB200_PIVOT_PARTIAL) {
-        LPB_CUDA(cudaFuncSetAttribute(gauss_jordan_batched_kernel<true>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        gauss_jordan_batched_kernel<true><<<B, kGjThreads, smem, stream>>>(n, wa, x);
+    // CTA size by system size: a 512-thread CTA idles on the small systems the course feeds this solver
+    // (energy_values: n <= 20), and two of them fill an SM; 64- and 128-thread CTAs put 16 / 8 there.
+#define LPB_GJ_LAUNCH(PP, T)                                                                                         \
+    do {                                                                                                             \
+        LPB_CUDA(cudaFuncSetAttribute(gauss_jordan_batched_kernel<PP, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                      smem));                                                                        \
+        gauss_jordan_batched_kernel<PP, T><<<B, T, smem, stream>>>(n, wa, x);                                       \
+    } while (0)
+    const bool pp = (pivoting == LPB200_PIVOT_PARTIAL);
+    int threads = n <= 64 ? 64 : (n <= 128 ? 128 : kGjMaxThreads);  // measured: tools/gpu/gj_small_rates.py
+    if (const char *g = getenv("LPB_DEBUG_GJ_THREADS")) threads = atoi(g);
+    if (threads == 64) {
+        if (pp) LPB_GJ_LAUNCH(true, 64); else LPB_GJ_LAUNCH(false, 64);
+    } else if (threads == 128) {
+        if (pp) LPB_GJ_LAUNCH(true, 128); else LPB_GJ_LAUNCH(false, 128);
     } else {
-        LPB_CUDA(cudaFuncSetAttribute(gauss_jordan_batched_kernel<false>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        gauss_jordan_batched_kernel<false><<<B, kGjThreads, smem, stream>>>(n, wa, x);
+        if (pp) LPB_GJ_LAUNCH(true, kGjMaxThreads); else LPB_GJ_LAUNCH(false, kGjMaxThreads);
     }
+#undef LPB_GJ_LAUNCH
     LPB_CUDA(cudaGetLastError());
     return 0;
 }
