@@ -313,12 +313,14 @@ static int gj_launch(int B, int n, double *wa, double *x, int pivoting, const De
         gauss_jordan_batched_kernel<PP, T><<<B, T, smem, stream>>>(n, wa, x);                                       \
     } while (0)
     const bool pp = (pivoting == LPB200_PIVOT_PARTIAL);
-    int threads = n <= 64 ? 64 : (n <= 128 ? 128 : kGjMaxThreads);  // measured: tools/gpu/gj_small_rates.py
+    int threads = n <= 64 ? 64 : (n <= 128 ? 128 : (n <= 256 ? 256 : kGjMaxThreads));  // measured: tools/gpu/gj_small_rates.py
     if (const char *g = getenv("LPB_DEBUG_GJ_THREADS")) threads = atoi(g);
     if (threads == 64) {
         if (pp) LPB_GJ_LAUNCH(true, 64); else LPB_GJ_LAUNCH(false, 64);
     } else if (threads == 128) {
         if (pp) LPB_GJ_LAUNCH(true, 128); else LPB_GJ_LAUNCH(false, 128);
+    } else if (threads == 256) {
+        if (pp) LPB_GJ_LAUNCH(true, 256); else LPB_GJ_LAUNCH(false, 256);
     } else {
         if (pp) LPB_GJ_LAUNCH(true, kGjMaxThreads); else LPB_GJ_LAUNCH(false, kGjMaxThreads);
     }
