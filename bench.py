@@ -69,7 +69,7 @@ def ncu_traffic(args, batch):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from the
     committed ncu --set full capture of this very command (profiles/, see tools/gpu/profile.sh).
     Only valid for the configuration that was captured; anything else reports null."""
-    path = os.path.join(ROOT, "profiles", "r1g_batched_ncu_summary.csv")
+    path = os.path.join(ROOT, "profiles", "r1h_batched_ncu_summary.csv")
     if not (batch == 65536 and args.dist == "D1" and args.n == 100 and args.m == 100 and os.path.exists(path)):
         return None, None
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
@@ -82,7 +82,7 @@ def ncu_traffic(args, batch):
                     total += float(row["value"]) * unit[row["unit"]]
     except Exception:
         return None, None
-    return (total if total > 0 else None), "profiles/r1g_batched_ncu_summary.csv (ncu --set full, same command)"
+    return (total if total > 0 else None), "profiles/r1h_batched_ncu_summary.csv (ncu --set full, same command)"
 
 
 def config_dict(args, batch):
