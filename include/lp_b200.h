@@ -131,6 +131,20 @@ int lpb200_simplex_single(int n, int m, const double *A, const double *b, const 
                           int32_t *npivots, int32_t *pivot_log, int log_cap, double *stats);
 
 /*
+ * The same two calls with a choice of pivoting rule (LPB200_RULE_* above; LPB200_RULE_REFERENCE is what
+ * the calls without _ex do).  The corrected rules make a large LP solvable to optimality: the
+ * reference's set-order rule needs thousands of pivots where Dantzig pricing needs tens.  Decisions
+ * and arithmetic are those of the batch kernel's corrected modes (same CPU restatement, bit-exact).
+ */
+int lpb200_simplex_single_ex_device(int n, int m, const double *A, const double *b, const double *c,
+                                    double tol, int max_pivots, int rule, int32_t *status, double *x,
+                                    double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap,
+                                    void *workspace, int64_t workspace_bytes, void *stream);
+int lpb200_simplex_single_ex(int n, int m, const double *A, const double *b, const double *c, double tol,
+                             int max_pivots, int rule, int32_t *status, double *x, double *objective,
+                             int32_t *npivots, int32_t *pivot_log, int log_cap, double *stats);
+
+/*
  * Single large LP, COLUMN-SHARDED over the GPUs of one NVLink/NVSwitch box (SURVEY.md 8(e),
  * BASELINE.json configs[4]).  One process per GPU; rank g owns column positions
  * [g*W, (g+1)*W) of every tableau row (W from lpb200_simplex_sharded_columns); per pivot the
@@ -168,6 +182,19 @@ int lpb200_simplex_sharded_device(lpb200_comm_t *comm, int n, int m, const doubl
 int lpb200_simplex_sharded_emulated(int nranks, int n, int m, const double *A, const double *b,
                                     const double *c, double tol, int max_pivots, int32_t *status, double *x,
                                     double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap);
+
+/* The sharded calls with a pivoting rule.  Under LPB200_RULE_DANTZIG the entering exchange carries
+ * (~bits(c_j), variable id) as two packets per rank and the minimum is lexicographic; the x_aux
+ * drive-out of the corrected modes costs one more key exchange after phase 1. */
+int lpb200_simplex_sharded_ex_device(lpb200_comm_t *comm, int n, int m, const double *A_cols, int64_t lda,
+                                     const double *b, const double *c, double tol, int max_pivots, int rule,
+                                     int32_t *status, double *x, double *objective, int32_t *npivots,
+                                     int32_t *pivot_log, int log_cap, void *workspace, int64_t workspace_bytes,
+                                     double timeout_s, void *stream);
+int lpb200_simplex_sharded_emulated_ex(int nranks, int n, int m, const double *A, const double *b,
+                                       const double *c, double tol, int max_pivots, int rule, int32_t *status,
+                                       double *x, double *objective, int32_t *npivots, int32_t *pivot_log,
+                                       int log_cap);
 
 /*
  * Batched Gauss-Jordan: B independent n x n systems a.x = b.

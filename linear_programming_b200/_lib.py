@@ -41,6 +41,12 @@ SIGNATURES = {
                                                     c_vp, ctypes.c_int64, c_vp]),
     "lpb200_simplex_single": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, ctypes.c_double,
                                              ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.c_int, c_vp]),
+    "lpb200_simplex_single_ex_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, ctypes.c_double,
+                                                       ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                                       ctypes.c_int, c_vp, ctypes.c_int64, c_vp]),
+    "lpb200_simplex_single_ex": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, ctypes.c_double,
+                                                ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                                ctypes.c_int, c_vp]),
     "lpb200_comm_handle_bytes": (ctypes.c_int64, []),
     "lpb200_comm_create": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(c_vp), c_vp]),
     "lpb200_comm_connect": (ctypes.c_int, [c_vp, c_vp]),
@@ -54,6 +60,13 @@ SIGNATURES = {
     "lpb200_simplex_sharded_emulated": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp,
                                                        ctypes.c_double, ctypes.c_int, c_vp, c_vp, c_vp, c_vp,
                                                        c_vp, ctypes.c_int]),
+    "lpb200_simplex_sharded_ex_device": (ctypes.c_int, [c_vp, ctypes.c_int, ctypes.c_int, c_vp, ctypes.c_int64,
+                                                        c_vp, c_vp, ctypes.c_double, ctypes.c_int, ctypes.c_int,
+                                                        c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.c_int, c_vp,
+                                                        ctypes.c_int64, ctypes.c_double, c_vp]),
+    "lpb200_simplex_sharded_emulated_ex": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp, c_vp,
+                                                          c_vp, ctypes.c_double, ctypes.c_int, ctypes.c_int, c_vp,
+                                                          c_vp, c_vp, c_vp, c_vp, ctypes.c_int]),
     "lpb200_gauss_jordan_workspace_bytes": (ctypes.c_int64, [ctypes.c_int, ctypes.c_int]),
     "lpb200_gauss_jordan_batch_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp,
                                                         ctypes.c_int64, c_vp]),

@@ -33,6 +33,12 @@
 // hanging the GPU.  For tests (and boxes with fewer GPUs than ranks) the same kernel runs all
 // ranks as CTA groups of one cooperative launch ("emulated"), which makes every wait safe.
 //
+// Pivoting rule (SingleArgs.rule, a run-time argument: the selection phases are a few microseconds
+// of a 1.3 ms pivot, the sweep is rule-independent): LPB200_RULE_REFERENCE = the reference's
+// decisions (parity); LPB200_RULE_BLAND / LPB200_RULE_DANTZIG = the corrected modes of the batch
+// kernel (lowest-id / largest-coefficient entering, zero ratios kept, true minimum of b, x_aux
+// driven out after phase 1, no crash classes), checked bit-exact against oracle/simplex_oracle.c.
+//
 // Tensor cores are not used: the update is a rank-1 AXPY at 0.125 flop/byte, HBM-bound.
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
@@ -53,14 +59,16 @@ constexpr int kTileCols = 2 * kSgThreads;  // 512 doubles: one double2 per threa
 constexpr int kTileRows = 64;
 constexpr int kRowUnroll = 8;
 constexpr int kMaxRanks = 32;
+constexpr int kDegenerateStreak = 8;  // Dantzig: degenerate pivots in a row before Bland takes over (as in the batch kernel)
+constexpr unsigned long long kKeyZeroRatio = 0x8000000000000000ull;  // order_key(+0.0)
 
 enum { ST_ISIZE = 0, ST_IFILL, ST_IUSED, ST_DSIZE, ST_DFILL, ST_DUSED, ST_NLIST, ST_COUNT = 16 };
 
 // Exchange buffer of one rank, in 8-byte words.  Every payload word is an "LL" word:
 // low 32 bits data, high 32 bits the epoch of the exchange that wrote it.
 constexpr int kXbEpoch = 0;  // running epoch, persists across solves on the same communicator
-constexpr int kXbKeys = 8;   // [2][nranks] packets of 2 words (double-buffered by exchange parity)
-__host__ __device__ inline int xb_fc(int nranks) { return kXbKeys + 4 * nranks; }  // [(n+2)] packets
+constexpr int kXbKeys = 8;   // [2][nranks] x (key packet, id packet) of 2 words each (double-buffered by exchange parity)
+__host__ __device__ inline int xb_fc(int nranks) { return kXbKeys + 8 * nranks; }  // [(n+2)] packets
 static inline size_t xbuf_bytes_for(int n, int nranks)
 {
     return ((size_t)(xb_fc(nranks) + 2 * (n + 2)) * 8 + 255) / 256 * 256;
@@ -101,6 +109,7 @@ struct SingleArgs {
     int max_pivots;
     int log_cap;
     int cpr;  // CTAs per rank in this launch
+    int rule; // LPB200_RULE_*: 0 = the reference's decisions, 1 = Bland, 2 = Dantzig (corrected modes)
     unsigned long long timeout_ns;
 };
 
@@ -210,6 +219,7 @@ struct LoopCtl {
     uint32_t parity;  // mbarrier phase bits of the two sweep stages
     unsigned epoch;   // exchange epoch (continues across solves)
     unsigned kx;      // key exchanges so far (parity selects the key buffer)
+    int streak;       // LPB200_RULE_DANTZIG: degenerate pivots in a row in the current loop
 };
 
 // Reduce the per-CTA partials written before the last grid.sync().
@@ -244,17 +254,33 @@ __device__ __forceinline__ void write_partial(const SingleWS &w, const LoopCtl &
 }
 
 // ---- P1: entering column (pick_entering_idx :390-392), own columns only ----
-__device__ __forceinline__ void phase_entering(BlockRed &br, const SingleWS &w, const LoopCtl &ctl, double tol)
+// pricing: 0 = first positive coefficient in CPython-set slot order (the reference), 1 = lowest
+// variable id (Bland), 2 = largest coefficient, ties -> lowest id (Dantzig).  The partial is the
+// lexicographic minimum of (key, id): rules 0/1 pack (priority << 32 | position) into the key,
+// rule 2 uses key = ~bits(c_j) (positive doubles order like their bit patterns) and id = variable.
+__device__ __forceinline__ void phase_entering(BlockRed &br, const SingleWS &w, const LoopCtl &ctl, double tol,
+                                               int pricing)
 {
     unsigned long long key = kKeyNone;
-    int var = 0, flag = 0;
+    int var = 0x7fffffff, flag = 0;
     const double *obj = w.T + (size_t)w.n * w.S;
     const int lim = min(w.wloc, ctl.ncols - w.c_lo);
+    const int *prio = (pricing == 0) ? w.colslot : w.colvar;
     for (int kl = ctl.bid * kSgThreads + threadIdx.x; kl < lim; kl += ctl.nblk * kSgThreads) {
-        if (obj[kl] > tol) {
+        const double v = obj[kl];
+        if (v > tol) {
             const int k = w.c_lo + kl;
-            const unsigned long long kk = ((unsigned long long)(unsigned)w.colslot[k] << 32) | (unsigned)k;
-            key = kk < key ? kk : key;
+            if (pricing == 2) {
+                const unsigned long long kk = ~(unsigned long long)__double_as_longlong(v);
+                const int id = w.colvar[k];
+                if (kk < key || (kk == key && id < var)) {
+                    key = kk;
+                    var = id;
+                }
+            } else {
+                const unsigned long long kk = ((unsigned long long)(unsigned)prio[k] << 32) | (unsigned)k;
+                key = kk < key ? kk : key;
+            }
         }
     }
     block_argmin(br, key, var, flag);
@@ -262,32 +288,44 @@ __device__ __forceinline__ void phase_entering(BlockRed &br, const SingleWS &w, 
 }
 
 // ---- all-to-all of the ranks' entering keys over NVLink, min on arrival ----
+// with_id: the (key, id) pair travels as two packets and the minimum is lexicographic (Dantzig).
 __device__ __forceinline__ unsigned long long exchange_key(BlockRed &br, const SingleWS &w, LoopCtl &ctl,
-                                                           unsigned long long key, unsigned long long timeout_ns)
+                                                           unsigned long long key, int &var, bool with_id,
+                                                           unsigned long long timeout_ns)
 {
     if (w.nranks == 1) return key;
     const int tid = threadIdx.x, G = w.nranks;
     const unsigned ep = ++ctl.epoch;
     const int buf = (int)(ctl.kx++ & 1u);
-    if (ctl.bid == 0 && tid < G) ll_store(w.peers[tid] + kXbKeys + 2 * (buf * G + w.rank), key, ep);
+    if (ctl.bid == 0 && tid < G) {
+        unsigned long long *dst = w.peers[tid] + kXbKeys + 4 * (buf * G + w.rank);
+        ll_store(dst, key, ep);
+        if (with_id) ll_store(dst + 2, (unsigned long long)(unsigned)var, ep);
+    }
     __syncthreads();  // previous readers of br are done
     if (tid < 32) {
         unsigned long long k = kKeyNone;
-        if (tid < G) k = ll_load(w.xbuf + kXbKeys + 2 * (buf * G + tid), ep, timeout_ns);
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            const unsigned long long o = __shfl_xor_sync(0xffffffffu, k, off);
-            k = o < k ? o : k;
+        int v = 0x7fffffff;
+        if (tid < G) {
+            const unsigned long long *src = w.xbuf + kXbKeys + 4 * (buf * G + tid);
+            k = ll_load(src, ep, timeout_ns);
+            if (with_id) v = (int)(unsigned)ll_load(src + 2, ep, timeout_ns);
         }
-        if (tid == 0) br.key[0] = k;
+        warp_argmin(k, v);
+        if (tid == 0) {
+            br.key[0] = k;
+            br.var[0] = v;
+        }
     }
     __syncthreads();
+    var = br.var[0];
     return br.key[0];
 }
 
 // ---- P2: pivot column p -> fc[] on every rank, min-ratio test on it (pick_leaving_idx :394-436) ----
+// corrected (rules 1, 2): zero ratios are kept and the None bookkeeping raises nothing.
 __device__ __forceinline__ void phase_ratio(BlockRed &br, const SingleWS &w, LoopCtl &ctl, int p, int e,
-                                            double tol, unsigned long long timeout_ns)
+                                            double tol, bool corrected, unsigned long long timeout_ns)
 {
     unsigned long long key = kKeyNone;
     int var = 0x7fffffff, crash = 0;
@@ -321,7 +359,7 @@ __device__ __forceinline__ void phase_ratio(BlockRed &br, const SingleWS &w, Loo
             const double coeff = -f;
             if (coeff > tol) {
                 const double ratio = snap(__ddiv_rn(w.bcol[i], coeff), tol);
-                if (ratio != 0.0) {
+                if (ratio != 0.0 || corrected) {
                     const unsigned long long k = order_key(ratio);
                     const int v = w.rowvar[i];
                     if (k < key || (k == key && v < var)) {
@@ -332,6 +370,7 @@ __device__ __forceinline__ void phase_ratio(BlockRed &br, const SingleWS &w, Loo
             }
         }
     }
+    if (corrected) crash = 0;
     block_argmin(br, key, var, crash);
     write_partial(w, ctl, 1, key, var, crash);
 }
@@ -507,26 +546,55 @@ __device__ __forceinline__ void single_pivot(cg::grid_group &grid, SweepSmem &sm
 __device__ __forceinline__ int single_run_loop(cg::grid_group &grid, BlockRed &br, SweepSmem &sm,
                                                const SingleWS &w, const SingleArgs &a, LoopCtl &ctl)
 {
+    const bool corrected = (a.rule != LPB200_RULE_REFERENCE);
+    ctl.streak = 0;
     for (;;) {
         unsigned long long key;
         int var, flag;
-        phase_entering(br, w, ctl, a.tol);
+        // Dantzig prices by coefficient until more than kDegenerateStreak pivots in a row made no progress
+        const int pricing = (a.rule == LPB200_RULE_DANTZIG && ctl.streak > kDegenerateStreak) ? LPB200_RULE_BLAND : a.rule;
+        phase_entering(br, w, ctl, a.tol, pricing);
         grid.sync();
         reduce_partials(br, w, ctl, 0, key, var, flag);
-        key = exchange_key(br, w, ctl, key, a.timeout_ns);
+        key = exchange_key(br, w, ctl, key, var, pricing == LPB200_RULE_DANTZIG, a.timeout_ns);
         if (key == kKeyNone) return 0;
-        const int p = (int)(key & 0xffffffffull);
+        const int p = (pricing == LPB200_RULE_DANTZIG) ? w.varpos[var] : (int)(key & 0xffffffffull);
         const int e = w.colvar[p];
-        phase_ratio(br, w, ctl, p, e, a.tol, a.timeout_ns);
+        phase_ratio(br, w, ctl, p, e, a.tol, corrected, a.timeout_ns);
         grid.sync();
         reduce_partials(br, w, ctl, 1, key, var, flag);
         if (flag) return LPB200_STATUS_REF_TYPE_ERROR;
         if (key == kKeyNone) return LPB200_STATUS_INFINITY;
+        ctl.streak = (key == kKeyZeroRatio) ? ctl.streak + 1 : 0;
         if (ctl.npiv >= a.max_pivots) return LPB200_STATUS_ITERATION_LIMIT;
         const int l = var;
         const int r = ~w.varpos[l];
         single_pivot(grid, sm, w, a, ctl, p, r, e, l);
     }
+}
+
+// Corrected modes: x_aux is still basic (at level 0) after phase 1 -> the non-basic variable with the
+// lowest id whose entry in x_aux's row r is non-zero; kKeyNone when the row is all zero (a redundant
+// constraint, left inert).  Grid-wide argmin + one key exchange, like P1.
+__device__ __forceinline__ unsigned long long driveout_key(cg::grid_group &grid, BlockRed &br, const SingleWS &w,
+                                                           const SingleArgs &a, LoopCtl &ctl, int r)
+{
+    unsigned long long key = kKeyNone;
+    int var = 0x7fffffff, flag = 0;
+    const double *row = w.T + (size_t)r * w.S;
+    const int lim = min(w.wloc, ctl.ncols - w.c_lo);
+    for (int kl = ctl.bid * kSgThreads + threadIdx.x; kl < lim; kl += ctl.nblk * kSgThreads) {
+        if (fabs(row[kl]) > a.tol) {
+            const int k = w.c_lo + kl;
+            const unsigned long long kk = ((unsigned long long)(unsigned)w.colvar[k] << 32) | (unsigned)k;
+            key = kk < key ? kk : key;
+        }
+    }
+    block_argmin(br, key, var, flag);
+    write_partial(w, ctl, 0, key, var, flag);
+    grid.sync();
+    reduce_partials(br, w, ctl, 0, key, var, flag);
+    return exchange_key(br, w, ctl, key, var, false, a.timeout_ns);
 }
 
 __global__ void __launch_bounds__(kSgThreads)
@@ -555,8 +623,10 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
     const int gtid = ctl.bid * kSgThreads + tid, gsize = ctl.nblk * kSgThreads;
     const int n = w.n, m = w.m, S = w.S, nv = n + m + 1;
     const double tol = a.tol;
+    const bool corrected = (a.rule != LPB200_RULE_REFERENCE);
     ctl.epoch = (w.nranks > 1) ? (unsigned)w.xbuf[kXbEpoch] : 0u;
     ctl.kx = 0u;
+    ctl.streak = 0;
 
     // ---- min_constant, idx = min_index(b) (:591): zeros count as +inf, first minimum wins ----
     int idx0;
@@ -565,7 +635,9 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
         int var = 0x7fffffff, flag = 0;
         for (int i = gtid; i < n; i += gsize) {
             const double bi = a.b[i];
-            const unsigned long long k = order_key(bi != 0.0 ? bi : CUDART_INF);
+            double kb = bi;  // the reference counts zeros as +inf (:161); the corrected modes take the true minimum
+            if (bi == 0.0) kb = corrected ? 0.0 : CUDART_INF;
+            const unsigned long long k = order_key(kb);
             if (k < key || (k == key && i < var)) {
                 key = k;
                 var = i;
@@ -580,7 +652,7 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
     const double min_c = a.b[idx0];
     const bool phase1 = (min_c < 0.0);
     int status = 0;
-    if (!phase1 && !(min_c > tol)) status = LPB200_STATUS_REF_ATTRIBUTE_ERROR;  // :626
+    if (!phase1 && !(min_c > tol) && !corrected) status = LPB200_STATUS_REF_ATTRIBUTE_ERROR;  // :626
     ctl.ncols = phase1 ? m + 1 : m;
     ctl.npiv = 0;
     ctl.track_dep = phase1;
@@ -654,14 +726,35 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
                 status = LPB200_STATUS_ITERATION_LIMIT;
             } else {
                 // forced pivot: x_aux enters, the most negative row leaves (:524)
-                phase_ratio(br, w, ctl, m, aux, tol, a.timeout_ns);  // column m -> fc[]; its partial is unused
+                phase_ratio(br, w, ctl, m, aux, tol, corrected, a.timeout_ns);  // column m -> fc[]; its partial is unused
                 grid.sync();
                 single_pivot(grid, sm, w, a, ctl, m, idx0, aux, idx0);
                 status = single_run_loop(grid, br, sm, w, a, ctl);  // :526
             }
             if (status == 0) {
                 if (!(fabs(w.bcol[n]) <= tol)) status = LPB200_STATUS_NO_SOLUTION;       // :528-530
-                else if (w.varpos[aux] < 0) status = LPB200_STATUS_REF_INDEX_ERROR;      // :541 -> :183
+                else if (w.varpos[aux] < 0) {
+                    if (!corrected) {
+                        status = LPB200_STATUS_REF_INDEX_ERROR;                          // :541 -> :183
+                    } else {
+                        // x_aux is basic at level 0: pivot it out on the lowest-id column with a non-zero
+                        // entry in its row, then let the loop run (the objective is -x_aux again: it ends at once)
+                        const int r = ~w.varpos[aux];
+                        const unsigned long long dk = driveout_key(grid, br, w, a, ctl, r);
+                        if (dk != kKeyNone) {
+                            if (ctl.npiv >= a.max_pivots) {
+                                status = LPB200_STATUS_ITERATION_LIMIT;
+                            } else {
+                                const int p = (int)(dk & 0xffffffffull);
+                                const int ev = w.colvar[p];
+                                phase_ratio(br, w, ctl, p, ev, tol, corrected, a.timeout_ns);  // column p -> fc[]
+                                grid.sync();
+                                single_pivot(grid, sm, w, a, ctl, p, r, ev, aux);
+                                status = single_run_loop(grid, br, sm, w, a, ctl);
+                            }
+                        }
+                    }
+                }
             }
             if (status == 0) {
                 // ---- rebuild the original objective (:537-541) ----
@@ -674,7 +767,7 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
                         const int s = s0 + tid;
                         const int v = (s < dsize) ? w.tab_d[s] : -1;
                         double f = 0.0;
-                        if (v >= n) f = a.c[v - n];
+                        if (v >= n && v < n + m) f = a.c[v - n];  // an inert basic x_aux (corrected modes) has none
                         const bool keep = (v >= n) && !(fabs(f) <= tol);
                         const unsigned msk = __ballot_sync(0xffffffffu, keep);
                         if (keep) {
@@ -700,7 +793,7 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
                         double o = 0.0;
                         if (k != kaux) {  // zip() truncates the x_aux column (:190)
                             const int v = w.colvar[k];
-                            o = (v >= n) ? a.c[v - n] : 0.0;
+                            o = (v >= n && v < n + m) ? a.c[v - n] : 0.0;
                             for (int t = 0; t < nlist; ++t)
                                 o = axpy_snap(o, w.cstage[t], w.T[(size_t)w.list[t] * S + kl], tol);
                         }
@@ -723,7 +816,7 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
                         w.basis0[q] = bits;
                     }
                     for (int i = gtid; i < n; i += gsize) w.untouched[i] = 1;
-                    if (gtid == 0) {  // independent.remove(nvars) (:574); the same sets live on
+                    if (gtid == 0 && kaux >= 0) {  // independent.remove(nvars) (:574); the same sets live on
                         PySet s = {w.state[ST_ISIZE], w.state[ST_IFILL], w.state[ST_IUSED]};
                         pyset_remove_slot(w.tab_i, s, w.colslot[kaux]);
                         w.state[ST_IUSED] = s.used;
@@ -816,10 +909,14 @@ static size_t carve_single(SingleWS *w, int n, int m, int rank, int nranks, unsi
 
 static const size_t kWsHeader = 4096;  // device copy of the rank's SingleWS lives at the workspace head
 
-static int check_single_args(int n, int m, double tol, int max_pivots, int log_cap)
+static int check_single_args(int n, int m, double tol, int max_pivots, int log_cap, int rule)
 {
     if (n < 1 || m < 1 || !(tol >= 0.0) || max_pivots < 0 || log_cap < 0) {
         set_error("lpb200_simplex_single: need n >= 1, m >= 1, tol >= 0, max_pivots >= 0");
+        return LPB200_E_INVALID;
+    }
+    if (rule != LPB200_RULE_REFERENCE && rule != LPB200_RULE_BLAND && rule != LPB200_RULE_DANTZIG) {
+        set_error("lpb200_simplex_single: rule must be LPB200_RULE_REFERENCE, LPB200_RULE_BLAND or LPB200_RULE_DANTZIG");
         return LPB200_E_INVALID;
     }
     if ((long long)n + m + 1 >= (1ll << 30)) {
@@ -859,9 +956,10 @@ static int pick_ctas_per_rank(const DeviceInfo &di, int n, int wcols, int groups
 }
 
 static int launch_single(const SingleWS *d_ranks, int groups, int cpr, const double *b, const double *c,
-                         double tol, int max_pivots, int log_cap, double timeout_s, cudaStream_t stream)
+                         double tol, int max_pivots, int rule, int log_cap, double timeout_s, cudaStream_t stream)
 {
     SingleArgs a;
+    a.rule = rule;
     a.b = b;
     a.c = c;
     a.tol = tol;
@@ -888,7 +986,18 @@ extern "C" int lpb200_simplex_single_device(int n, int m, const double *A, const
                                             int log_cap, void *workspace, int64_t workspace_bytes,
                                             void *stream_v)
 {
-    int rc = check_single_args(n, m, tol, max_pivots, log_cap);
+    return lpb200_simplex_single_ex_device(n, m, A, b, c, tol, max_pivots, LPB200_RULE_REFERENCE, status, x,
+                                           objective, npivots, pivot_log, log_cap, workspace, workspace_bytes,
+                                           stream_v);
+}
+
+extern "C" int lpb200_simplex_single_ex_device(int n, int m, const double *A, const double *b, const double *c,
+                                               double tol, int max_pivots, int rule, int32_t *status, double *x,
+                                               double *objective, int32_t *npivots, int32_t *pivot_log,
+                                               int log_cap, void *workspace, int64_t workspace_bytes,
+                                               void *stream_v)
+{
+    int rc = check_single_args(n, m, tol, max_pivots, log_cap, rule);
     if (rc) return rc;
     cudaStream_t stream = (cudaStream_t)stream_v;
     DeviceInfo di;
@@ -919,8 +1028,8 @@ extern "C" int lpb200_simplex_single_device(int n, int m, const double *A, const
     w.pivot_log = pivot_log;
     // pageable source: the runtime stages it before returning, so the stack copy is safe
     LPB_CUDA(cudaMemcpyAsync(workspace, &w, sizeof(w), cudaMemcpyHostToDevice, stream));
-    return launch_single(static_cast<const SingleWS *>(workspace), 1, cpr, b, c, tol, max_pivots, log_cap, 0.0,
-                         stream);
+    return launch_single(static_cast<const SingleWS *>(workspace), 1, cpr, b, c, tol, max_pivots, rule, log_cap,
+                         0.0, stream);
 }
 
 extern "C" int lpb200_simplex_single(int n, int m, const double *A, const double *b, const double *c,
@@ -928,7 +1037,16 @@ extern "C" int lpb200_simplex_single(int n, int m, const double *A, const double
                                      double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap,
                                      double *stats)
 {
-    int rc = check_single_args(n, m, tol, max_pivots, log_cap);
+    return lpb200_simplex_single_ex(n, m, A, b, c, tol, max_pivots, LPB200_RULE_REFERENCE, status, x, objective,
+                                    npivots, pivot_log, log_cap, stats);
+}
+
+extern "C" int lpb200_simplex_single_ex(int n, int m, const double *A, const double *b, const double *c,
+                                        double tol, int max_pivots, int rule, int32_t *status, double *x,
+                                        double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap,
+                                        double *stats)
+{
+    int rc = check_single_args(n, m, tol, max_pivots, log_cap, rule);
     if (rc) return rc;
     DeviceInfo di;
     rc = get_device_info(&di);
@@ -966,8 +1084,8 @@ extern "C" int lpb200_simplex_single(int n, int m, const double *A, const double
     if (rc == 0) {
         LPB_TRY(cudaEventRecord(ev0, 0));
         if (rc == 0)
-            rc = lpb200_simplex_single_device(n, m, dA, db, dc, tol, max_pivots, dst, dx, dobj, dnp, dlog,
-                                              log_cap, ws, wsb, nullptr);
+            rc = lpb200_simplex_single_ex_device(n, m, dA, db, dc, tol, max_pivots, rule, dst, dx, dobj, dnp, dlog,
+                                                 log_cap, ws, wsb, nullptr);
         LPB_TRY(cudaEventRecord(ev1, 0));
     }
     if (rc == 0) {
@@ -1101,7 +1219,19 @@ extern "C" int lpb200_simplex_sharded_device(lpb200_comm_t *comm, int n, int m, 
                                              void *workspace, int64_t workspace_bytes, double timeout_s,
                                              void *stream_v)
 {
-    int rc = check_single_args(n, m, tol, max_pivots, log_cap);
+    return lpb200_simplex_sharded_ex_device(comm, n, m, A_cols, lda, b, c, tol, max_pivots, LPB200_RULE_REFERENCE,
+                                            status, x, objective, npivots, pivot_log, log_cap, workspace,
+                                            workspace_bytes, timeout_s, stream_v);
+}
+
+extern "C" int lpb200_simplex_sharded_ex_device(lpb200_comm_t *comm, int n, int m, const double *A_cols,
+                                                int64_t lda, const double *b, const double *c, double tol,
+                                                int max_pivots, int rule, int32_t *status, double *x,
+                                                double *objective, int32_t *npivots, int32_t *pivot_log,
+                                                int log_cap, void *workspace, int64_t workspace_bytes,
+                                                double timeout_s, void *stream_v)
+{
+    int rc = check_single_args(n, m, tol, max_pivots, log_cap, rule);
     if (rc) return rc;
     if (comm == nullptr || !comm->connected) {
         set_error("lpb200_simplex_sharded: communicator is not connected");
@@ -1138,7 +1268,7 @@ extern "C" int lpb200_simplex_sharded_device(lpb200_comm_t *comm, int n, int m, 
     w.npivots = npivots;
     w.pivot_log = pivot_log;
     LPB_CUDA(cudaMemcpyAsync(workspace, &w, sizeof(w), cudaMemcpyHostToDevice, stream));
-    return launch_single(static_cast<const SingleWS *>(workspace), 1, cpr, b, c, tol, max_pivots, log_cap,
+    return launch_single(static_cast<const SingleWS *>(workspace), 1, cpr, b, c, tol, max_pivots, rule, log_cap,
                          timeout_s > 0.0 ? timeout_s : 20.0, stream);
 }
 
@@ -1150,7 +1280,16 @@ extern "C" int lpb200_simplex_sharded_emulated(int nranks, int n, int m, const d
                                                double *x, double *objective, int32_t *npivots,
                                                int32_t *pivot_log, int log_cap)
 {
-    int rc = check_single_args(n, m, tol, max_pivots, log_cap);
+    return lpb200_simplex_sharded_emulated_ex(nranks, n, m, A, b, c, tol, max_pivots, LPB200_RULE_REFERENCE, status,
+                                              x, objective, npivots, pivot_log, log_cap);
+}
+
+extern "C" int lpb200_simplex_sharded_emulated_ex(int nranks, int n, int m, const double *A, const double *b,
+                                                  const double *c, double tol, int max_pivots, int rule,
+                                                  int32_t *status, double *x, double *objective,
+                                                  int32_t *npivots, int32_t *pivot_log, int log_cap)
+{
+    int rc = check_single_args(n, m, tol, max_pivots, log_cap, rule);
     if (rc) return rc;
     if (nranks < 1 || nranks > kMaxRanks) {
         set_error("lpb200_simplex_sharded_emulated: need 1 <= nranks <= 32");
@@ -1212,7 +1351,7 @@ extern "C" int lpb200_simplex_sharded_emulated(int nranks, int n, int m, const d
         }
         LPB_TRY(cudaMemcpy(d_ranks, hw.data(), sizeof(SingleWS) * G, cudaMemcpyHostToDevice));
     }
-    if (rc == 0) rc = launch_single(d_ranks, G, cpr, db, dc, tol, max_pivots, log_cap, 20.0, nullptr);
+    if (rc == 0) rc = launch_single(d_ranks, G, cpr, db, dc, tol, max_pivots, rule, log_cap, 20.0, nullptr);
     if (rc == 0) LPB_TRY(cudaDeviceSynchronize());
     for (int g = 0; g < G && rc == 0; ++g) {
         const SingleWS &w = hw[g];

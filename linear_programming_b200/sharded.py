@@ -18,7 +18,7 @@ import ctypes
 import numpy as np
 
 from . import _lib
-from .simplex import DEFAULT_TOLERANCE, BatchResult, default_max_pivots
+from .simplex import DEFAULT_TOLERANCE, BatchResult, _rule_code, default_max_pivots
 
 
 def problem_shard(total: int, world: int, rank: int):
@@ -76,10 +76,10 @@ class ShardedComm:
             self._comm = ctypes.c_void_p()
 
     def solve(self, A_cols, b, c, n: int, m: int, tol: float = DEFAULT_TOLERANCE, max_pivots=None,
-              log_cap: int = 0, timeout_s: float = 20.0, workspace=None) -> BatchResult:
+              log_cap: int = 0, timeout_s: float = 20.0, workspace=None, rule: str = "reference") -> BatchResult:
         """Collective: every rank calls it with ITS columns of A (CUDA float64 tensor [n, c_count],
         any row stride) and the full b, c.  Enqueues on the current stream; results (replicated
-        on every rank) stay on the GPU."""
+        on every rank) stay on the GPU.  rule: as in solve_batch (every rank must pass the same)."""
         import torch
         L = _lib.lib()
         if max_pivots is None:
@@ -101,8 +101,9 @@ class ShardedComm:
             obj = torch.empty(1, dtype=torch.float64, device=dev)
             npiv = torch.empty(1, dtype=torch.int32, device=dev)
             log = torch.full((1, log_cap, 2), -1, dtype=torch.int32, device=dev) if log_cap > 0 else None
-            _lib.check(L.lpb200_simplex_sharded_device(
-                self._comm, n, m, a_ptr, lda, b.data_ptr(), c.data_ptr(), tol, max_pivots, status.data_ptr(),
+            _lib.check(L.lpb200_simplex_sharded_ex_device(
+                self._comm, n, m, a_ptr, lda, b.data_ptr(), c.data_ptr(), tol, max_pivots, _rule_code(rule),
+                status.data_ptr(),
                 x.data_ptr(), obj.data_ptr(), npiv.data_ptr(), log.data_ptr() if log is not None else None,
                 log_cap, ws.data_ptr(), wsb, timeout_s, stream))
         res = BatchResult(status, x, obj, npiv, log)
@@ -111,7 +112,7 @@ class ShardedComm:
 
 
 def solve_sharded_emulated(A, b, c, nranks: int, tol: float = DEFAULT_TOLERANCE, max_pivots=None,
-                           log_cap: int = 0):
+                           log_cap: int = 0, rule: str = "reference"):
     """The nranks-way column-sharded protocol with every rank emulated as a CTA group of one
     cooperative launch on the current GPU.  Returns one BatchResult whose leading axis is the
     RANK (all ranks must agree); used by the parity tests and on boxes with fewer GPUs."""
@@ -133,6 +134,7 @@ def solve_sharded_emulated(A, b, c, nranks: int, tol: float = DEFAULT_TOLERANCE,
 
     def vp(a):
         return ctypes.c_void_p(a.ctypes.data)
-    _lib.check(L.lpb200_simplex_sharded_emulated(G, n, m, vp(A), vp(b), vp(c), tol, max_pivots, vp(status), vp(x),
-                                                 vp(obj), vp(npiv), vp(log) if log is not None else None, log_cap))
+    _lib.check(L.lpb200_simplex_sharded_emulated_ex(G, n, m, vp(A), vp(b), vp(c), tol, max_pivots, _rule_code(rule),
+                                                    vp(status), vp(x), vp(obj), vp(npiv),
+                                                    vp(log) if log is not None else None, log_cap))
     return BatchResult(status, x, obj, npiv, log)

@@ -91,11 +91,9 @@ RULE_REFERENCE, RULE_BLAND, RULE_DANTZIG = 0, 1, 2
 _RULES = {"reference": RULE_REFERENCE, "bland": RULE_BLAND, "dantzig": RULE_DANTZIG}
 
 
-def _rule_code(rule: str, mode: str) -> int:
+def _rule_code(rule: str) -> int:
     if rule not in _RULES:
         raise ValueError("rule must be 'reference', 'bland' or 'dantzig'")
-    if rule != "reference" and mode == "single":
-        raise ValueError("rule=%r is served by the batch kernel only (mode='batch' or 'auto')" % rule)
     return _RULES[rule]
 
 
@@ -110,7 +108,8 @@ def solve_batch(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None 
     rule: "reference" reproduces the reference bit for bit, bugs included; "bland" is the
     corrected mode (include/lp_b200.h LPB200_RULE_BLAND: Bland's rule, zero ratios kept, x_aux
     driven out, no crash classes) and "dantzig" the same with largest-coefficient pricing (far
-    fewer pivots; Bland takes over on degenerate streaks) -- not reference behaviour, batch kernel only.
+    fewer pivots; Bland takes over on degenerate streaks) -- not reference behaviour; both kernels
+    serve all three rules with identical decisions.
     mode: "batch" (one CTA per LP, tableau in shared memory), "single" (grid-wide kernel, one
     LP after the other), "auto" (batch when the tableau fits shared memory).
     """
@@ -136,7 +135,7 @@ def solve_batch(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None 
     log = np.full((B, log_cap, 2), -1, dtype=np.int32) if log_cap > 0 else None
     if mode == "auto":
         mode = "batch" if fits_batch_kernel(n, m) else "single"
-    r_code = _rule_code(rule, mode)
+    r_code = _rule_code(rule)
     if mode == "batch":
         _lib.check(L.lpb200_simplex_batch_ex(B, n, m, _vp(A), a_code, _vp(b), _vp(c), tol, max_pivots, r_code,
                                              _vp(status), _vp(x), _vp(obj), _vp(npiv),
@@ -146,10 +145,10 @@ def solve_batch(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None 
             A = A.astype(np.float64)
         for p in range(B):
             lp = log[p] if log is not None else None
-            _lib.check(L.lpb200_simplex_single(n, m, _vp(A[p]), _vp(b[p]), _vp(c[p]), tol, max_pivots,
-                                               _vp(status[p:p + 1]), _vp(x[p]), _vp(obj[p:p + 1]),
-                                               _vp(npiv[p:p + 1]), _vp(lp) if lp is not None else None,
-                                               log_cap, None))
+            _lib.check(L.lpb200_simplex_single_ex(n, m, _vp(A[p]), _vp(b[p]), _vp(c[p]), tol, max_pivots, r_code,
+                                                  _vp(status[p:p + 1]), _vp(x[p]), _vp(obj[p:p + 1]),
+                                                  _vp(npiv[p:p + 1]), _vp(lp) if lp is not None else None,
+                                                  log_cap, None))
     else:
         raise ValueError("mode must be 'auto', 'batch' or 'single'")
     return BatchResult(status, x, obj, npiv, log)
@@ -179,7 +178,7 @@ def _solve_batch_torch(L, A, b, c, tol, max_pivots, log_cap, mode, rule="referen
         logp = log.data_ptr() if log is not None else None
         if mode == "auto":
             mode = "batch" if fits_batch_kernel(n, m) else "single"
-        r_code = _rule_code(rule, mode)
+        r_code = _rule_code(rule)
         if mode == "batch":
             _lib.check(L.lpb200_simplex_batch_ex_device(B, n, m, A.data_ptr(), a_code, b.data_ptr(),
                                                         c.data_ptr(), tol, max_pivots, r_code,
@@ -191,8 +190,8 @@ def _solve_batch_torch(L, A, b, c, tol, max_pivots, log_cap, mode, rule="referen
             wsb = int(L.lpb200_simplex_single_workspace_bytes(n, m))
             ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
             for p in range(B):
-                _lib.check(L.lpb200_simplex_single_device(
-                    n, m, A[p].data_ptr(), b[p].data_ptr(), c[p].data_ptr(), tol, max_pivots,
+                _lib.check(L.lpb200_simplex_single_ex_device(
+                    n, m, A[p].data_ptr(), b[p].data_ptr(), c[p].data_ptr(), tol, max_pivots, r_code,
                     status[p:].data_ptr(), x[p].data_ptr(), obj[p:].data_ptr(), npiv[p:].data_ptr(),
                     (log[p].data_ptr() if log is not None else None), log_cap, ws.data_ptr(), wsb, stream))
         else:

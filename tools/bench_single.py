@@ -12,6 +12,12 @@ written once), whatever the number of GPUs.  Inputs are generated o
 stream, max over ranks, barrier on both sides) is the whole persistent kernel including
 tableau set-up, so the set-up cost is measured separately with max_pivots = 0 and subtracted.
 `pivot_crc` is a checksum of the (entering, leaving) sequence: it must not depend on N.
+
+--rule bland|dantzig runs the corrected modes (lpb200_simplex_single_ex_device /
+lpb200_simplex_sharded_ex_device); with a generous --pivots the LP is solved TO OPTIMALITY and the
+line carries `solve_ms`, the status, the optimum and a size-independent check of the answer computed
+on the GPU outside the timed region: x >= 0, max(Ax - b) <= 1e-6 * max|b| and |c.x - optimum| <= 1e-9 * |optimum|
+(1-GPU runs only: the check needs all of A).
 """
 import argparse
 import json
@@ -36,6 +42,7 @@ def main():
     ap.add_argument("--pivots", type=int, default=200)
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--dist", default="D1")
+    ap.add_argument("--rule", default="reference", choices=["reference", "bland", "dantzig"])
     ap.add_argument("--gpus", type=int, default=None, help="informational; the world size comes from torchrun")
     args = ap.parse_args()
     n, m = args.n, args.m
@@ -45,6 +52,7 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     L = _lib.lib()
+    rule = {"reference": 0, "bland": 1, "dantzig": 2}[args.rule]
     comm = None
     if world > 1:
         import torch.distributed as dist
@@ -89,16 +97,16 @@ def main():
         torch.cuda.synchronize()
         e0.record()
         if world == 1:
-            _lib.check(L.lpb200_simplex_single_device(n, m, dA.data_ptr(), db.data_ptr(), dc.data_ptr(), 1e-9,
-                                                      maxpiv, st.data_ptr(), x.data_ptr(), obj.data_ptr(),
-                                                      npv.data_ptr(), log.data_ptr(), cap, ws.data_ptr(), wsb,
-                                                      stream))
+            _lib.check(L.lpb200_simplex_single_ex_device(n, m, dA.data_ptr(), db.data_ptr(), dc.data_ptr(), 1e-9,
+                                                         maxpiv, rule, st.data_ptr(), x.data_ptr(), obj.data_ptr(),
+                                                         npv.data_ptr(), log.data_ptr(), cap, ws.data_ptr(), wsb,
+                                                         stream))
         else:
-            _lib.check(L.lpb200_simplex_sharded_device(comm._comm, n, m, dA.data_ptr() if cnt else None,
-                                                       dA.stride(0) if cnt else 0, db.data_ptr(), dc.data_ptr(),
-                                                       1e-9, maxpiv, st.data_ptr(), x.data_ptr(), obj.data_ptr(),
-                                                       npv.data_ptr(), log.data_ptr(), cap, ws.data_ptr(), wsb,
-                                                       30.0, stream))
+            _lib.check(L.lpb200_simplex_sharded_ex_device(comm._comm, n, m, dA.data_ptr() if cnt else None,
+                                                          dA.stride(0) if cnt else 0, db.data_ptr(), dc.data_ptr(),
+                                                          1e-9, maxpiv, rule, st.data_ptr(), x.data_ptr(),
+                                                          obj.data_ptr(), npv.data_ptr(), log.data_ptr(), cap,
+                                                          ws.data_ptr(), wsb, 30.0, stream))
         e1.record()
         torch.cuda.synchronize()
         ms = max_over_ranks(e0.elapsed_time(e1))
@@ -122,8 +130,22 @@ def main():
     except Exception:
         pass
     gbs = alg / (per_pivot_ms * 1e-3) / 1e9
+    extra = {}
+    if args.rule != "reference":
+        extra = {"rule": args.rule, "solve_ms": ms, "objective": float(obj.item())}
+        if world == 1 and status == 0:
+            xs = x.clone()
+            slack = torch.mv(dA, xs) - db
+            cx = float(torch.dot(dc, xs).item())
+            o = float(obj.item())
+            extra["check"] = {"x_min": float(xs.min().item()), "max_Ax_minus_b": float(slack.max().item()),
+                              "b_scale": float(db.abs().max().item()), "c_dot_x": cx,
+                              "feasible": bool(xs.min().item() >= 0.0 and
+                                               slack.max().item() <= 1e-6 * db.abs().max().item()),
+                              "objective_matches": bool(abs(cx - o) <= 1e-9 * max(1.0, abs(o))),
+                              "basic_nonzero_x": int((xs != 0).sum().item())}
     if rank == 0:
-        print(json.dumps({
+        print(json.dumps({**extra, 
             "workload": "configs[4]: single dense LP, condensed tableau %d x %d (n=%d, m=%d), %s, "
                         "column-sharded over %d GPU(s)" % (n + 1, m + 1, n, m, args.dist, world),
             "n_gpus": world, "pivots": piv, "status": status, "pivot_crc": crc, "total_ms": ms,
