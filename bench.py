@@ -252,6 +252,9 @@ def ours_arm(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
+        # the ranks of one box share its host cores: each rank's narrowing pool (second lane of the
+        # host-pointer path) gets its share instead of every rank spawning one thread per core
+        os.environ.setdefault("LPB_HOST_THREADS", str(max(1, (os.cpu_count() or 1) // world)))
 
     def barrier():
         if world > 1:
@@ -359,6 +362,10 @@ def ours_arm(args):
             _lib.check(L.lpb200_simplex_batch(B, n, m, hA.data_ptr(), hb.data_ptr(), hc.data_ptr(), tol, cap,
                                               h_st.data_ptr(), h_x.data_ptr(), h_obj.data_ptr(),
                                               h_np.data_ptr(), None, 0))
+        def last_lanes():
+            out = (ctypes.c_int64 * 4)()
+            L.lpb200_simplex_batch_last_lanes(out)
+            return [int(v) for v in out]
         Ke = max(1, min(K, 3))
         e2e_step()  # warm-up
         barrier()
@@ -371,11 +378,17 @@ def ours_arm(args):
         barrier()
         same = bool(torch.equal(h_st, d_st.cpu()) and torch.equal(h_np, d_np.cpu())
                     and torch.equal(h_x.view(torch.int64), d_x.cpu().view(torch.int64)))
+        lanes = last_lanes()  # of the last timed step on this rank
         e2e = {"value": world * B * Ke / dt, "unit": UNIT,
-               "h2d_bytes_per_step": int(B * (n * m + n + m) * 8),
+               "h2d_bytes_per_step": int(lanes[3] + B * (n + m) * 8),
+               "host_fp64_bytes_per_step": int(B * (n * m + n + m) * 8),
                "d2h_bytes_per_step": int(B * (m * 8 + 8 + 4 + 4)), "steps": Ke,
                "ms_per_step": dt / Ke * 1e3, "matches_device_path": same,
-               "api": "lpb200_simplex_batch (host pointers, pinned; chunked 2-stream copy/solve pipeline)"}
+               "lanes": {"copy_engine_chunks": lanes[0], "host_narrowing_chunks": lanes[1],
+                         "narrowed_to_int8": lanes[2], "host_threads": int(L.lpb200_host_threads())},
+               "api": "lpb200_simplex_batch (fp64 host pointers, pinned; chunked copy/solve pipeline, two lanes: "
+                      "the copy engine ships fp64 chunks while the host cores narrow other chunks to int8 "
+                      "exactly -- answers bit-identical, see include/lp_b200.h)"}
 
     # ---- the same call with the constraint matrix held as int8 on the host (the reference parses
     #      integers, simplex.py:712-717; Config 4's coefficients are in [-100, 100]): 1/8 of the A bytes

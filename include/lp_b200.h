@@ -131,6 +131,25 @@ int lpb200_simplex_single(int n, int m, const double *A, const double *b, const 
                           int32_t *npivots, int32_t *pivot_log, int log_cap, double *stats);
 
 /*
+ * Host-core helpers of the end-to-end path (no GPU involved).  lpb200_simplex_batch[_ex] called with HOST
+ * pointers and an fp64 A runs two lanes over the chunks of a large batch: the copy engine ships chunks as
+ * they are while the host cores narrow other chunks to int8 -- only chunks in which every element is an
+ * integer in [-127, 127] (and no -0.0), so that the kernel's exact widening reproduces the caller's bits --
+ * and ship 1/8 of the bytes; answers are bit-identical either way (LPB_HOST_NARROW=0 disables the second
+ * lane, LPB_HOST_THREADS sets the pool size; default = the cores the process may run on, at most 32).
+ *   lpb200_narrow_f64_to_i8     the same exact narrowing for callers that want to hold A as int8 themselves
+ *                               (then pass LPB200_DTYPE_I8): 1 = dst is valid, 0 = some element is not
+ *                               representable (dst unspecified), < 0 = bad argument
+ *   lpb200_host_threads         size of the host pool
+ *   lpb200_simplex_batch_last_lanes  out4[0..3] = chunks served by the copy-engine lane / by the narrowing
+ *                               lane / narrowed to int8, and the bytes of A that crossed PCIe, in the calling
+ *                               thread's last chunked host-pointer batch call
+ */
+int lpb200_narrow_f64_to_i8(const double *src, int8_t *dst, int64_t count);
+int lpb200_host_threads(void);
+int lpb200_simplex_batch_last_lanes(int64_t *out4);
+
+/*
  * The same two calls with a choice of pivoting rule (LPB200_RULE_* above; LPB200_RULE_REFERENCE is what
  * the calls without _ex do).  The corrected rules make a large LP solvable to optimality: the
  * reference's set-order rule needs thousands of pivots where Dantzig pricing needs tens.  Decisions

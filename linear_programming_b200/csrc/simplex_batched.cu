@@ -36,8 +36,13 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <atomic>
+#include <string>
+#include <thread>
+
 #include "lp_common.cuh"
 #include "lp_host.h"
+#include "host_narrow.h"
 
 
 // ---- kernel variants (same source, different parameters) ----
@@ -276,16 +281,24 @@ extern "C" int lpb200_simplex_batch_device(int B, int n, int m, const double *A,
 // few thousand LPs); grown on demand, released when the thread exits.
 constexpr size_t kStageBytes = (size_t)4 << 20;  // calls smaller than this go through one pinned staging buffer
 
+// sets 0-1: the copy-engine lane; sets 2..: the host-narrowing lane (see below).  The narrowing lane is deeper:
+// its small copies queue behind the other lane's 96 MB transfers on the PCIe link, so a chunk takes a few
+// milliseconds to leave the GPU although the cores narrow one in about a millisecond.
+constexpr int kCopySets = 2, kNarrowSets = 4, kMaxSets = kCopySets + kNarrowSets;
+
 struct HostArena {
     int device = -1;
     size_t cap = 0;
-    char *mem[2] = {nullptr, nullptr};
-    cudaStream_t stream[2] = {nullptr, nullptr};
+    char *mem[kMaxSets] = {};
+    cudaStream_t stream[kMaxSets] = {};
+    cudaEvent_t done[kMaxSets] = {};  // blocking-sync events: "the set's last chunk has left the GPU"
     char *stage = nullptr;  // pinned host mirror of a small call's buffer set (one copy in, one copy out)
+    int8_t *narrow[kNarrowSets] = {};  // pinned int8 staging of the narrowing lane's sets
+    size_t narrow_cap = 0;
 
     void release_memory()
     {
-        for (int s = 0; s < 2; ++s) {
+        for (int s = 0; s < kMaxSets; ++s) {
             if (mem[s]) cudaFree(mem[s]);
             mem[s] = nullptr;
         }
@@ -294,13 +307,34 @@ struct HostArena {
     void release()
     {
         release_memory();
-        for (int s = 0; s < 2; ++s) {
+        for (int s = 0; s < kMaxSets; ++s) {
             if (stream[s]) cudaStreamDestroy(stream[s]);
+            if (done[s]) cudaEventDestroy(done[s]);
             stream[s] = nullptr;
+            done[s] = nullptr;
         }
         if (stage) cudaFreeHost(stage);
         stage = nullptr;
+        for (int s = 0; s < kNarrowSets; ++s) {
+            if (narrow[s]) cudaFreeHost(narrow[s]);
+            narrow[s] = nullptr;
+        }
+        narrow_cap = 0;
         device = -1;
+    }
+    int ensure_narrow(size_t bytes)
+    {
+        if (bytes <= narrow_cap) return 0;
+        for (int s = 0; s < kMaxSets; ++s)
+            if (stream[s]) LPB_CUDA(cudaStreamSynchronize(stream[s]));
+        for (int s = 0; s < kNarrowSets; ++s) {
+            if (narrow[s]) cudaFreeHost(narrow[s]);
+            narrow[s] = nullptr;
+        }
+        narrow_cap = 0;
+        for (int s = 0; s < kNarrowSets; ++s) LPB_CUDA(cudaMallocHost((void **)&narrow[s], bytes));
+        narrow_cap = bytes;
+        return 0;
     }
     int ensure(int dev, int nset, size_t bytes)
     {
@@ -311,13 +345,14 @@ struct HostArena {
         if (bytes > cap) {  // grow geometrically (at least 8 MB): a run of slightly larger batches reallocates once
             size_t want = cap * 2 > bytes ? cap * 2 : bytes;
             if (want < ((size_t)8 << 20)) want = (size_t)8 << 20;
-            for (int s = 0; s < 2; ++s)
+            for (int s = 0; s < kMaxSets; ++s)
                 if (stream[s]) LPB_CUDA(cudaStreamSynchronize(stream[s]));
             release_memory();
             cap = want;
         }
         for (int s = 0; s < nset; ++s) {
             if (!stream[s]) LPB_CUDA(cudaStreamCreateWithFlags(&stream[s], cudaStreamNonBlocking));
+            if (!done[s]) LPB_CUDA(cudaEventCreateWithFlags(&done[s], cudaEventBlockingSync | cudaEventDisableTiming));
             if (!mem[s]) LPB_CUDA(cudaMalloc((void **)&mem[s], cap));
         }
         if (!stage && bytes <= kStageBytes) LPB_CUDA(cudaMallocHost((void **)&stage, kStageBytes));
@@ -326,10 +361,40 @@ struct HostArena {
     ~HostArena() { release(); }
 };
 static thread_local HostArena g_arena;
+static thread_local long long g_last_lanes[4] = {0, 0, 0, 0};
 
 // Host-pointer entry point: the batch is cut into chunks that are copied in, solved and
 // copied out on two alternating streams, so the PCIe copy of chunk k+1 overlaps the solve of
 // chunk k and device memory stays bounded (two chunk-sized buffer sets).
+//
+// Large fp64 batches run TWO LANES that pull chunks off one counter (work stealing): the copy-engine
+// lane ships a chunk's A as the caller holds it (fp64, PCIe-bound: ~55 GB/s), while the host cores
+// narrow another chunk's A to int8 (host_narrow.cpp; only when every element survives the round trip
+// bit for bit, else the chunk goes over as fp64) and ship 1/8 of the bytes.  The kernel widens int8
+// exactly, so every answer is bit-identical to the single-lane path; the end-to-end rate becomes
+// (PCIe rate + narrowing rate of the host cores) instead of the PCIe rate.  LPB_HOST_NARROW=0 turns
+// the second lane off; LPB_HOST_THREADS sets the pool size (default: the cores of the process).
+constexpr size_t kNarrowSlice = (size_t)1 << 18;  // elements per pool work item (2 MB of fp64)
+struct NarrowJob {
+    const double *src;
+    int8_t *dst;
+    size_t total;
+    std::atomic<int> failed;
+};
+static void narrow_item(void *ctx, int i)
+{
+    NarrowJob *j = static_cast<NarrowJob *>(ctx);
+    if (j->failed.load(std::memory_order_relaxed)) return;  // the chunk goes over as fp64 anyway
+    const size_t lo = (size_t)i * kNarrowSlice;
+    const size_t len = j->total - lo < kNarrowSlice ? j->total - lo : kNarrowSlice;
+    if (!narrow_f64_to_i8(j->src + lo, j->dst + lo, len)) j->failed.store(1, std::memory_order_relaxed);
+}
+
+struct LaneResult {
+    int rc = 0;
+    std::string error;
+    long long chunks = 0, narrowed = 0, a_bytes = 0;
+};
 extern "C" int lpb200_simplex_batch_ex(int B, int n, int m, const void *A_v, int a_dtype, const double *b,
                                        const double *c, double tol, int max_pivots, int rule, int32_t *status,
                                        double *x, double *objective, int32_t *npivots, int32_t *pivot_log,
@@ -350,16 +415,29 @@ extern "C" int lpb200_simplex_batch_ex(int B, int n, int m, const void *A_v, int
     const size_t lpA = (size_t)n * m, lpb = (size_t)n, lpc = (size_t)m;
     const size_t lplog = pivot_log ? (size_t)log_cap * 2 : 0;
     const size_t lp_bytes = lpA * esz + (lpb + 2 * lpc + 1) * 8 + 8 + lplog * 4;
-    long long chunk = (long long)((size_t)(96u << 20) / lp_bytes);  // ~96 MB per chunk
+    size_t chunk_bytes = (size_t)96 << 20;  // ~96 MB per chunk
+    if (const char *e = getenv("LPB_HOST_CHUNK_BYTES")) {  // tests shrink it to drive both lanes with small batches
+        const long long v = atoll(e);
+        if (v > 0) chunk_bytes = (size_t)v;
+    }
+    long long chunk = (long long)(chunk_bytes / lp_bytes);
     if (chunk < 1) chunk = 1;
     if (chunk > B) chunk = B;
     const int nset = (chunk < B) ? 2 : 1;
+    // second lane: fp64 A, enough chunks to share, more than the calling thread to narrow with
+    bool two_lanes = (a_dtype == LPB200_DTYPE_F64) && (B + chunk - 1) / chunk >= 8;
+    if (two_lanes) {
+        const char *e = getenv("LPB_HOST_NARROW");
+        if (e && e[0] == '0') two_lanes = false;
+    }
+    const int nsets_used = two_lanes ? kMaxSets : nset;
     struct Set {
         char *A;
         double *b, *c, *x, *obj;
         int32_t *st, *np, *log;
         cudaStream_t stream;
-    } set[2] = {};
+    } set[kMaxSets] = {};
+    g_last_lanes[0] = g_last_lanes[1] = g_last_lanes[2] = g_last_lanes[3] = 0;
     rc = 0;
 #define LPB_TRY(call)                                                 \
     do {                                                              \
@@ -375,9 +453,10 @@ extern "C" int lpb200_simplex_batch_ex(int B, int n, int m, const void *A_v, int
         off[0] = 0;
         for (int i = 0; i < 8; ++i) off[i + 1] = off[i] + (sizes[i] + 255) / 256 * 256;
     }
-    rc = g_arena.ensure(di.device, nset, off[8]);
+    rc = g_arena.ensure(di.device, nsets_used, off[8]);
+    if (rc == 0 && two_lanes) rc = g_arena.ensure_narrow((size_t)chunk * lpA);
     if (rc) return rc;
-    for (int s = 0; s < nset; ++s) {
+    for (int s = 0; s < nsets_used; ++s) {
         char *base = g_arena.mem[s];
         set[s].A = base + off[0];
         set[s].b = reinterpret_cast<double *>(base + off[1]);
@@ -415,37 +494,102 @@ extern "C" int lpb200_simplex_batch_ex(int B, int n, int m, const void *A_v, int
 #undef LPB_TRY
         return rc;
     }
+    // One lane: claims chunks off the shared counter and runs them on its two buffer sets.
+    HostArena *const arena = &g_arena;  // thread_local: the copier thread must use the CALLER's arena
+    std::atomic<long long> next_chunk{0};
+    const long long nchunks = (B + chunk - 1) / chunk;
+    auto run_lane = [&](int lane, bool narrow, bool backpressure, LaneResult *out) {
+        int rc = 0;
 #define LPB_TRY(call)                                                 \
     do {                                                              \
         cudaError_t _e = (call);                                      \
         if (_e != cudaSuccess && rc == 0) rc = cuda_fail(_e, #call);  \
     } while (0)
-    int k = 0;
-    for (long long lo = 0; lo < B && rc == 0; lo += chunk, ++k) {
-        const long long cnt = (B - lo < chunk) ? (B - lo) : chunk;
-        Set &q = set[k % nset];
-        LPB_TRY(cudaMemcpyAsync(q.A, A + lo * lpA * esz, cnt * lpA * esz, cudaMemcpyHostToDevice, q.stream));
-        LPB_TRY(cudaMemcpyAsync(q.b, b + lo * lpb, cnt * lpb * 8, cudaMemcpyHostToDevice, q.stream));
-        LPB_TRY(cudaMemcpyAsync(q.c, c + lo * lpc, cnt * lpc * 8, cudaMemcpyHostToDevice, q.stream));
-        if (lplog) LPB_TRY(cudaMemsetAsync(q.log, 0xff, cnt * lplog * 4, q.stream));
-        if (rc == 0)
-            rc = lpb200_simplex_batch_ex_device((int)cnt, n, m, q.A, a_dtype, q.b, q.c, tol, max_pivots, rule, q.st,
-                                                q.x, q.obj, q.np, q.log, log_cap, q.stream);
-        LPB_TRY(cudaMemcpyAsync(status + lo, q.st, cnt * 4, cudaMemcpyDeviceToHost, q.stream));
-        LPB_TRY(cudaMemcpyAsync(x + lo * lpc, q.x, cnt * lpc * 8, cudaMemcpyDeviceToHost, q.stream));
-        LPB_TRY(cudaMemcpyAsync(objective + lo, q.obj, cnt * 8, cudaMemcpyDeviceToHost, q.stream));
-        LPB_TRY(cudaMemcpyAsync(npivots + lo, q.np, cnt * 4, cudaMemcpyDeviceToHost, q.stream));
-        if (lplog)
-            LPB_TRY(cudaMemcpyAsync(pivot_log + lo * lplog, q.log, cnt * lplog * 4, cudaMemcpyDeviceToHost, q.stream));
+        LPB_TRY(cudaSetDevice(di.device));
+        int k = 0, misses = 0;
+        while (rc == 0) {
+            const long long ci = next_chunk.fetch_add(1, std::memory_order_relaxed);
+            if (ci >= nchunks) break;
+            const long long lo = ci * chunk;
+            const long long cnt = (B - lo < chunk) ? (B - lo) : chunk;
+            const int si = (lane == 0) ? (k++ % kCopySets) : kCopySets + (k++ % kNarrowSets);
+            Set &q = set[si];
+            // the set's previous chunk has left the GPU: bounds the lane to two chunks in flight (so the other
+            // lane gets its share of the counter) and frees the set's pinned staging buffer
+            if (backpressure) LPB_TRY(cudaEventSynchronize(arena->done[si]));
+            int dtype = a_dtype;
+            const char *srcA = A + lo * lpA * esz;
+            size_t bytesA = (size_t)cnt * lpA * esz;
+            if (narrow) {
+                NarrowJob job = {reinterpret_cast<const double *>(srcA), arena->narrow[si - kCopySets], (size_t)cnt * lpA, {0}};
+                const int items = (int)((job.total + kNarrowSlice - 1) / kNarrowSlice);
+                HostPool::instance().parallel_for(items, narrow_item, &job);
+                if (job.failed.load() == 0) {
+                    dtype = LPB200_DTYPE_I8;
+                    srcA = reinterpret_cast<const char *>(job.dst);
+                    bytesA = job.total;
+                    ++out->narrowed;
+                } else if (++misses >= 2 && out->narrowed == 0) {
+                    narrow = false;  // not small-integer data: stop scanning, this lane copies fp64 like the other
+                }
+            }
+            LPB_TRY(cudaMemcpyAsync(q.A, srcA, bytesA, cudaMemcpyHostToDevice, q.stream));
+            LPB_TRY(cudaMemcpyAsync(q.b, b + lo * lpb, cnt * lpb * 8, cudaMemcpyHostToDevice, q.stream));
+            LPB_TRY(cudaMemcpyAsync(q.c, c + lo * lpc, cnt * lpc * 8, cudaMemcpyHostToDevice, q.stream));
+            if (lplog) LPB_TRY(cudaMemsetAsync(q.log, 0xff, cnt * lplog * 4, q.stream));
+            if (rc == 0)
+                rc = lpb200_simplex_batch_ex_device((int)cnt, n, m, q.A, dtype, q.b, q.c, tol, max_pivots, rule, q.st,
+                                                    q.x, q.obj, q.np, q.log, log_cap, q.stream);
+            LPB_TRY(cudaMemcpyAsync(status + lo, q.st, cnt * 4, cudaMemcpyDeviceToHost, q.stream));
+            LPB_TRY(cudaMemcpyAsync(x + lo * lpc, q.x, cnt * lpc * 8, cudaMemcpyDeviceToHost, q.stream));
+            LPB_TRY(cudaMemcpyAsync(objective + lo, q.obj, cnt * 8, cudaMemcpyDeviceToHost, q.stream));
+            LPB_TRY(cudaMemcpyAsync(npivots + lo, q.np, cnt * 4, cudaMemcpyDeviceToHost, q.stream));
+            if (lplog)
+                LPB_TRY(cudaMemcpyAsync(pivot_log + lo * lplog, q.log, cnt * lplog * 4, cudaMemcpyDeviceToHost,
+                                        q.stream));
+            if (backpressure) LPB_TRY(cudaEventRecord(arena->done[si], q.stream));
+            ++out->chunks;
+            out->a_bytes += (long long)bytesA;
+        }
+#undef LPB_TRY
+        out->rc = rc;
+        if (rc) out->error = lpb200_last_error();
+    };
+    LaneResult lane_res[2];
+    if (two_lanes) {
+        std::thread copier(run_lane, 0, false, true, &lane_res[0]);  // the copy-engine lane only enqueues and waits
+        run_lane(1, true, true, &lane_res[1]);                       // the caller drives the host pool
+        copier.join();
+    } else {
+        run_lane(0, false, false, &lane_res[0]);
     }
-    for (int s = 0; s < nset; ++s) {
+    for (int l = 0; l < 2 && rc == 0; ++l) {
+        if (lane_res[l].rc) {
+            rc = lane_res[l].rc;
+            set_error(lane_res[l].error);
+        }
+    }
+    for (int s = 0; s < nsets_used; ++s) {
         if (set[s].stream) {
             cudaError_t e = cudaStreamSynchronize(set[s].stream);
             if (e != cudaSuccess && rc == 0) rc = cuda_fail(e, "cudaStreamSynchronize");
         }
     }
-#undef LPB_TRY
+    g_last_lanes[0] = lane_res[0].chunks;
+    g_last_lanes[1] = lane_res[1].chunks;
+    g_last_lanes[2] = lane_res[1].narrowed;
+    g_last_lanes[3] = lane_res[0].a_bytes + lane_res[1].a_bytes;
     return rc;
+}
+
+// Chunks served by the copy-engine lane / the narrowing lane / narrowed to int8, and the bytes of A that
+// crossed PCIe, in the calling thread's last chunked lpb200_simplex_batch[_ex] call (diagnostics for
+// bench.py and the tests).
+extern "C" int lpb200_simplex_batch_last_lanes(int64_t *out4)
+{
+    if (out4 == nullptr) return LPB200_E_INVALID;
+    for (int i = 0; i < 4; ++i) out4[i] = g_last_lanes[i];
+    return 0;
 }
 
 extern "C" int lpb200_simplex_batch(int B, int n, int m, const double *A, const double *b, const double *c,

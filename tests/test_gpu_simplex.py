@@ -383,3 +383,56 @@ def test_automatic_variant_choice_large_batches_vs_oracle(oracle_lib):
         assert np.array_equal(res.status, st)
         assert np.array_equal(res.npivots, npiv)
         assert np.array_equal(res.x.view(np.int64), x.view(np.int64))
+
+
+def _lanes():
+    import ctypes
+    from linear_programming_b200 import _lib
+    out = (ctypes.c_int64 * 4)()
+    assert _lib.lib().lpb200_simplex_batch_last_lanes(out) == 0
+    return [int(v) for v in out]
+
+
+@pytest.mark.parametrize("kind", ["integers", "mixed", "fractional"])
+def test_two_lane_host_path_is_bit_identical(oracle_lib, monkeypatch, kind):
+    """The host-pointer call on a large fp64 batch runs two lanes (copy engine ships fp64 chunks, host cores
+    narrow other chunks to int8 exactly -- include/lp_b200.h).  Chunks shrunk to 64 KB so that 700 small LPs
+    make ~90 chunks.  'mixed': every 5th LP holds a fraction or a -0.0, so its chunk must go over as fp64;
+    'fractional': nothing can be narrowed and the second lane turns into a second copy lane.  Answers must
+    equal the single-lane call and the oracle bit for bit."""
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    A, b, c = workloads.simplex_batch("D3", 700, 24, 31, seed=41)
+    if kind == "mixed":
+        A[::5, 3, 7] = 0.5
+        A[2::10, 0, 0] = -0.0
+    elif kind == "fractional":
+        A = A + 0.25
+    monkeypatch.setenv("LPB_HOST_CHUNK_BYTES", str(64 * 1024))
+    monkeypatch.setenv("LPB_HOST_NARROW", "0")
+    one = lp.solve_batch(A, b, c, max_pivots=20000, log_cap=16)
+    assert _lanes()[1] == 0 and _lanes()[0] > 50
+    monkeypatch.setenv("LPB_HOST_NARROW", "1")
+    two = lp.solve_batch(A, b, c, max_pivots=20000, log_cap=16)
+    cl, nl, narrowed, abytes = _lanes()
+    assert cl + nl == _ceil_div(700, (64 * 1024) // _lp_bytes(24, 31, 16))
+    if kind == "integers":
+        assert narrowed == nl and nl > 0 and abytes < A.nbytes
+    elif kind == "mixed":
+        assert 0 <= narrowed <= nl
+    else:
+        assert narrowed == 0 and abytes == A.nbytes
+    st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=20000)
+    for r in (one, two):
+        assert np.array_equal(r.status, st) and np.array_equal(r.npivots, npiv)
+        assert np.array_equal(r.x.view(np.int64), x.view(np.int64))
+        assert np.array_equal(r.objective.view(np.int64), obj.view(np.int64))
+    assert np.array_equal(one.pivot_log, two.pivot_log)
+
+
+def _lp_bytes(n, m, log_cap):
+    return n * m * 8 + (n + 2 * m + 1) * 8 + 8 + log_cap * 2 * 4
+
+
+def _ceil_div(a, b):
+    return (a + b - 1) // b
