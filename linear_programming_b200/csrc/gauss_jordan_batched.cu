@@ -52,14 +52,22 @@ constexpr int kGjRows = LPB_GJ_ROWS;
 #ifndef LPB_GJ_BLOCK
 #define LPB_GJ_BLOCK 32
 #endif
+#ifndef LPB_GJ_PAIR_BLOCK
+#define LPB_GJ_PAIR_BLOCK 32
+#endif
+constexpr int kGjPairBlock = LPB_GJ_PAIR_BLOCK;  // rows per work item of the column-pair trailing update
 constexpr int kGjBlockRows = LPB_GJ_BLOCK;  // rows per work item of the trailing update   // rows in flight per thread in the trailing update
 
 // a: [B][n][n] working copy (destroyed), x: [B][n] holds b on entry and the solution on exit.
 #ifndef LPB_GJ_MINB
 #define LPB_GJ_MINB 2
 #endif
-template <bool kPartial, int kGjThreads>
-__global__ void __launch_bounds__(kGjThreads, (kGjThreads == kGjMaxThreads ? LPB_GJ_MINB : 1024 / kGjThreads))
+// kPairs: the trailing update takes TWO adjacent columns per thread (one 16-byte load/store per row, the
+// row's K scales read from shared memory once for both columns): half the shared-memory and global
+// instructions per fp64 operation.  Needs 2 x K pivot-row values in registers, hence 256-thread CTAs at
+// 128 registers, two per SM.  Same operations per element in the same order: bit-identical.
+template <bool kPartial, int kGjThreads, bool kPairs = false>
+__global__ void __launch_bounds__(kGjThreads, (kPairs ? 2 : (kGjThreads == kGjMaxThreads ? LPB_GJ_MINB : 1024 / kGjThreads)))
 gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restrict__ x_all)
 {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -211,16 +219,83 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
             }
         }
         __syncthreads();
+        // column pairs: every row of `a` starts 16-byte aligned (n even) and the trailing block starts on an
+        // even column; the b column (and everything, when the conditions fail) goes through the one-column loop
+        const bool pairs = kPairs && Kp == kGjK && (n & 1) == 0 && (jfirst & 1) == 0;
+        if (kPairs && pairs) {
+            const int nblk = (n + kGjPairBlock - 1) / kGjPairBlock;
+            const int CP = (n - jfirst) >> 1;
+            const int items = CP * nblk;
+            const size_t cs2 = (size_t)(n >> 1);  // row stride in double2
+            for (int item = tid; item < items; item += kGjThreads) {
+                const int blk = item / CP, jp = item - blk * CP;
+                const int i0 = blk * kGjPairBlock, i1 = min(n, i0 + kGjPairBlock);
+                // the block's rows minus the panel's pivot rows [k0, k0 + K): row of the c-th one
+                const int before = min(max(k0 - i0, 0), i1 - i0);
+                const int inside = max(0, min(i1, k0 + kGjK) - max(i0, k0));
+                const int nrows = (i1 - i0) - inside;
+                double2 *col = reinterpret_cast<double2 *>(a + jfirst + 2 * jp);
+                double2 R[kGjK];
+#pragma unroll
+                for (int q = 0; q < kGjK; ++q) R[q] = __ldcg(col + (size_t)(k0 + q) * cs2);
+#define LPB_GJ_ROW(c) (i0 + (c) + ((c) >= before ? inside : 0))
+                // software pipeline: the loads of chunk c+2 are in flight while chunk c is worked on
+                double2 cur[2], nxt[2];
+                int rcur[2], rnxt[2];
+#pragma unroll
+                for (int r = 0; r < 2; ++r) {
+                    rcur[r] = LPB_GJ_ROW(min(r, nrows - 1));
+                    if (nrows > 0) cur[r] = col[(size_t)rcur[r] * cs2];
+                }
+                for (int c = 0; c < nrows; c += 2) {
+                    const bool more = c + 2 < nrows;
+#pragma unroll
+                    for (int r = 0; r < 2; ++r) {
+                        rnxt[r] = LPB_GJ_ROW(min(c + 2 + r, nrows - 1));
+                        if (more) nxt[r] = col[(size_t)rnxt[r] * cs2];
+                    }
+#pragma unroll
+                    for (int r = 0; r < 2; ++r) {
+                        const int cp = c + 2 * kGjAhead + r;
+                        if (cp < nrows) asm volatile("prefetch.global.L1 [%0];" ::"l"(col + (size_t)LPB_GJ_ROW(cp) * cs2));
+                    }
+                    const double *P0 = P + (size_t)rcur[0] * kGjPS, *P1 = P + (size_t)rcur[1] * kGjPS;
+#pragma unroll
+                    for (int t = 0; t < kGjK; t += 2) {
+                        const double2 s0 = *reinterpret_cast<const double2 *>(P0 + t);
+                        const double2 s1 = *reinterpret_cast<const double2 *>(P1 + t);
+                        cur[0].x = __dadd_rn(cur[0].x, __dmul_rn(s0.x, R[t].x));
+                        cur[0].y = __dadd_rn(cur[0].y, __dmul_rn(s0.x, R[t].y));
+                        cur[1].x = __dadd_rn(cur[1].x, __dmul_rn(s1.x, R[t].x));
+                        cur[1].y = __dadd_rn(cur[1].y, __dmul_rn(s1.x, R[t].y));
+                        cur[0].x = __dadd_rn(cur[0].x, __dmul_rn(s0.y, R[t + 1].x));
+                        cur[0].y = __dadd_rn(cur[0].y, __dmul_rn(s0.y, R[t + 1].y));
+                        cur[1].x = __dadd_rn(cur[1].x, __dmul_rn(s1.y, R[t + 1].x));
+                        cur[1].y = __dadd_rn(cur[1].y, __dmul_rn(s1.y, R[t + 1].y));
+                    }
+                    col[(size_t)rcur[0] * cs2] = cur[0];
+                    if (c + 1 < nrows) col[(size_t)rcur[1] * cs2] = cur[1];  // odd tail: the twin of row 0 is dropped
+#pragma unroll
+                    for (int r = 0; r < 2; ++r) {
+                        cur[r] = nxt[r];
+                        rcur[r] = rnxt[r];
+                    }
+                }
+#undef LPB_GJ_ROW
+            }
+        }
         {
             // work items = (column, block of kGjBlockRows rows), dealt round-robin: consecutive
             // threads take consecutive columns (coalesced) and every thread gets the same number
             // of items to within one, however narrow the trailing matrix has become
             const int nblk = (n + kGjBlockRows - 1) / kGjBlockRows;
-            const int items = C * nblk;
+            const int jskip = (kPairs && pairs) ? (n - jfirst) : 0;  // columns already done as pairs
+            const int C1 = C - jskip;
+            const int items = C1 * nblk;
             for (int item = tid; item < items; item += kGjThreads) {
-                const int blk = item / C, jj = item - blk * C;
+                const int blk = item / C1, jj = item - blk * C1;
                 const int i0 = blk * kGjBlockRows, i1 = min(n, i0 + kGjBlockRows);
-                const int j = jfirst + jj;
+                const int j = jfirst + jskip + jj;
                 double *col = (j < n) ? (a + j) : bx;
                 const size_t cs = (j < n) ? (size_t)n : 1;
                 double R[kGjK];
@@ -306,16 +381,22 @@ static int gj_launch(int B, int n, double *wa, double *x, int pivoting, const De
     }
     // CTA size by system size: a 512-thread CTA idles on the small systems the course feeds this solver
     // (energy_values: n <= 20), and two of them fill an SM; 64- and 128-thread CTAs put 16 / 8 there.
-#define LPB_GJ_LAUNCH(PP, T)                                                                                         \
+#define LPB_GJ_LAUNCH(PP, T, ...)                                                                                    \
     do {                                                                                                             \
-        LPB_CUDA(cudaFuncSetAttribute(gauss_jordan_batched_kernel<PP, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                      smem));                                                                        \
-        gauss_jordan_batched_kernel<PP, T><<<B, T, smem, stream>>>(n, wa, x);                                       \
+        LPB_CUDA(cudaFuncSetAttribute(gauss_jordan_batched_kernel<PP, T, ##__VA_ARGS__>,                             \
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, smem));                           \
+        gauss_jordan_batched_kernel<PP, T, ##__VA_ARGS__><<<B, T, smem, stream>>>(n, wa, x);                        \
     } while (0)
     const bool pp = (pivoting == LPB200_PIVOT_PARTIAL);
     int threads = n <= 64 ? 64 : (n <= 128 ? 128 : (n <= 256 ? 256 : kGjMaxThreads));  // measured: tools/gpu/gj_small_rates.py
     if (const char *g = getenv("LPB_DEBUG_GJ_THREADS")) threads = atoi(g);
-    if (threads == 64) {
+    // n > 256, even: the column-pair trailing update on 256-thread CTAs at 128 registers (two per SM) --
+    // 80.6 ms against 88.8 ms of the one-column 512-thread kernel on 4096 x 512 x 512 (tools/bench_gj.py)
+    bool use_pairs = (n > 256) && (n & 1) == 0;
+    if (const char *g = getenv("LPB_DEBUG_GJ_PAIRS")) use_pairs = atoi(g) != 0;
+    if (use_pairs) {
+        if (pp) LPB_GJ_LAUNCH(true, 256, true); else LPB_GJ_LAUNCH(false, 256, true);
+    } else if (threads == 64) {
         if (pp) LPB_GJ_LAUNCH(true, 64); else LPB_GJ_LAUNCH(false, 64);
     } else if (threads == 128) {
         if (pp) LPB_GJ_LAUNCH(true, 128); else LPB_GJ_LAUNCH(false, 128);

@@ -92,3 +92,25 @@ def test_partial_pivoting_device_tensors_and_workload(oracle_lib):
     torch.cuda.synchronize()
     want, _ = oracle_lib.gauss_jordan_batch(a, b, full_sweep=False, pivoting="partial")
     assert np.array_equal(x.cpu().numpy().view(np.int64), want.view(np.int64))
+
+
+@pytest.mark.parametrize("pairs", ["0", "1"])
+@pytest.mark.parametrize("n,count,frac,pivoting", [(512, 6, 0.5, "reference"), (258, 6, 0.5, "reference"),
+                                                   (300, 5, 1.0, "reference"), (34, 20, 0.5, "reference"),
+                                                   (100, 10, 0.5, "reference"), (257, 4, 0.5, "reference"),
+                                                   (386, 4, 0.0, "partial"), (512, 4, 0.0, "partial")])
+def test_column_pair_variant_vs_oracle(oracle_lib, monkeypatch, pairs, n, count, frac, pivoting):
+    """Both trailing-update variants forced on every shape class: the column-pair kernel (default for even
+    n > 256) handles rows that are not a multiple of the block, pivot rows in the middle of a block, panels
+    truncated by a zero pivot (odd first trailing column -> one-column fallback for that panel) and odd n
+    (fallback throughout); the one-column kernel is the default elsewhere.  Same bits from both."""
+    import linear_programming_b200 as lp
+    monkeypatch.setenv("LPB_DEBUG_GJ_PAIRS", pairs)
+    if pivoting == "partial":
+        from test_oracle_gauss_jordan import _hard_systems
+        a, b, _ = _hard_systems(count, n, seed=6)
+    else:
+        a, b = workloads.gauss_jordan_batch(count, n=n, seed=3, swap_frac=frac)
+    x = lp.solve_equation_batch(a, b, pivoting=pivoting)
+    want, _ = oracle_lib.gauss_jordan_batch(a, b, full_sweep=False, pivoting=pivoting)
+    assert np.array_equal(x.view(np.int64), want.view(np.int64))

@@ -35,19 +35,20 @@ def main():
                                  ("D3", 7, 5, 50), ("D2", 200, 40000, 60)):
         A, b, c = workloads.simplex_batch(dist_name, 1, n, m, seed=11)
         A, b, c = A[0], b[0], c[0]
-        want = oracle.simplex(A, b, c, max_pivots=cap)
         lo, cnt = column_shard(m, world, rank)
         dA = torch.from_numpy(np.ascontiguousarray(A[:, lo:lo + cnt])).to(dev)
-        res = None
-        for _ in range(2):  # twice on the same communicator: epochs carry over between solves
-            res = comm.solve(dA, torch.from_numpy(b).to(dev), torch.from_numpy(c).to(dev), n, m,
-                             max_pivots=cap, log_cap=cap)
-            torch.cuda.synchronize()
-        good = (int(res.status[0]) == want["status"] and res.pivots(0) == want["pivots"]
-                and np.array_equal(res.x[0].cpu().numpy().view(np.int64), want["x"].view(np.int64)))
-        ok = ok and good
-        report.append({"dist": dist_name, "n": n, "m": m, "status": want["status"], "pivots": want["npivots"],
-                       "match": bool(good)})
+        for rule in ("reference", "bland", "dantzig"):  # the corrected rules: Dantzig's key is two packets per rank
+            want = oracle.simplex(A, b, c, max_pivots=cap, rule=rule)
+            res = None
+            for _ in range(2):  # twice on the same communicator: epochs carry over between solves
+                res = comm.solve(dA, torch.from_numpy(b).to(dev), torch.from_numpy(c).to(dev), n, m,
+                                 max_pivots=cap, log_cap=cap, rule=rule)
+                torch.cuda.synchronize()
+            good = (int(res.status[0]) == want["status"] and res.pivots(0) == want["pivots"]
+                    and np.array_equal(res.x[0].cpu().numpy().view(np.int64), want["x"].view(np.int64)))
+            ok = ok and good
+            report.append({"dist": dist_name, "n": n, "m": m, "rule": rule, "status": want["status"],
+                           "pivots": want["npivots"], "match": bool(good)})
     flags = [None] * world
     dist.all_gather_object(flags, bool(ok))
     if rank == 0:
