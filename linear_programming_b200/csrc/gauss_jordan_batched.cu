@@ -32,6 +32,7 @@
 // start of pass 1.  No panel is ever truncated; the arithmetic per element is unchanged.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #include "lp_common.cuh"
 #include "lp_host.h"
@@ -58,6 +59,44 @@ constexpr int kGjRows = LPB_GJ_ROWS;
 constexpr int kGjPairBlock = LPB_GJ_PAIR_BLOCK;  // rows per work item of the column-pair trailing update
 constexpr int kGjBlockRows = LPB_GJ_BLOCK;  // rows per work item of the trailing update   // rows in flight per thread in the trailing update
 
+// Step Q of the panel factorisation for the rows of one thread: whole panel rows go through registers
+// with 16-byte shared-memory accesses (conflict-free at a row stride of 9 x 16 bytes).  Element by
+// element, every load would wait for the store of the previous element (the compiler cannot tell
+// P[i][t] from P[k][t+1]) and 8-byte accesses at this stride are 4-way bank conflicts.  Columns >= K of
+// a short last panel are padding: updated, never used.
+template <int Q, int kThreads>
+__device__ __forceinline__ void gj_factor_rows(double *P, int n, int k, int tid)
+{
+    constexpr int T0 = Q & ~1;  // first 16-byte piece that holds a column >= Q
+    double pk[kGjK];
+    {
+        const double2 *Pk2 = reinterpret_cast<const double2 *>(P + (size_t)k * kGjPS);
+#pragma unroll
+        for (int t = T0; t < kGjK; t += 2) {
+            const double2 v = Pk2[t >> 1];
+            pk[t] = v.x;
+            pk[t + 1] = v.y;
+        }
+    }
+    for (int i = tid; i < n; i += kThreads) {
+        if (i == k) continue;
+        double2 *Pi2 = reinterpret_cast<double2 *>(P + (size_t)i * kGjPS);
+        double r[kGjK];
+#pragma unroll
+        for (int t = T0; t < kGjK; t += 2) {
+            const double2 v = Pi2[t >> 1];
+            r[t] = v.x;
+            r[t + 1] = v.y;
+        }
+        const double s = -r[Q];  // scale = -1 * a[i][k]  (:151)
+#pragma unroll
+        for (int t = Q + 1; t < kGjK; ++t) r[t] = __dadd_rn(r[t], __dmul_rn(s, pk[t]));
+        r[Q] = s;  // keep the scale for the trailing update
+#pragma unroll
+        for (int t = T0; t < kGjK; t += 2) Pi2[t >> 1] = make_double2(r[t], r[t + 1]);
+    }
+}
+
 // a: [B][n][n] working copy (destroyed), x: [B][n] holds b on entry and the solution on exit.
 #ifndef LPB_GJ_MINB
 #define LPB_GJ_MINB 2
@@ -81,6 +120,17 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
     double *a = a_all + (size_t)blockIdx.x * n * n;
     double *bx = x_all + (size_t)blockIdx.x * n;
 
+#ifdef LPB_GJ_TIMING
+    long long tacc[5] = {0, 0, 0, 0, 0}, tlast = clock64();
+#define LPB_GJ_T(ph)                       \
+    do {                                   \
+        const long long _t = clock64();    \
+        tacc[ph] += _t - tlast;            \
+        tlast = _t;                        \
+    } while (0)
+#else
+#define LPB_GJ_T(ph) do { } while (0)
+#endif
     for (int k0 = 0; k0 < n;) {
         const int K = min(kGjK, n - k0);
         // ---- SelectPivotElement for step k0, on the up-to-date matrix in global memory ----
@@ -111,6 +161,7 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
             P[(size_t)i * kGjPS + q] = a[(size_t)i * n + k0 + q];
         }
         __syncthreads();
+        LPB_GJ_T(0);
         // ---- factorise the panel in shared memory ----
         int Kp = K;
         for (int q = 0; q < K; ++q) {
@@ -170,13 +221,23 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
             // scale the pivot row (division per element, :143-145)
             if (tid > q && tid < K) P[(size_t)k * kGjPS + tid] = __ddiv_rn(P[(size_t)k * kGjPS + tid], value);
             __syncthreads();
-            for (int i = tid; i < n; i += kGjThreads) {
-                if (i == k) continue;
-                double *Pi = P + (size_t)i * kGjPS;
-                const double s = -Pi[q];  // scale = -1 * a[i][k]  (:151)
-                for (int t = q + 1; t < K; ++t)
-                    Pi[t] = __dadd_rn(Pi[t], __dmul_rn(s, P[(size_t)k * kGjPS + t]));
-                Pi[q] = s;  // keep the scale for the trailing update
+            if (kPairs) {
+                switch (q) {  // compile-time step index: no predicated-off fp64 work, no selects
+#define LPB_GJ_CASE(Q) case Q: gj_factor_rows<Q, kGjThreads>(P, n, k, tid); break;
+                    LPB_GJ_CASE(0) LPB_GJ_CASE(1) LPB_GJ_CASE(2) LPB_GJ_CASE(3) LPB_GJ_CASE(4) LPB_GJ_CASE(5)
+                    LPB_GJ_CASE(6) LPB_GJ_CASE(7) LPB_GJ_CASE(8) LPB_GJ_CASE(9) LPB_GJ_CASE(10) LPB_GJ_CASE(11)
+                    LPB_GJ_CASE(12) LPB_GJ_CASE(13) LPB_GJ_CASE(14) LPB_GJ_CASE(15)
+#undef LPB_GJ_CASE
+                }
+            } else {
+                for (int i = tid; i < n; i += kGjThreads) {
+                    if (i == k) continue;
+                    double *Pi = P + (size_t)i * kGjPS;
+                    const double s = -Pi[q];  // scale = -1 * a[i][k]  (:151)
+                    for (int t = q + 1; t < K; ++t)
+                        Pi[t] = __dadd_rn(Pi[t], __dmul_rn(s, P[(size_t)k * kGjPS + t]));
+                    Pi[q] = s;  // keep the scale for the trailing update
+                }
             }
             __syncthreads();
         }
@@ -190,6 +251,7 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
         //      order, one read and one write per element, four rows in flight;
         //   3. one thread per column: the pivot rows are eliminated by the later pivots of the
         //      panel (Gauss-JORDAN) and take their final values.
+        LPB_GJ_T(1);
         const int jfirst = k0 + Kp;
         const int C = n + 1 - jfirst;
         for (int j = jfirst + tid; j <= n; j += kGjThreads) {
@@ -205,20 +267,27 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
                     }
                 }
             }
+            // all Kp loads first, all stores last: interleaved, each load would wait for the store before it
+            // (the compiler cannot tell the rows apart) and the chain would pay 16 memory round trips
             double R[kGjK];
+#pragma unroll
+            for (int q = 0; q < kGjK; ++q) R[q] = (q < Kp) ? col[(size_t)(k0 + q) * cs] : 0.0;
 #pragma unroll
             for (int q = 0; q < kGjK; ++q) {
                 if (q < Kp) {
                     const double *Pk = P + (size_t)(k0 + q) * kGjPS;
-                    double v = col[(size_t)(k0 + q) * cs];
+                    double v = R[q];
 #pragma unroll
                     for (int t = 0; t < q; ++t) v = __dadd_rn(v, __dmul_rn(Pk[t], R[t]));
                     R[q] = __ddiv_rn(v, Pk[q]);
-                    col[(size_t)(k0 + q) * cs] = R[q];
                 }
             }
+#pragma unroll
+            for (int q = 0; q < kGjK; ++q)
+                if (q < Kp) col[(size_t)(k0 + q) * cs] = R[q];
         }
         __syncthreads();
+        LPB_GJ_T(2);
         // column pairs: every row of `a` starts 16-byte aligned (n even) and the trailing block starts on an
         // even column; the b column (and everything, when the conditions fail) goes through the one-column loop
         const bool pairs = kPairs && Kp == kGjK && (n & 1) == 0 && (jfirst & 1) == 0;
@@ -230,67 +299,89 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
             for (int item = tid; item < items; item += kGjThreads) {
                 const int blk = item / CP, jp = item - blk * CP;
                 const int i0 = blk * kGjPairBlock, i1 = min(n, i0 + kGjPairBlock);
-                // the block's rows minus the panel's pivot rows [k0, k0 + K): row of the c-th one
-                const int before = min(max(k0 - i0, 0), i1 - i0);
-                const int inside = max(0, min(i1, k0 + kGjK) - max(i0, k0));
-                const int nrows = (i1 - i0) - inside;
                 double2 *col = reinterpret_cast<double2 *>(a + jfirst + 2 * jp);
                 double2 R[kGjK];
 #pragma unroll
                 for (int q = 0; q < kGjK; ++q) R[q] = __ldcg(col + (size_t)(k0 + q) * cs2);
-#define LPB_GJ_ROW(c) (i0 + (c) + ((c) >= before ? inside : 0))
-                // software pipeline: the loads of chunk c+2 are in flight while chunk c is worked on
-                double2 cur[2], nxt[2];
-                int rcur[2], rnxt[2];
+                // the block's rows minus the panel's pivot rows [k0, k0 + K): at most two contiguous runs
+#pragma unroll 1
+                for (int run = 0; run < 2; ++run) {
+                    const int ra = run == 0 ? i0 : max(i0, k0 + kGjK);
+                    const int rb = run == 0 ? min(i1, k0) : i1;
+                    if (ra >= rb) continue;
+                    double2 *g = col + (size_t)ra * cs2;
+                    const double *Pr = P + (size_t)ra * kGjPS;
+                    const int npair = (rb - ra) >> 1;
+                    // software pipeline: the loads of the next two rows are in flight while these two are worked on
+                    double2 cur0, cur1, nxt0, nxt1;
+                    if (npair > 0) {
+                        cur0 = g[0];
+                        cur1 = g[cs2];
+                    }
+#pragma unroll 1
+                    for (int c = 0; c < npair; ++c) {
+                        double2 *gn = g + 2 * cs2;
+                        if (c + 1 < npair) {
+                            nxt0 = gn[0];
+                            nxt1 = gn[cs2];
+                        }
+                        if (c + kGjAhead < npair) {
+                            asm volatile("prefetch.global.L1 [%0];" ::"l"(g + 2 * kGjAhead * cs2));
+                            asm volatile("prefetch.global.L1 [%0];" ::"l"(g + (2 * kGjAhead + 1) * cs2));
+                        }
 #pragma unroll
-                for (int r = 0; r < 2; ++r) {
-                    rcur[r] = LPB_GJ_ROW(min(r, nrows - 1));
-                    if (nrows > 0) cur[r] = col[(size_t)rcur[r] * cs2];
+                        for (int t = 0; t < kGjK; t += 2) {
+                            const double2 s0 = *reinterpret_cast<const double2 *>(Pr + t);
+                            const double2 s1 = *reinterpret_cast<const double2 *>(Pr + kGjPS + t);
+                            cur0.x = __dadd_rn(cur0.x, __dmul_rn(s0.x, R[t].x));
+                            cur0.y = __dadd_rn(cur0.y, __dmul_rn(s0.x, R[t].y));
+                            cur1.x = __dadd_rn(cur1.x, __dmul_rn(s1.x, R[t].x));
+                            cur1.y = __dadd_rn(cur1.y, __dmul_rn(s1.x, R[t].y));
+                            cur0.x = __dadd_rn(cur0.x, __dmul_rn(s0.y, R[t + 1].x));
+                            cur0.y = __dadd_rn(cur0.y, __dmul_rn(s0.y, R[t + 1].y));
+                            cur1.x = __dadd_rn(cur1.x, __dmul_rn(s1.y, R[t + 1].x));
+                            cur1.y = __dadd_rn(cur1.y, __dmul_rn(s1.y, R[t + 1].y));
+                        }
+                        g[0] = cur0;
+                        g[cs2] = cur1;
+                        cur0 = nxt0;
+                        cur1 = nxt1;
+                        g = gn;
+                        Pr += 2 * kGjPS;
+                    }
+                    if ((rb - ra) & 1) {  // odd run: the last row on its own
+                        double2 v = g[0];
+#pragma unroll
+                        for (int t = 0; t < kGjK; ++t) {
+                            v.x = __dadd_rn(v.x, __dmul_rn(Pr[t], R[t].x));
+                            v.y = __dadd_rn(v.y, __dmul_rn(Pr[t], R[t].y));
+                        }
+                        g[0] = v;
+                    }
                 }
-                for (int c = 0; c < nrows; c += 2) {
-                    const bool more = c + 2 < nrows;
-#pragma unroll
-                    for (int r = 0; r < 2; ++r) {
-                        rnxt[r] = LPB_GJ_ROW(min(c + 2 + r, nrows - 1));
-                        if (more) nxt[r] = col[(size_t)rnxt[r] * cs2];
-                    }
-#pragma unroll
-                    for (int r = 0; r < 2; ++r) {
-                        const int cp = c + 2 * kGjAhead + r;
-                        if (cp < nrows) asm volatile("prefetch.global.L1 [%0];" ::"l"(col + (size_t)LPB_GJ_ROW(cp) * cs2));
-                    }
-                    const double *P0 = P + (size_t)rcur[0] * kGjPS, *P1 = P + (size_t)rcur[1] * kGjPS;
-#pragma unroll
-                    for (int t = 0; t < kGjK; t += 2) {
-                        const double2 s0 = *reinterpret_cast<const double2 *>(P0 + t);
-                        const double2 s1 = *reinterpret_cast<const double2 *>(P1 + t);
-                        cur[0].x = __dadd_rn(cur[0].x, __dmul_rn(s0.x, R[t].x));
-                        cur[0].y = __dadd_rn(cur[0].y, __dmul_rn(s0.x, R[t].y));
-                        cur[1].x = __dadd_rn(cur[1].x, __dmul_rn(s1.x, R[t].x));
-                        cur[1].y = __dadd_rn(cur[1].y, __dmul_rn(s1.x, R[t].y));
-                        cur[0].x = __dadd_rn(cur[0].x, __dmul_rn(s0.y, R[t + 1].x));
-                        cur[0].y = __dadd_rn(cur[0].y, __dmul_rn(s0.y, R[t + 1].y));
-                        cur[1].x = __dadd_rn(cur[1].x, __dmul_rn(s1.y, R[t + 1].x));
-                        cur[1].y = __dadd_rn(cur[1].y, __dmul_rn(s1.y, R[t + 1].y));
-                    }
-                    col[(size_t)rcur[0] * cs2] = cur[0];
-                    if (c + 1 < nrows) col[(size_t)rcur[1] * cs2] = cur[1];  // odd tail: the twin of row 0 is dropped
-#pragma unroll
-                    for (int r = 0; r < 2; ++r) {
-                        cur[r] = nxt[r];
-                        rcur[r] = rnxt[r];
-                    }
-                }
-#undef LPB_GJ_ROW
             }
         }
-        {
+        if (kPairs && pairs) {
+            // the b column, one row per thread and round (as one 32-row item per thread it would keep 16
+            // threads busy and the rest of the CTA waiting at the barrier)
+            double Rb[kGjK];
+#pragma unroll
+            for (int q = 0; q < kGjK; ++q) Rb[q] = __ldcg(bx + k0 + q);
+            for (int i = tid; i < n; i += kGjThreads) {
+                if (i >= k0 && i < k0 + kGjK) continue;  // pivot rows are handled by passes 1 and 3
+                const double *Pi = P + (size_t)i * kGjPS;
+                double v = bx[i];
+#pragma unroll
+                for (int t = 0; t < kGjK; ++t) v = __dadd_rn(v, __dmul_rn(Pi[t], Rb[t]));
+                bx[i] = v;
+            }
+        } else {
             // work items = (column, block of kGjBlockRows rows), dealt round-robin: consecutive
             // threads take consecutive columns (coalesced) and every thread gets the same number
             // of items to within one, however narrow the trailing matrix has become
             const int nblk = (n + kGjBlockRows - 1) / kGjBlockRows;
-            const int jskip = (kPairs && pairs) ? (n - jfirst) : 0;  // columns already done as pairs
-            const int C1 = C - jskip;
+            const int jskip = 0;
+            const int C1 = C;
             const int items = C1 * nblk;
             for (int item = tid; item < items; item += kGjThreads) {
                 const int blk = item / C1, jj = item - blk * C1;
@@ -342,6 +433,7 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
             }
         }
         __syncthreads();
+        LPB_GJ_T(3);
         for (int j = jfirst + tid; j <= n; j += kGjThreads) {
             double *col = (j < n) ? (a + j) : bx;
             const size_t cs = (j < n) ? (size_t)n : 1;
@@ -361,8 +453,15 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
             }
         }
         __syncthreads();
+        LPB_GJ_T(4);
         k0 += Kp;
     }
+#ifdef LPB_GJ_TIMING
+    if (tid == 0 && (blockIdx.x == 0 || blockIdx.x == 300))
+        printf("gj timing cta %d: select+load %lld  factor %lld  pass1 %lld  pass2 %lld  pass3 %lld cycles\n", blockIdx.x,
+               tacc[0], tacc[1], tacc[2], tacc[3], tacc[4]);
+#endif
+#undef LPB_GJ_T
 }
 
 }  // namespace lpb
