@@ -156,6 +156,7 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
             __syncthreads();
         }
         // ---- load the n x K panel ----
+        // (batching these loads through registers, 8 x 16 bytes per thread, was measured: 73.3 ms against 70.2 ms)
         for (int idx = tid; idx < n * K; idx += kGjThreads) {
             const int i = idx / K, q = idx - i * K;
             P[(size_t)i * kGjPS + q] = a[(size_t)i * n + k0 + q];
@@ -489,9 +490,10 @@ static int gj_launch(int B, int n, double *wa, double *x, int pivoting, const De
     const bool pp = (pivoting == LPB200_PIVOT_PARTIAL);
     int threads = n <= 64 ? 64 : (n <= 128 ? 128 : (n <= 256 ? 256 : kGjMaxThreads));  // measured: tools/gpu/gj_small_rates.py
     if (const char *g = getenv("LPB_DEBUG_GJ_THREADS")) threads = atoi(g);
-    // n > 256, even: the column-pair trailing update on 256-thread CTAs at 128 registers (two per SM) --
-    // 80.6 ms against 88.8 ms of the one-column 512-thread kernel on 4096 x 512 x 512 (tools/bench_gj.py)
-    bool use_pairs = (n > 256) && (n & 1) == 0;
+    // n > 192, even: the column-pair trailing update on 256-thread CTAs at 128 registers (two per SM) --
+    // 70.2 ms against 88.8 ms of the one-column 512-thread kernel on 4096 x 512 x 512 (tools/bench_gj.py),
+    // 0.381 M against 0.299 M systems/s at n = 256, but 1.60 M against 1.93 M at n = 128 (tools/gpu/gj_small_rates.py)
+    bool use_pairs = (n > 192) && (n & 1) == 0;
     if (const char *g = getenv("LPB_DEBUG_GJ_PAIRS")) use_pairs = atoi(g) != 0;
     if (use_pairs) {
         if (pp) LPB_GJ_LAUNCH(true, 256, true); else LPB_GJ_LAUNCH(false, 256, true);
