@@ -131,6 +131,20 @@ int lpb200_simplex_single(int n, int m, const double *A, const double *b, const 
                           int32_t *npivots, int32_t *pivot_log, int log_cap, double *stats);
 
 /*
+ * Batched Simplex.verify_bounds (simplex.py:663-671; stress.py:21-87 runs it after every "Bounded solution"):
+ * for every LP with status[p] == LPB200_STATUS_BOUNDED (status == NULL: every LP) and every constraint r, in
+ * order: sum = 0; sum += A[r][i] * x[i] for i = 0..m-1 (product and sum rounded separately, left to right);
+ * the reference asserts sum <= b[r] + 1e-3 (it ignores its `tolerance` argument; pass 1e-3 to reproduce it).
+ *   first_bad_row[B]   the first r whose assertion would fire, -1 when the answer passes (or was skipped)
+ * One CTA per LP, A read from HBM once (8*n*m bytes per LP: HBM-bound).
+ */
+int lpb200_verify_bounds_batch_device(int B, int n, int m, const double *A, const double *b, const double *x,
+                                      const int32_t *status, double tolerance, int32_t *first_bad_row,
+                                      void *stream);
+int lpb200_verify_bounds_batch(int B, int n, int m, const double *A, const double *b, const double *x,
+                               const int32_t *status, double tolerance, int32_t *first_bad_row);
+
+/*
  * Host-core helpers of the end-to-end path (no GPU involved).  lpb200_simplex_batch[_ex] called with HOST
  * pointers and an fp64 A runs two lanes over the chunks of a large batch: the copy engine ships chunks as
  * they are while the host cores narrow other chunks to int8 -- only chunks in which every element is an

@@ -35,6 +35,10 @@ SIGNATURES = {
     "lpb200_simplex_batch_ex": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp, ctypes.c_int,
                                                c_vp, c_vp, ctypes.c_double, ctypes.c_int, ctypes.c_int, c_vp,
                                                c_vp, c_vp, c_vp, c_vp, ctypes.c_int]),
+    "lpb200_verify_bounds_batch_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp,
+                                                         c_vp, ctypes.c_double, c_vp, c_vp]),
+    "lpb200_verify_bounds_batch": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp,
+                                                  ctypes.c_double, c_vp]),
     "lpb200_narrow_f64_to_i8": (ctypes.c_int, [c_vp, c_vp, ctypes.c_int64]),
     "lpb200_host_threads": (ctypes.c_int, []),
     "lpb200_simplex_batch_last_lanes": (ctypes.c_int, [c_vp]),

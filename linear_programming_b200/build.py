@@ -15,7 +15,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "liblp_b200.so")
-SOURCES = ["lp_api.cu", "simplex_batched.cu", "simplex_single.cu", "gauss_jordan_batched.cu", "host_narrow.cpp"]
+SOURCES = ["lp_api.cu", "simplex_batched.cu", "simplex_single.cu", "gauss_jordan_batched.cu", "verify_bounds.cu", "host_narrow.cpp"]
 HEADERS = ["lp_common.cuh", "lp_host.h", "host_narrow.h", "simplex_batched_impl.cuh", os.path.join("..", "..", "include", "lp_b200.h")]
 
 NVCC_FLAGS = [

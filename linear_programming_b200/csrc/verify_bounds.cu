@@ -1,0 +1,158 @@
+// verify_bounds.cu -- batched Simplex.verify_bounds (week-2/diet/simplex.py:663-671) for sm_100a.
+//
+// The reference checks an answer row by row: sum = 0; for x in [row[i] * ansx[i] ...]: sum += x;
+// assert(sum <= b[r] + 1e-3) -- products and the running sum rounded separately, left to right, the
+// literal 1e-3 whatever `tolerance` was passed.  stress.py:21-87 runs it after every "Bounded solution";
+// here it is the acceptance test of the GPU-batched fuzzer: one CTA per LP, A read
+// from HBM exactly once (the kernel is HBM-bound: 8*n*m bytes per LP), staged in shared memory with
+// coalesced 16-byte loads, then one thread per constraint walks its row in the reference's order against
+// x (broadcast reads).  Output per LP: the first row whose assertion would fire, or -1.
+// LPs whose status is not LPB200_STATUS_BOUNDED have no x and are skipped (-1).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "lp_common.cuh"
+#include "lp_host.h"
+
+namespace lpb {
+
+constexpr int kVbThreads = 128;
+
+// kStaged: the LP's A fits the CTA's shared memory (row stride padded to an odd number of doubles, so
+// the threads of a warp -- one row each -- hit distinct banks); otherwise rows are read straight from
+// global memory (each thread streams its own row; L1 turns the 8-byte steps into line reuse).
+template <bool kStaged>
+__global__ void __launch_bounds__(kVbThreads)
+verify_bounds_kernel(int B, int n, int m, const double *__restrict__ A, const double *__restrict__ b,
+                     const double *__restrict__ x, const int32_t *__restrict__ status, double tolerance,
+                     int32_t *__restrict__ first_bad)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int tid = threadIdx.x;
+    const int sm_stride = m | 1;
+    double *xs = reinterpret_cast<double *>(smem);                     // [m]
+    double *As = xs + ((m + 1) & ~1);                                   // [n][sm_stride]   (staged only)
+    __shared__ int bad;
+    for (int lp = blockIdx.x; lp < B; lp += gridDim.x) {
+        if (status != nullptr && status[lp] != LPB200_STATUS_BOUNDED) {  // uniform across the CTA
+            if (tid == 0) first_bad[lp] = -1;
+            continue;
+        }
+        const double *Alp = A + (size_t)lp * n * m;
+        if (tid == 0) bad = 0x7fffffff;
+        for (int j = tid; j < m; j += kVbThreads) xs[j] = x[(size_t)lp * m + j];
+        if (kStaged) {
+            const size_t total = (size_t)n * m;
+            if ((total & 1) == 0 && (reinterpret_cast<uintptr_t>(Alp) & 15) == 0) {
+                const double2 *A2 = reinterpret_cast<const double2 *>(Alp);
+                for (size_t q = tid; q < total / 2; q += kVbThreads) {
+                    const double2 v = __ldcs(A2 + q);
+                    const size_t e0 = 2 * q, e1 = 2 * q + 1;
+                    As[(e0 / m) * sm_stride + (e0 % m)] = v.x;
+                    As[(e1 / m) * sm_stride + (e1 % m)] = v.y;
+                }
+            } else {
+                for (size_t e = tid; e < total; e += kVbThreads) As[(e / m) * sm_stride + (e % m)] = __ldcs(Alp + e);
+            }
+        }
+        __syncthreads();
+        int mine = 0x7fffffff;
+        for (int r = tid; r < n; r += kVbThreads) {
+            const double *row = kStaged ? (As + (size_t)r * sm_stride) : (Alp + (size_t)r * m);
+            double sum = 0.0;  // int 0 + float in the reference: the same value
+            for (int i = 0; i < m; ++i) sum = __dadd_rn(sum, __dmul_rn(row[i], xs[i]));
+            if (!(sum <= __dadd_rn(b[(size_t)lp * n + r], tolerance))) mine = min(mine, r);
+        }
+        mine = __reduce_min_sync(0xffffffffu, mine);
+        if ((tid & 31) == 0 && mine != 0x7fffffff) atomicMin(&bad, mine);
+        __syncthreads();
+        if (tid == 0) first_bad[lp] = (bad == 0x7fffffff) ? -1 : bad;
+        __syncthreads();  // xs / As / bad are rewritten by the next LP
+    }
+}
+
+}  // namespace lpb
+
+using namespace lpb;
+
+extern "C" int lpb200_verify_bounds_batch_device(int B, int n, int m, const double *A, const double *b,
+                                                 const double *x, const int32_t *status, double tolerance,
+                                                 int32_t *first_bad_row, void *stream_v)
+{
+    if (B < 0 || n < 1 || m < 1 || !(tolerance >= 0.0)) {
+        set_error("lpb200_verify_bounds_batch: need B >= 0, n >= 1, m >= 1, tolerance >= 0");
+        return LPB200_E_INVALID;
+    }
+    if (B == 0) return 0;
+    if (A == nullptr || b == nullptr || x == nullptr || first_bad_row == nullptr) {
+        set_error("lpb200_verify_bounds_batch: null argument");
+        return LPB200_E_INVALID;
+    }
+    DeviceInfo di;
+    int rc = get_device_info(&di);
+    if (rc) return rc;
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    const size_t xs_bytes = (size_t)((m + 1) & ~1) * 8;
+    const size_t staged_bytes = xs_bytes + (size_t)n * (m | 1) * 8;
+    const bool staged = staged_bytes <= (size_t)di.max_smem_optin;
+    if (!staged && xs_bytes > (size_t)di.max_smem_optin) {
+        set_error("lpb200_verify_bounds_batch: m too large for the shared-memory copy of x");
+        return LPB200_E_TOO_LARGE;
+    }
+    const size_t smem = staged ? staged_bytes : xs_bytes;
+    int per_sm = (int)((size_t)di.max_smem_per_sm / (smem + 1024));
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm > 16) per_sm = 16;
+    long long grid = (long long)di.sm_count * per_sm;
+    if (grid > B) grid = B;
+    if (staged) {
+        LPB_CUDA(cudaFuncSetAttribute(verify_bounds_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        verify_bounds_kernel<true><<<(int)grid, kVbThreads, smem, stream>>>(B, n, m, A, b, x, status, tolerance,
+                                                                            first_bad_row);
+    } else {
+        LPB_CUDA(cudaFuncSetAttribute(verify_bounds_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        verify_bounds_kernel<false><<<(int)grid, kVbThreads, smem, stream>>>(B, n, m, A, b, x, status, tolerance,
+                                                                             first_bad_row);
+    }
+    LPB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int lpb200_verify_bounds_batch(int B, int n, int m, const double *A, const double *b, const double *x,
+                                          const int32_t *status, double tolerance, int32_t *first_bad_row)
+{
+    if (B < 0 || n < 1 || m < 1 || !(tolerance >= 0.0)) {
+        set_error("lpb200_verify_bounds_batch: need B >= 0, n >= 1, m >= 1, tolerance >= 0");
+        return LPB200_E_INVALID;
+    }
+    if (B == 0) return 0;
+    DeviceInfo di;
+    int rc = get_device_info(&di);
+    if (rc) return rc;
+    const size_t nA = (size_t)B * n * m * 8, nb = (size_t)B * n * 8, nx = (size_t)B * m * 8, ns = (size_t)B * 4;
+    char *d = nullptr;
+    const size_t oA = 0, ob = oA + (nA + 255) / 256 * 256, ox = ob + (nb + 255) / 256 * 256,
+                 os = ox + (nx + 255) / 256 * 256, of = os + (ns + 255) / 256 * 256, total = of + ns;
+    cudaError_t e = cudaMalloc((void **)&d, total);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    rc = 0;
+#define LPB_TRY(call)                                                 \
+    do {                                                              \
+        cudaError_t _e = (call);                                      \
+        if (_e != cudaSuccess && rc == 0) rc = cuda_fail(_e, #call);  \
+    } while (0)
+    LPB_TRY(cudaMemcpy(d + oA, A, nA, cudaMemcpyHostToDevice));
+    LPB_TRY(cudaMemcpy(d + ob, b, nb, cudaMemcpyHostToDevice));
+    LPB_TRY(cudaMemcpy(d + ox, x, nx, cudaMemcpyHostToDevice));
+    if (status) LPB_TRY(cudaMemcpy(d + os, status, ns, cudaMemcpyHostToDevice));
+    if (rc == 0)
+        rc = lpb200_verify_bounds_batch_device(B, n, m, reinterpret_cast<const double *>(d + oA),
+                                               reinterpret_cast<const double *>(d + ob),
+                                               reinterpret_cast<const double *>(d + ox),
+                                               status ? reinterpret_cast<const int32_t *>(d + os) : nullptr, tolerance,
+                                               reinterpret_cast<int32_t *>(d + of), nullptr);
+    LPB_TRY(cudaMemcpy(first_bad_row, d + of, ns, cudaMemcpyDeviceToHost));
+#undef LPB_TRY
+    cudaFree(d);
+    return rc;
+}

@@ -199,6 +199,39 @@ def _solve_batch_torch(L, A, b, c, tol, max_pivots, log_cap, mode, rule="referen
     return BatchResult(status, x, obj, npiv, log)
 
 
+def verify_bounds_batch(A, b, x, status=None, tolerance: float = 1e-3):
+    """Batched ``Simplex.verify_bounds`` (simplex.py:663-671): for every LP p with status[p] == 0 (all, when
+    status is None) the first constraint r with  sum_i A[r][i]*x[i] > b[r] + tolerance  (summed left to right like
+    the reference), -1 when the answer passes.  numpy in -> numpy int32[B]; CUDA float64 tensors in -> CUDA
+    int32 tensor (enqueued on the current stream).  The reference hard-codes 1e-3 and ignores its argument."""
+    L = _lib.lib()
+    if _is_torch_cuda(A):
+        import torch
+        B, n, m = A.shape
+        for t, shape in ((A, (B, n, m)), (b, (B, n)), (x, (B, m))):
+            if not (_is_torch_cuda(t) and t.dtype == torch.float64 and t.is_contiguous() and tuple(t.shape) == shape):
+                raise ValueError("CUDA A[B,n,m], b[B,n], x[B,m] must be contiguous float64 tensors")
+        if status is not None and not (_is_torch_cuda(status) and status.dtype == torch.int32 and status.is_contiguous()):
+            raise ValueError("CUDA status must be a contiguous int32 tensor")
+        with torch.cuda.device(A.device):
+            out = torch.empty(B, dtype=torch.int32, device=A.device)
+            _lib.check(L.lpb200_verify_bounds_batch_device(
+                B, n, m, A.data_ptr(), b.data_ptr(), x.data_ptr(), status.data_ptr() if status is not None else None,
+                tolerance, out.data_ptr(), torch.cuda.current_stream(A.device).cuda_stream))
+        return out
+    A = np.ascontiguousarray(A, dtype=np.float64)
+    b = np.ascontiguousarray(b, dtype=np.float64)
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    if A.ndim != 3 or b.shape != A.shape[:2] or x.shape != (A.shape[0], A.shape[2]):
+        raise ValueError("expected A[B,n,m], b[B,n], x[B,m]")
+    B, n, m = A.shape
+    st = np.ascontiguousarray(status, dtype=np.int32) if status is not None else None
+    out = np.full(B, -1, dtype=np.int32)
+    _lib.check(L.lpb200_verify_bounds_batch(B, n, m, _vp(A), _vp(b), _vp(x), _vp(st) if st is not None else None,
+                                            tolerance, _vp(out)))
+    return out
+
+
 def solve(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None = None, mode: str = "auto",
           rule: str = "reference"):
     """Per-problem surface: solve(A, b, c) -> (status, x).  x is a list of m floats when
@@ -269,6 +302,15 @@ class Simplex:
         if st == STATUS_ITERATION_LIMIT:
             raise IterationLimitError("no optimum after %d pivots" % self.npivots)
         raise RuntimeError("unknown status %d" % st)
+
+    def verify_bounds(self, tolerance=1e-3):
+        """simplex.py:663-671: assert A x <= b + 1e-3 row by row on the last answer (the reference reads the
+        module-global ``ansx`` and ignores ``tolerance``; here the answer is ``self.assignment``)."""
+        n, m = self.n, self.m
+        A = np.asarray(self.A, dtype=np.float64).reshape(1, n, m)
+        b = np.asarray(self.b, dtype=np.float64).reshape(1, n)
+        x = np.asarray(self.assignment, dtype=np.float64).reshape(1, m)
+        assert int(verify_bounds_batch(A, b, x, tolerance=1e-3)[0]) < 0
 
     @staticmethod
     def parse(stream=sys.stdin, file=None):

@@ -81,6 +81,8 @@ def lib():
         L.lp_oracle_gauss_jordan_batch_pivot.restype = ctypes.c_int
         L.lp_oracle_gauss_jordan_batch_pivot.argtypes = [ctypes.c_int, ctypes.c_int, _dp, _dp, _dp,
                                                          ctypes.c_int, ctypes.c_int, ctypes.c_int]
+        L.lp_oracle_verify_bounds.restype = ctypes.c_int
+        L.lp_oracle_verify_bounds.argtypes = [ctypes.c_int, ctypes.c_int, _dp, _dp, _dp, ctypes.c_double]
         L.lp_oracle_pyset_replay.restype = ctypes.c_int
         L.lp_oracle_pyset_replay.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int, _ip, _ip, _ip]
         _lib = L
@@ -116,6 +118,14 @@ def simplex(A, b, c, tol: float = 1e-9, max_pivots: int = 1_000_000, log_cap: in
     k = int(npiv[0])
     return {"status": int(st), "x": x, "objective": float(obj[0]), "npivots": k,
             "pivots": [tuple(int(v) for v in r) for r in log[:min(k, log_cap)]]}
+
+
+def verify_bounds(A, b, x, tolerance: float = 1e-3) -> int:
+    """First row on which the reference's Simplex.verify_bounds (simplex.py:663-671) would assert, else -1."""
+    A, b, x = _d(A), _d(b), _d(x)
+    n, m = b.shape[0], x.shape[0]
+    assert A.shape == (n, m)
+    return int(lib().lp_oracle_verify_bounds(n, m, _p(A), _p(b), _p(x), tolerance))
 
 
 def driveouts(reset: bool = True) -> int:

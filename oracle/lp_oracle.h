@@ -79,6 +79,8 @@ int lp_oracle_simplex_batch_rule(int B, int n, int m, const double *A, const dou
                                  double tol, int max_pivots, int rule, int32_t *status, double *x,
                                  double *objective, int32_t *npivots, int threads);
 
+/* Simplex.verify_bounds (simplex.py:663-671): first row r with sum_i A[r][i]*x[i] > b[r] + tolerance, else -1 */
+int lp_oracle_verify_bounds(int n, int m, const double *A, const double *b, const double *x, double tolerance);
 int lp_oracle_driveouts(int reset); /* LP_RULE_BLAND: x_aux drive-out pivots so far (test instrumentation) */
 
 /* Batch driver used for the timed CPU baseline: pthreads over problems

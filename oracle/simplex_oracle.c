@@ -394,6 +394,22 @@ done_noset:
     return status;
 }
 
+/* Simplex.verify_bounds, simplex.py:663-671: sum = 0; sum += row[i] * ansx[i] left to right (product and sum
+ * rounded separately); assert(sum <= b[r] + 1e-3) -- the reference ignores its tolerance argument, the caller
+ * passes 1e-3 to reproduce it.  Returns the first row whose assertion fires, -1 when the answer passes. */
+int lp_oracle_verify_bounds(int n, int m, const double *A, const double *b, const double *x, double tolerance)
+{
+    for (int r = 0; r < n; ++r) {
+        double sum = 0.0;
+        for (int i = 0; i < m; ++i) {
+            const double prod = A[(size_t)r * m + i] * x[i];
+            sum = sum + prod;
+        }
+        if (!(sum <= b[r] + tolerance)) return r;
+    }
+    return -1;
+}
+
 /* ---- batch driver for the timed CPU baseline: pthreads pulling problems off a shared counter ---- */
 typedef struct {
     int B, n, m;

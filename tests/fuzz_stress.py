@@ -9,7 +9,8 @@ Per run: LPs from the stress.py distribution (n, m ~ U{1..nmax}, A ~ U{-100..99}
 b ~ U{-10^6..10^6-1} with 7 % zeros, c ~ U{-100..99}) are grouped by shape, each group is ONE
 batched engine call, and every LP is compared with the checker: status, pivot count, pivot
 sequence, x and objective bit for bit.  Then the reference's own post-conditions:
-  * verify_bounds (simplex.py:663-671): A x <= b + 1e-3 on every "Bounded" answer, batched;
+  * verify_bounds (simplex.py:663-671): A x <= b + 1e-3 on every "Bounded" answer, batched ON THE GPU
+    (lpb200_verify_bounds_batch, itself compared with the checker's restatement on a sample);
     violations are COUNTED, not failed -- the reference's degenerate-skip ratio test returns
     infeasible x on some inputs (SURVEY A.8) and parity means reproducing that;
   * scipy cross-check (stress.py:48-83) on a sample: status agreement and |c.x - c.x_ref| <= 1e-3
@@ -67,9 +68,15 @@ def run(count=100000, seed=0, nmax=7, scipy_sample=200, max_pivots=2000):
         status[idxs] = res.status
         ok = res.status == 0
         bounded += int(ok.sum())
-        if ok.any():  # verify_bounds, batched
-            lhs = np.einsum("bnm,bm->bn", A[ok], res.x[ok])
-            viol += int(((lhs > b[ok] + 1e-3).any(axis=1) | (res.x[ok] < -1e-3).any(axis=1)).sum())
+        if ok.any():  # verify_bounds (simplex.py:663-671), batched on the GPU: first asserting row per LP
+            t1 = time.perf_counter()
+            first_bad = lp.simplex.verify_bounds_batch(A, b, res.x, res.status)
+            t_gpu += time.perf_counter() - t1
+            viol += int((first_bad >= 0).sum())
+            # the kernel against the checker's restatement on a sample of the group
+            for k in np.nonzero(ok)[0][:: max(1, int(ok.sum()) // 16)]:
+                if int(first_bad[k]) != oracle.verify_bounds(A[k], b[k], res.x[k]):
+                    mism.append(int(idxs[k]))
         for k, i in enumerate(idxs):
             xs[i] = res.x[k]
     out = {"count": count, "seed": seed, "nmax": nmax, "shapes": len(groups),
