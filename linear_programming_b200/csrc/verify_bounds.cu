@@ -16,7 +16,8 @@
 
 namespace lpb {
 
-constexpr int kVbThreads = 128;
+constexpr int kVbThreads = 256;
+constexpr int kVbRows = 8;  // rows per warp and tile of the staging loop: 8 x 4 loads in flight per lane
 
 // kStaged: the LP's A fits the CTA's shared memory (row stride padded to an odd number of doubles, so
 // the threads of a warp -- one row each -- hit distinct banks); otherwise rows are read straight from
@@ -42,25 +43,56 @@ verify_bounds_kernel(int B, int n, int m, const double *__restrict__ A, const do
         if (tid == 0) bad = 0x7fffffff;
         for (int j = tid; j < m; j += kVbThreads) xs[j] = x[(size_t)lp * m + j];
         if (kStaged) {
-            const size_t total = (size_t)n * m;
-            if ((total & 1) == 0 && (reinterpret_cast<uintptr_t>(Alp) & 15) == 0) {
-                const double2 *A2 = reinterpret_cast<const double2 *>(Alp);
-                for (size_t q = tid; q < total / 2; q += kVbThreads) {
-                    const double2 v = __ldcs(A2 + q);
-                    const size_t e0 = 2 * q, e1 = 2 * q + 1;
-                    As[(e0 / m) * sm_stride + (e0 % m)] = v.x;
-                    As[(e1 / m) * sm_stride + (e1 % m)] = v.y;
+            // one warp per row, lanes along the row: coalesced 8-byte loads, no index division.  All 32 loads of
+            // an 8-row x 128-column tile are issued before the first shared-memory store (a store right behind
+            // its load would leave each warp with ONE load in flight: 0.8 TB/s instead of the HBM rate)
+            const int warp = tid >> 5, lane = tid & 31;
+            constexpr int kWarps = kVbThreads / 32;
+            for (int r0 = warp * kVbRows; r0 < n; r0 += kWarps * kVbRows) {
+                for (int j0 = 0; j0 < m; j0 += 128) {
+                    double v[kVbRows][4];
+#pragma unroll
+                    for (int u = 0; u < kVbRows; ++u)
+#pragma unroll
+                        for (int w = 0; w < 4; ++w) {
+                            const int r = r0 + u, j = j0 + 32 * w + lane;
+                            if (r < n && j < m) v[u][w] = __ldcs(Alp + (size_t)r * m + j);
+                        }
+#pragma unroll
+                    for (int u = 0; u < kVbRows; ++u)
+#pragma unroll
+                        for (int w = 0; w < 4; ++w) {
+                            const int r = r0 + u, j = j0 + 32 * w + lane;
+                            if (r < n && j < m) As[(size_t)r * sm_stride + j] = v[u][w];
+                        }
                 }
-            } else {
-                for (size_t e = tid; e < total; e += kVbThreads) As[(e / m) * sm_stride + (e % m)] = __ldcs(Alp + e);
             }
         }
         __syncthreads();
+        {
+            // pull the next LP of this CTA towards L2 while the rows are summed (a latency chain of m dependent
+            // additions on n of the CTA's threads): its staging loop then starts from L2 instead of DRAM
+            const int nxt = lp + (int)gridDim.x;
+            if (nxt < B && (status == nullptr || status[nxt] == LPB200_STATUS_BOUNDED)) {
+                const char *pa = reinterpret_cast<const char *>(A + (size_t)nxt * n * m);
+                const size_t bytes = (size_t)n * m * 8;
+                for (size_t o = (size_t)(kVbThreads - 1 - tid) * 128; o < bytes; o += (size_t)kVbThreads * 128)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pa + o));
+            }
+        }
         int mine = 0x7fffffff;
         for (int r = tid; r < n; r += kVbThreads) {
             const double *row = kStaged ? (As + (size_t)r * sm_stride) : (Alp + (size_t)r * m);
             double sum = 0.0;  // int 0 + float in the reference: the same value
-            for (int i = 0; i < m; ++i) sum = __dadd_rn(sum, __dmul_rn(row[i], xs[i]));
+            int i = 0;
+            for (; i + 8 <= m; i += 8) {  // eight products ahead of the (inherently serial) chain of additions
+                double pr[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) pr[k] = __dmul_rn(row[i + k], xs[i + k]);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) sum = __dadd_rn(sum, pr[k]);
+            }
+            for (; i < m; ++i) sum = __dadd_rn(sum, __dmul_rn(row[i], xs[i]));
             if (!(sum <= __dadd_rn(b[(size_t)lp * n + r], tolerance))) mine = min(mine, r);
         }
         mine = __reduce_min_sync(0xffffffffu, mine);
