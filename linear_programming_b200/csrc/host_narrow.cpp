@@ -17,6 +17,7 @@
 #include <sched.h>
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 
 namespace lpb {
 
@@ -100,11 +101,16 @@ HostPool::HostPool()
     }
     if (want > 32) want = 32;
     nthreads_ = want;
+    owner_pid_ = (int)getpid();
     for (int t = 1; t < nthreads_; ++t) workers_.emplace_back([this] { worker(); });  // the caller is thread 0
 }
 
 HostPool::~HostPool()
 {
+    if ((int)getpid() != owner_pid_) {  // forked child: the std::thread objects refer to threads that do not exist here
+        for (auto &w : workers_) w.detach();
+        return;
+    }
     {
         std::lock_guard<std::mutex> lock(mu_);
         stop_ = true;
@@ -144,7 +150,8 @@ void HostPool::parallel_for(int nitems, void (*fn)(void *, int), void *ctx)
 {
     std::lock_guard<std::mutex> serial(call_mu_);  // one parallel_for at a time (callers on several threads queue up)
     if (nitems <= 0) return;
-    if (workers_.empty() || nitems == 1) {
+    // a fork()ed child inherits the pool object but none of its worker threads: run the items inline there
+    if (workers_.empty() || nitems == 1 || (int)getpid() != owner_pid_) {
         for (int i = 0; i < nitems; ++i) fn(ctx, i);
         return;
     }

@@ -32,6 +32,7 @@ private:
     void worker();
     void drain();
     int nthreads_ = 1;
+    int owner_pid_ = 0;
     std::vector<std::thread> workers_;
     std::mutex mu_, call_mu_;
     std::condition_variable cv_start_, cv_done_;

@@ -72,3 +72,28 @@ def test_many_calls_from_two_threads(L):
     t2 = threading.Thread(target=work, args=("bad", bad, 0))
     t1.start(); t2.start(); t1.join(); t2.join()
     assert res == {"good": True, "bad": True}
+
+
+def test_forked_child_runs_without_the_pool_threads(L):
+    """fork() copies the pool object but not its worker threads: the child must neither hang nor crash."""
+    import os
+    src = np.arange(700_000, dtype=np.float64) % 100
+    assert _narrow(L, src)[0] == 1  # the pool exists in the parent
+    pid = os.fork()
+    if pid == 0:
+        try:
+            rc, dst = _narrow(L, src)
+            ok = rc == 1 and np.array_equal(dst.astype(np.float64), src)
+            os._exit(0 if ok else 3)
+        except BaseException:
+            os._exit(4)
+    for _ in range(300):
+        done, st = os.waitpid(pid, os.WNOHANG)
+        if done:
+            break
+        import time
+        time.sleep(0.1)
+    else:
+        os.kill(pid, 9)
+        pytest.fail("forked child hung in the host pool")
+    assert os.WIFEXITED(st) and os.WEXITSTATUS(st) == 0
