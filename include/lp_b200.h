@@ -149,8 +149,10 @@ int lpb200_verify_bounds_batch(int B, int n, int m, const double *A, const doubl
  * pointers and an fp64 A runs two lanes over the chunks of a large batch: the copy engine ships chunks as
  * they are while the host cores narrow other chunks to int8 -- only chunks in which every element is an
  * integer in [-127, 127] (and no -0.0), so that the kernel's exact widening reproduces the caller's bits --
- * and ship 1/8 of the bytes; answers are bit-identical either way (LPB_HOST_NARROW=0 disables the second
- * lane, LPB_HOST_THREADS sets the pool size; default = the cores the process may run on, at most 32).
+ * and ship 1/8 of the bytes; answers are bit-identical either way.  LPB_HOST_THREADS sets the pool size
+ * (default = the cores the process may run on, at most 32); the second lane runs when the pool has at least
+ * 10 threads (with fewer -- many GPU ranks sharing one host -- the cores' reads only take host memory
+ * bandwidth from the copy engines), LPB_HOST_NARROW=0 / 1 forces it off / on.
  *   lpb200_narrow_f64_to_i8     the same exact narrowing for callers that want to hold A as int8 themselves
  *                               (then pass LPB200_DTYPE_I8): 1 = dst is valid, 0 = some element is not
  *                               representable (dst unspecified), < 0 = bad argument

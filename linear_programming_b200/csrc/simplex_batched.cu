@@ -427,8 +427,15 @@ extern "C" int lpb200_simplex_batch_ex(int B, int n, int m, const void *A_v, int
     // second lane: fp64 A, enough chunks to share, more than the calling thread to narrow with
     bool two_lanes = (a_dtype == LPB200_DTYPE_F64) && (B + chunk - 1) / chunk >= 8;
     if (two_lanes) {
+        // LPB_HOST_NARROW: 0 = off, 1 = on, unset = on when this process has at least kMinNarrowThreads pool
+        // threads.  Measured on the 8-GPU box (32 cores shared by 8 ranks, 4 pool threads each): the cores'
+        // reads starve the eight copy engines of host memory bandwidth -- 2.04 M LPs/s with the second lane
+        // against 2.23 M without; with 12 threads per rank (2 GPUs) 1.89 M against 1.33 M, with 16 (1 GPU)
+        // 1.31 M against 0.67 M.
+        constexpr int kMinNarrowThreads = 10;
         const char *e = getenv("LPB_HOST_NARROW");
         if (e && e[0] == '0') two_lanes = false;
+        else if (!(e && e[0] == '1') && HostPool::instance().threads() < kMinNarrowThreads) two_lanes = false;
     }
     const int nsets_used = two_lanes ? kMaxSets : nset;
     struct Set {
