@@ -97,6 +97,12 @@ int lpb200_simplex_batch(int B, int n, int m, const double *A, const double *b, 
  * the largest objective coefficient enters, ties -> lowest id; after more than 8 degenerate pivots
  * in a row (leaving ratio 0) Bland's choice is used until a pivot makes progress, so it cannot
  * cycle.  Typically 5-10x fewer pivots than either other rule.
+ * LPB200_RULE_DEVEX prices by Devex reference-framework weights (Forrest & Goldfarb's approximation of
+ * steepest edge): the column with the largest c*c/w among c > tol enters; a pivot with entering position p,
+ * new pivot row nr[] and wq = w[p] sets w[k] = max(w[k], (nr[k]*nr[k])*wq), w[p] = max((nr[p]*nr[p])*wq, 1);
+ * weights restart at 1 wherever a pivot loop is entered; same Bland fallback.  Element-wise updates, so the
+ * batch kernel, the grid-wide kernel, any number of GPUs and the CPU restatement agree bit for bit.  About a
+ * third fewer pivots than Dantzig on the mixed-sign 100x100 batch.
  */
 #define LPB200_DTYPE_F64 0
 #define LPB200_DTYPE_F32 1
@@ -106,6 +112,7 @@ int lpb200_simplex_batch(int B, int n, int m, const double *A, const double *b, 
 #define LPB200_RULE_REFERENCE 0
 #define LPB200_RULE_BLAND 1
 #define LPB200_RULE_DANTZIG 2
+#define LPB200_RULE_DEVEX 3
 int lpb200_simplex_batch_ex_device(int B, int n, int m, const void *A, int a_dtype, const double *b,
                                    const double *c, double tol, int max_pivots, int rule, int32_t *status,
                                    double *x, double *objective, int32_t *npivots, int32_t *pivot_log,

@@ -142,6 +142,31 @@
 #undef LPB_MIN_BLOCKS
 #undef LPB_RULE
 
+// LPB200_RULE_DEVEX: Devex reference-framework weights (approximate steepest edge), same Bland fallback
+#define LPB_NS devex8
+#define LPB_SWEEP_WARPS 8
+#define LPB_REG_ROWS 0
+#define LPB_MIN_BLOCKS 2
+#define LPB_RULE 3
+#include "simplex_batched_impl.cuh"
+#undef LPB_NS
+#undef LPB_SWEEP_WARPS
+#undef LPB_REG_ROWS
+#undef LPB_MIN_BLOCKS
+#undef LPB_RULE
+
+#define LPB_NS devex_tiny1
+#define LPB_SWEEP_WARPS 1
+#define LPB_REG_ROWS 0
+#define LPB_MIN_BLOCKS 16
+#define LPB_RULE 3
+#include "simplex_batched_impl.cuh"
+#undef LPB_NS
+#undef LPB_SWEEP_WARPS
+#undef LPB_REG_ROWS
+#undef LPB_MIN_BLOCKS
+#undef LPB_RULE
+
 // the corrected rules on diet-size problems (n, m <= 30): the two-warp CTA
 #define LPB_NS bland_tiny1
 #define LPB_SWEEP_WARPS 1
@@ -237,7 +262,8 @@ extern "C" int lpb200_simplex_batch_ex_device(int B, int n, int m, const void *A
         set_error("lpb200_simplex_batch: a_dtype must be one of LPB200_DTYPE_*");
         return LPB200_E_INVALID;
     }
-    if (rule != LPB200_RULE_REFERENCE && rule != LPB200_RULE_BLAND && rule != LPB200_RULE_DANTZIG) {
+    if (rule != LPB200_RULE_REFERENCE && rule != LPB200_RULE_BLAND && rule != LPB200_RULE_DANTZIG &&
+        rule != LPB200_RULE_DEVEX) {
         set_error("lpb200_simplex_batch: rule must be one of LPB200_RULE_*");
         return LPB200_E_INVALID;
     }
@@ -251,6 +277,7 @@ extern "C" int lpb200_simplex_batch_ex_device(int B, int n, int m, const void *A
     if (rule != LPB200_RULE_REFERENCE) {  // corrected modes: the two-warp CTA for diet-size problems, else 8+1 warps
         const char *force = getenv("LPB_BATCH_KERNEL");
         const bool tiny = (n <= 30 && m <= 30 && !(force && force[0] == 's' && force[1] == 'm' && force[2] == 'e'));
+        if (rule == LPB200_RULE_DEVEX) return tiny ? LPB_LAUNCH(devex_tiny1) : LPB_LAUNCH(devex8);
         if (rule == LPB200_RULE_DANTZIG) return tiny ? LPB_LAUNCH(dantzig_tiny1) : LPB_LAUNCH(dantzig8);
         return tiny ? LPB_LAUNCH(bland_tiny1) : LPB_LAUNCH(bland8);
     }

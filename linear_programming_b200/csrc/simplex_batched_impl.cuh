@@ -12,7 +12,8 @@
 namespace lpb {
 namespace LPB_NS {
 
-// LPB_RULE: 0 = the reference's decisions (parity), 1 = Bland, 2 = Dantzig with Bland fallback.
+// LPB_RULE: 0 = the reference's decisions (parity), 1 = Bland, 2 = Dantzig with Bland fallback,
+// 3 = Devex reference-framework weights with the same fallback.
 // Everything that differs from the reference is compiled in only when LPB_CORRECTED.
 #undef LPB_CORRECTED
 #define LPB_CORRECTED (LPB_RULE != 0)
@@ -207,6 +208,67 @@ __device__ __forceinline__ int select_entering_dantzig(const Ctx &c, int ncols, 
         warp_argmin(key, id);
         if ((tid & 31) == 0) {
             c.redkey[2 * (tid >> 5)] = key;  // redkey[] is 16 bytes per warp (RatioPartial)
+            c.redvar[tid >> 5] = id;
+        }
+    }
+    __syncthreads();
+    unsigned long long best = c.redkey[0];
+    int bid = c.redvar[0];
+#pragma unroll
+    for (int w = 1; w < kSweepWarps; ++w) {
+        const unsigned long long k = c.redkey[2 * w];
+        const int v = c.redvar[w];
+        if (k < best || (k == best && v < bid)) {
+            best = k;
+            bid = v;
+        }
+    }
+    __syncthreads();  // redkey/redvar are rewritten by the next ratio test
+    return bid == 0x7fffffff ? -1 : (bid & 0xffff);
+}
+#endif
+
+#if LPB_RULE == 3
+// Devex pricing (Forrest & Goldfarb's approximation of steepest edge): every column position k carries a
+// reference-framework weight w[k] (kept in nr[], which the shared-memory variants do not use inside the pivot
+// loop); the column with the largest (c*c)/w among c > tol enters, ties -> lowest variable id, Bland's choice on
+// a degenerate streak.  upd_row >= 0: the pivot just performed (entering position p_prev, weight wq read before
+// the sweep, new pivot row in physical row upd_row) first updates the weights, element-wise:
+//   w[k] = max(w[k], (nr[k]*nr[k])*wq) for k != p_prev,   w[p_prev] = max((nr[p_prev]*nr[p_prev])*wq, 1).
+// One thread owns a column in this pass, so the update needs no reduction and gives the same bits whatever
+// the thread mapping -- the grid-wide kernel and the CPU restatement compute exactly these expressions.
+__device__ __forceinline__ int select_entering_devex(const Ctx &c, int ncols, bool bland_now, int upd_row, int p_prev,
+                                                     double wq)
+{
+    const int tid = threadIdx.x;
+    if (tid < kSweepThreads) {
+        unsigned long long key = kKeyNone;
+        int id = 0x7fffffff;
+        const double *obj = c.T + (size_t)c.n * c.S + 1;
+        const double *nrow = c.T + (size_t)(upd_row >= 0 ? upd_row : 0) * c.S + 1;
+        for (int k = tid; k < ncols; k += kSweepThreads) {
+            double w = c.nr[k];
+            if (upd_row >= 0) {
+                const double a = nrow[k];
+                const double cand = __dmul_rn(__dmul_rn(a, a), wq);
+                if (k == p_prev) w = cand > 1.0 ? cand : 1.0;
+                else if (cand > w) w = cand;
+                c.nr[k] = w;
+            }
+            const double v = obj[k];
+            if (v > c.tol) {
+                const double d = __ddiv_rn(__dmul_rn(v, v), w);
+                const unsigned long long kk = bland_now ? 0ull : ~(unsigned long long)__double_as_longlong(d);
+                const int ii = (c.colvar[k] << 16) | k;
+                if (kk < key || (kk == key && ii < id)) {
+                    key = kk;
+                    id = ii;
+                }
+            }
+        }
+        warp_argmin(key, id);
+        if ((tid & 31) == 0) {
+            c.redkey[2 * (tid >> 5)] = key;
             c.redvar[tid >> 5] = id;
         }
     }
@@ -790,7 +852,14 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
                                         int log_cap, int forced_p, int forced_lr)
 {
     bool forced = forced_lr >= 0;
-#if LPB_RULE == 2
+#if LPB_RULE == 3
+    int streak = 0;  // degenerate pivots in a row (uniform across the CTA)
+    unsigned long long best_key = 0ull;
+    // a new reference framework wherever a pivot loop is entered (also ahead of a forced pivot)
+    for (int k = threadIdx.x; k < c.S; k += kThreads) c.nr[k] = 1.0;
+    __syncthreads();
+    int p = forced ? forced_p : select_entering_devex(c, ncols, false, -1, 0, 1.0);
+#elif LPB_RULE == 2
     int streak = 0;  // degenerate pivots in a row (uniform across the CTA)
     unsigned long long best_key = 0ull;
     int p = forced ? forced_p : select_entering_dantzig(c, ncols, false);
@@ -808,7 +877,11 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
         long long t0 = clock64(), t1, t2 = 0, t3;
 #endif
         const int e = c.colvar[p];
-#if LPB_RULE == 2
+#if LPB_RULE == 3
+        const double wq = c.nr[p];  // every thread reads it here; the barriers of the ratio test order the later write
+        const int dest_row = c.spare;  // physical row the sweep writes the new pivot row to
+#endif
+#if LPB_RULE >= 2
         int lr = stage_and_ratio(c, p, e, forced, &best_key);
         if (!forced) streak = (best_key == kKeyZeroRatio) ? streak + 1 : 0;
 #else
@@ -830,7 +903,10 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
         sweep(c, ncols, p, src, e, l, log, log_cap, npiv);
 #endif
         ++npiv;
-#if LPB_RULE == 2
+#if LPB_RULE == 3
+        forced = false;
+        p = select_entering_devex(c, ncols, streak > kDegenerateStreak, dest_row, p, wq);
+#elif LPB_RULE == 2
         forced = false;
         p = select_entering_dantzig(c, ncols, streak > kDegenerateStreak);
 #else

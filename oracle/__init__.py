@@ -97,7 +97,7 @@ def _p(a, t=_dp):
     return a.ctypes.data_as(t)
 
 
-RULES = {"reference": 0, "bland": 1, "dantzig": 2}
+RULES = {"reference": 0, "bland": 1, "dantzig": 2, "devex": 3}
 
 
 def simplex(A, b, c, tol: float = 1e-9, max_pivots: int = 1_000_000, log_cap: int | None = None,

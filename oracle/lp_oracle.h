@@ -71,6 +71,7 @@ int lp_oracle_simplex(int n, int m, const double *A, const double *b, const doub
 #define LP_RULE_REFERENCE 0
 #define LP_RULE_BLAND 1
 #define LP_RULE_DANTZIG 2 /* largest coefficient, Bland after LP_DEGENERATE_STREAK degenerate pivots in a row */
+#define LP_RULE_DEVEX 3   /* Devex reference-framework weights (Forrest & Goldfarb), same Bland fallback */
 #define LP_DEGENERATE_STREAK 8
 int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const double *c, double tol,
                            int max_pivots, int rule, double *x, double *objective, int32_t *npivots,

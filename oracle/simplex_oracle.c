@@ -37,6 +37,14 @@
  * with the largest c[j] > tol (ties -> lowest id); once more than LP_DEGENERATE_STREAK pivots in a
  * row (within one run of the loop) had a zero leaving ratio, Bland's entering choice is used until
  * a pivot with a non-zero ratio happens.
+ * rule = LP_RULE_DEVEX is LP_RULE_DANTZIG priced by Devex reference-framework weights (Forrest & Goldfarb's
+ * approximation of steepest edge): every non-basic position k carries a weight w[k]; entering = the column
+ * with the largest (c*c)/w among c > tol (ties -> lowest id); a pivot with entering position p, new pivot row
+ * nr[] (make_pivot_constraint, :325-345) and wq = w[p] sets w[k] = max(w[k], (nr[k]*nr[k])*wq) for k != p and
+ * w[p] = max((nr[p]*nr[p])*wq, 1) (position p now holds the leaving variable).  Element-wise, no reduction:
+ * the same bits whatever kernel, thread mapping or GPU count serves the LP.  Weights are reset to 1 (a new
+ * reference framework) where a pivot loop is entered: before the forced phase-1 pivot, before an x_aux
+ * drive-out pivot, and before phase 2.
  */
 #include <math.h>
 #include <stdlib.h>
@@ -71,7 +79,14 @@ typedef struct {
     int32_t *log;
     int logcap;
     double *newrow;
+    double *wts; /* LP_RULE_DEVEX: reference-framework weight of non-basic position k, [m+1] */
 } lp_t;
+
+static void devex_reset(lp_t *s)
+{
+    if (s->rule == LP_RULE_DEVEX)
+        for (int k = 0; k <= s->m; ++k) s->wts[k] = 1.0;
+}
 
 /* test instrumentation: x_aux drive-out pivots performed since the last reset (not thread-safe) */
 static int g_driveouts = 0;
@@ -109,6 +124,15 @@ static void do_pivot(lp_t *s, int e, int l)
     pinv = snap(pinv, tol);
     for (int k = 0; k < W; ++k) nr[k] = snap(pinv * Tr[k], tol);
     nr[1 + p] = snap(-1.0 * pinv, tol); /* position p now belongs to l: coefficient 1/pivot */
+    if (s->rule == LP_RULE_DEVEX) {
+        const double wq = s->wts[p];
+        for (int k = 0; k < s->ncols; ++k) {
+            const double a = nr[1 + k];
+            const double cand = (a * a) * wq;
+            if (k == p) s->wts[k] = cand > 1.0 ? cand : 1.0;
+            else if (cand > s->wts[k]) s->wts[k] = cand;
+        }
+    }
 
     /* substitute into every other basic row and into the objective (row n) */
     for (int i = 0; i <= n; ++i) {
@@ -152,6 +176,20 @@ static void do_pivot(lp_t *s, int e, int l)
 static int pick_entering(const lp_t *s)
 {
     const double *c = s->T + (size_t)s->n * s->stride;
+    if (s->rule == LP_RULE_DEVEX && s->streak <= LP_DEGENERATE_STREAK) {
+        int best = -1;
+        double bestd = 0.0;
+        for (int k = 0; k < s->ncols; ++k) {
+            const double v = c[1 + k];
+            if (!(v > s->tol)) continue;
+            const double d = (v * v) / s->wts[k];
+            if (best < 0 || d > bestd || (d == bestd && s->colvar[k] < best)) {
+                best = s->colvar[k];
+                bestd = d;
+            }
+        }
+        return best;
+    }
     if (s->rule == LP_RULE_DANTZIG && s->streak <= LP_DEGENERATE_STREAK) {
         int best = -1;
         double bestv = 0.0;
@@ -252,6 +290,7 @@ int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const
     s.colvar = (int *)malloc(sizeof(int) * (size_t)(m + 1));
     s.varpos = (int *)malloc(sizeof(int) * (size_t)nv);
     s.isbasic = (char *)calloc((size_t)nv, 1);
+    s.wts = (double *)calloc((size_t)(m + 2), sizeof(double));
     s.none_col = (int *)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1));
     s.untouched = (char *)calloc((size_t)(n > 0 ? n : 1), 1);
     s.basis0 = (char *)calloc((size_t)nv, 1);
@@ -309,6 +348,7 @@ int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const
     if (phase1) {
         const int aux = n + m;
         if (s.npiv >= s.maxpiv) { status = LP_STATUS_ITERATION_LIMIT; goto done; }
+        devex_reset(&s);
         do_pivot(&s, aux, idx); /* aux_sf.pivot(n + m, min_idx), :524 */
         status = run_loop(&s);  /* :526 */
         if (status != 0) goto done;
@@ -323,6 +363,7 @@ int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const
                 if (fabs(Tr[1 + k]) > tol && (ev < 0 || s.colvar[k] < ev)) ev = s.colvar[k];
             if (ev >= 0) {
                 if (s.npiv >= s.maxpiv) { status = LP_STATUS_ITERATION_LIMIT; goto done; }
+                devex_reset(&s);
                 do_pivot(&s, ev, aux);
                 ++g_driveouts;
                 status = run_loop(&s); /* the objective is -x_aux again: ends at once */
@@ -378,6 +419,7 @@ int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const
         if (!s.isbasic[aux]) pyset_remove(&s.indep, aux); /* :574 -- the same set objects live on into phase 2 */
     }
 
+    devex_reset(&s);
     status = run_loop(&s); /* :599 / :619 */
     if (status == 0) {
         for (int j = 0; j < m; ++j) /* assignment, :474-478, 603 */
@@ -390,6 +432,7 @@ done:
 done_noset:
     *npivots = s.npiv;
     free(s.T); free(s.newrow); free(s.rowvar); free(s.colvar); free(s.varpos);
+    free(s.wts);
     free(s.isbasic); free(s.none_col); free(s.untouched); free(s.basis0);
     return status;
 }

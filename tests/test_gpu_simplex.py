@@ -233,7 +233,7 @@ def test_typed_device_tensor_and_golden_cases(simplex_golden):
     assert checked >= 400
 
 
-@pytest.mark.parametrize("rule", ["bland", "dantzig"])
+@pytest.mark.parametrize("rule", ["bland", "dantzig", "devex"])
 def test_bland_rule_stress_distribution_vs_oracle(oracle_lib, rule):
     """LPB200_RULE_BLAND (corrected mode): status, pivot sequence and x bit-identical to the CPU
     restatement of the same rule (itself checked against HiGHS in tests/test_oracle_bland.py),
@@ -262,7 +262,7 @@ def test_bland_rule_stress_distribution_vs_oracle(oracle_lib, rule):
 
 @pytest.mark.parametrize("dist,n,m,count", [("D1", 100, 100, 64), ("D2", 100, 100, 8), ("D3", 100, 100, 12),
                                             ("D3", 37, 61, 64), ("D3", 64, 20, 64)])
-@pytest.mark.parametrize("rule", ["bland", "dantzig"])
+@pytest.mark.parametrize("rule", ["bland", "dantzig", "devex"])
 def test_bland_rule_random_batches_vs_oracle(oracle_lib, dist, n, m, count, rule):
     import linear_programming_b200 as lp
     from linear_programming_b200 import workloads
@@ -279,7 +279,7 @@ def test_bland_rule_random_batches_vs_oracle(oracle_lib, dist, n, m, count, rule
 
 @pytest.mark.parametrize("n,m,count", [(1, 1, 64), (1, 7, 64), (7, 1, 64), (2, 129, 32), (129, 2, 32), (3, 255, 16),
                                        (160, 160, 4), (100, 250, 4), (250, 100, 4), (20, 1000, 4)])
-@pytest.mark.parametrize("rule", ["reference", "bland", "dantzig"])
+@pytest.mark.parametrize("rule", ["reference", "bland", "dantzig", "devex"])
 def test_edge_shapes_vs_oracle(oracle_lib, n, m, count, rule):
     """Degenerate and extreme shapes of the one-CTA-per-LP kernel: a single row or column, odd widths,
     more than 64 column pairs (lanes loop), and the largest tableaus shared memory holds (one CTA/SM)."""
@@ -436,3 +436,17 @@ def _lp_bytes(n, m, log_cap):
 
 def _ceil_div(a, b):
     return (a + b - 1) // b
+
+
+def test_devex_is_served_by_the_batch_kernel_only_and_needs_fewer_pivots(oracle_lib):
+    import linear_programming_b200 as lp
+    from linear_programming_b200 import workloads
+    A, b, c = workloads.simplex_batch("D2", 64, 100, 100, seed=2)
+    rd = lp.solve_batch(A.astype(np.int8), b, c, rule="dantzig", max_pivots=200000)
+    rx = lp.solve_batch(A.astype(np.int8), b, c, rule="devex", max_pivots=200000)
+    assert np.array_equal(rd.status, rx.status)
+    ok = rd.status == 0
+    assert np.allclose(rd.objective[ok], rx.objective[ok], rtol=1e-6)  # different pivot paths, same optimum
+    assert rx.npivots.sum() * 5 < rd.npivots.sum() * 4  # at least a fifth fewer pivots
+    with pytest.raises(lp.EngineError):
+        lp.solve_batch(A[:1], b[:1], c[:1], rule="devex", mode="single")

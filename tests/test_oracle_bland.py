@@ -30,7 +30,7 @@ def _check(A, b, c, o):
         assert abs(float(c @ x) - o["objective"]) <= 1e-6 * max(1.0, abs(opt))
 
 
-@pytest.mark.parametrize("rule", ["bland", "dantzig"])
+@pytest.mark.parametrize("rule", ["bland", "dantzig", "devex"])
 def test_bland_oracle_matches_highs_on_the_stress_distribution(oracle_lib, rule):
     """stress.py:23-26 distribution with zeros forced into b: every input on which the reference
     crashes (AttributeError / IndexError / TypeError) or cycles gets a proper answer here."""
@@ -44,7 +44,7 @@ def test_bland_oracle_matches_highs_on_the_stress_distribution(oracle_lib, rule)
     assert seen == {0, -1, 1}
 
 
-@pytest.mark.parametrize("rule", ["bland", "dantzig"])
+@pytest.mark.parametrize("rule", ["bland", "dantzig", "devex"])
 @pytest.mark.parametrize("dist,n,m,count", [("D3", 20, 20, 120), ("D2", 30, 40, 40), ("D3", 40, 25, 80)])
 def test_bland_oracle_matches_highs_mid_size(oracle_lib, dist, n, m, count, rule):
     from linear_programming_b200 import workloads
@@ -54,7 +54,7 @@ def test_bland_oracle_matches_highs_mid_size(oracle_lib, dist, n, m, count, rule
         _check(A[p], b[p], c[p], {"status": int(st[p]), "x": x[p], "objective": float(obj[p])})
 
 
-@pytest.mark.parametrize("rule", ["bland", "dantzig"])
+@pytest.mark.parametrize("rule", ["bland", "dantzig", "devex"])
 def test_bland_answers_the_reference_crash_fixtures(oracle_lib, simplex_golden, rule):
     """Every golden case on which the reference raises (status 3/4/5) is a well-posed LP."""
     crashed = [k for k in simplex_golden["cases"] if k["status"] in (3, 4, 5)]

@@ -1,4 +1,4 @@
-"""LPs/s and pivots/s of the three pivoting rules on Config 4 (device-resident inputs, CUDA events)."""
+"""LPs/s and pivots/s of the four pivoting rules on Config 4 (device-resident inputs, CUDA events)."""
 import json
 import os
 import sys
@@ -13,7 +13,7 @@ for dist, B in (("D1", 65536), ("D2", 8192)):
     A, b, c = workloads.simplex_batch(dist, B, 100, 100, seed=2)
     dA = torch.from_numpy(A).to(torch.int8).cuda()
     db, dc = torch.from_numpy(b).cuda(), torch.from_numpy(c).cuda()
-    for rule in ("reference", "bland", "dantzig"):
+    for rule in ("reference", "bland", "dantzig", "devex"):
         lp.solve_batch(dA, db, dc, rule=rule)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
