@@ -225,9 +225,11 @@ int lpb200_simplex_sharded_emulated(int nranks, int n, int m, const double *A, c
                                     const double *c, double tol, int max_pivots, int32_t *status, double *x,
                                     double *objective, int32_t *npivots, int32_t *pivot_log, int log_cap);
 
-/* The sharded calls with a pivoting rule.  Under LPB200_RULE_DANTZIG the entering exchange carries
- * (~bits(c_j), variable id) as two packets per rank and the minimum is lexicographic; the x_aux
- * drive-out of the corrected modes costs one more key exchange after phase 1. */
+/* The sharded calls with a pivoting rule.  Under LPB200_RULE_DANTZIG / LPB200_RULE_DEVEX the entering
+ * exchange carries (~bits(value), variable id) as two packets per rank and the minimum is lexicographic;
+ * Devex weights stay with the rank that owns the column, the weight of the entering column rides along
+ * with the pivot-column broadcast; the x_aux drive-out of the corrected modes costs one more key
+ * exchange after phase 1. */
 int lpb200_simplex_sharded_ex_device(lpb200_comm_t *comm, int n, int m, const double *A_cols, int64_t lda,
                                      const double *b, const double *c, double tol, int max_pivots, int rule,
                                      int32_t *status, double *x, double *objective, int32_t *npivots,

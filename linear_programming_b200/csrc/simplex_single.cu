@@ -35,9 +35,11 @@
 //
 // Pivoting rule (SingleArgs.rule, a run-time argument: the selection phases are a few microseconds
 // of a 1.3 ms pivot, the sweep is rule-independent): LPB200_RULE_REFERENCE = the reference's
-// decisions (parity); LPB200_RULE_BLAND / LPB200_RULE_DANTZIG = the corrected modes of the batch
-// kernel (lowest-id / largest-coefficient entering, zero ratios kept, true minimum of b, x_aux
-// driven out after phase 1, no crash classes), checked bit-exact against oracle/simplex_oracle.c.
+// decisions (parity); LPB200_RULE_BLAND / LPB200_RULE_DANTZIG / LPB200_RULE_DEVEX = the corrected
+// modes of the batch kernel (lowest-id / largest-coefficient / Devex-weighted entering, zero ratios
+// kept, true minimum of b, x_aux driven out after phase 1, no crash classes), checked bit-exact
+// against oracle/simplex_oracle.c.  Devex keeps one weight per owned column (wts[]); the weight of
+// the entering column rides along with the pivot-column broadcast as element n+1.
 //
 // Tensor cores are not used: the update is a rank-1 AXPY at 0.125 flop/byte, HBM-bound.
 #include <cooperative_groups.h>
@@ -87,6 +89,7 @@ struct SingleWS {
     double *fc;                   // [n+1]       pivot column factors, replicated
     double *cstage;               // scratch: factors of the objective rebuild
     double *scal;                 // [4]         nr constant
+    double *wts;                  // [S]         LPB200_RULE_DEVEX: reference-framework weights of the owned columns
     int *rowvar, *nonecol, *untouched, *rowslot;  // [n]      replicated
     int *colvar, *colslot;                        // [m+1]    replicated (global positions)
     int *varpos;                                  // [n+m+1]  replicated
@@ -219,7 +222,11 @@ struct LoopCtl {
     uint32_t parity;  // mbarrier phase bits of the two sweep stages
     unsigned epoch;   // exchange epoch (continues across solves)
     unsigned kx;      // key exchanges so far (parity selects the key buffer)
-    int streak;       // LPB200_RULE_DANTZIG: degenerate pivots in a row in the current loop
+    int streak;       // LPB200_RULE_DANTZIG / DEVEX: degenerate pivots in a row in the current loop
+    // LPB200_RULE_DEVEX: the last pivot (entering position, its weight) still has to update the weights
+    bool upd;
+    int p_prev;
+    double wq;
 };
 
 // Reduce the per-CTA partials written before the last grid.sync().
@@ -258,8 +265,12 @@ __device__ __forceinline__ void write_partial(const SingleWS &w, const LoopCtl &
 // variable id (Bland), 2 = largest coefficient, ties -> lowest id (Dantzig).  The partial is the
 // lexicographic minimum of (key, id): rules 0/1 pack (priority << 32 | position) into the key,
 // rule 2 uses key = ~bits(c_j) (positive doubles order like their bit patterns) and id = variable.
+// Devex (rule 3): key = ~bits((c_j*c_j)/w_j), id = variable; the weights of the owned columns are first brought
+// up to date with the pivot performed last (ctl.upd; one thread of the grid owns a column in this pass):
+// w[k] = max(w[k], (nr[k]*nr[k])*wq), w[p_prev] = max((nr[p_prev]*nr[p_prev])*wq, 1) -- the expressions of
+// select_entering_devex() in the batch kernel and of the CPU restatement.
 __device__ __forceinline__ void phase_entering(BlockRed &br, const SingleWS &w, const LoopCtl &ctl, double tol,
-                                               int pricing)
+                                               int pricing, int rule)
 {
     unsigned long long key = kKeyNone;
     int var = 0x7fffffff, flag = 0;
@@ -268,9 +279,27 @@ __device__ __forceinline__ void phase_entering(BlockRed &br, const SingleWS &w, 
     const int *prio = (pricing == 0) ? w.colslot : w.colvar;
     for (int kl = ctl.bid * kSgThreads + threadIdx.x; kl < lim; kl += ctl.nblk * kSgThreads) {
         const double v = obj[kl];
+        double wgt = 1.0;
+        if (rule == LPB200_RULE_DEVEX) {
+            wgt = w.wts[kl];
+            if (ctl.upd) {
+                const double a = w.nr[kl];
+                const double cand = __dmul_rn(__dmul_rn(a, a), ctl.wq);
+                if (w.c_lo + kl == ctl.p_prev) wgt = cand > 1.0 ? cand : 1.0;
+                else if (cand > wgt) wgt = cand;
+                w.wts[kl] = wgt;
+            }
+        }
         if (v > tol) {
             const int k = w.c_lo + kl;
-            if (pricing == 2) {
+            if (pricing == LPB200_RULE_DEVEX) {
+                const unsigned long long kk = ~(unsigned long long)__double_as_longlong(__ddiv_rn(__dmul_rn(v, v), wgt));
+                const int id = w.colvar[k];
+                if (kk < key || (kk == key && id < var)) {
+                    key = kk;
+                    var = id;
+                }
+            } else if (pricing == 2) {
                 const unsigned long long kk = ~(unsigned long long)__double_as_longlong(v);
                 const int id = w.colvar[k];
                 if (kk < key || (kk == key && id < var)) {
@@ -323,9 +352,10 @@ __device__ __forceinline__ unsigned long long exchange_key(BlockRed &br, const S
 }
 
 // ---- P2: pivot column p -> fc[] on every rank, min-ratio test on it (pick_leaving_idx :394-436) ----
-// corrected (rules 1, 2): zero ratios are kept and the None bookkeeping raises nothing.
+// corrected (rules 1, 2, 3): zero ratios are kept and the None bookkeeping raises nothing.
+// devex: the Devex weight of the entering column travels with the pivot column as element n+1 of fc[].
 __device__ __forceinline__ void phase_ratio(BlockRed &br, const SingleWS &w, LoopCtl &ctl, int p, int e,
-                                            double tol, bool corrected, unsigned long long timeout_ns)
+                                            double tol, bool corrected, bool devex, unsigned long long timeout_ns)
 {
     unsigned long long key = kKeyNone;
     int var = 0x7fffffff, crash = 0;
@@ -339,11 +369,16 @@ __device__ __forceinline__ void phase_ratio(BlockRed &br, const SingleWS &w, Loo
         ep = ++ctl.epoch;
         fcll = w.xbuf + xb_fc(G);
     }
-    for (int i = ctl.bid * kSgThreads + threadIdx.x; i <= n; i += ctl.nblk * kSgThreads) {
+    const int ilast = devex ? n + 1 : n;
+    for (int i = ctl.bid * kSgThreads + threadIdx.x; i <= ilast; i += ctl.nblk * kSgThreads) {
         double f = 0.0;
         if (mine) {
-            f = w.T[(size_t)i * w.S + pl];
-            if (fabs(f) <= tol) f = 0.0;  // substitute() skips a zero coefficient (:203-205)
+            if (i <= n) {
+                f = w.T[(size_t)i * w.S + pl];
+                if (fabs(f) <= tol) f = 0.0;  // substitute() skips a zero coefficient (:203-205)
+            } else {
+                f = w.wts[pl];
+            }
         }
         if (G > 1) {
             if (mine) {  // broadcast: one LL packet per element into every rank's buffer
@@ -528,6 +563,11 @@ __device__ __forceinline__ void phase_sweep(SweepSmem &sm, const SingleWS &w, Lo
 __device__ __forceinline__ void single_pivot(cg::grid_group &grid, SweepSmem &sm, const SingleWS &w,
                                              const SingleArgs &a, LoopCtl &ctl, int p, int r, int e, int l)
 {
+    if (a.rule == LPB200_RULE_DEVEX) {  // fc[n+1] carries the entering column's weight (phase_ratio)
+        ctl.wq = w.fc[w.n + 1];
+        ctl.p_prev = p;
+        ctl.upd = true;
+    }
     phase_pivot_row(w, ctl, p, r, e, a.tol);
     grid.sync();
     if (ctl.bid == ctl.nblk - 1 && threadIdx.x == kSgThreads - 32) {
@@ -552,15 +592,17 @@ __device__ __forceinline__ int single_run_loop(cg::grid_group &grid, BlockRed &b
         unsigned long long key;
         int var, flag;
         // Dantzig prices by coefficient until more than kDegenerateStreak pivots in a row made no progress
-        const int pricing = (a.rule == LPB200_RULE_DANTZIG && ctl.streak > kDegenerateStreak) ? LPB200_RULE_BLAND : a.rule;
-        phase_entering(br, w, ctl, a.tol, pricing);
+        const int pricing = (a.rule >= LPB200_RULE_DANTZIG && ctl.streak > kDegenerateStreak) ? LPB200_RULE_BLAND : a.rule;
+        const bool with_id = pricing >= LPB200_RULE_DANTZIG;  // (value key, variable id) instead of (priority, position)
+        phase_entering(br, w, ctl, a.tol, pricing, a.rule);
+        ctl.upd = false;  // the Devex weights are up to date with the last pivot
         grid.sync();
         reduce_partials(br, w, ctl, 0, key, var, flag);
-        key = exchange_key(br, w, ctl, key, var, pricing == LPB200_RULE_DANTZIG, a.timeout_ns);
+        key = exchange_key(br, w, ctl, key, var, with_id, a.timeout_ns);
         if (key == kKeyNone) return 0;
-        const int p = (pricing == LPB200_RULE_DANTZIG) ? w.varpos[var] : (int)(key & 0xffffffffull);
+        const int p = with_id ? w.varpos[var] : (int)(key & 0xffffffffull);
         const int e = w.colvar[p];
-        phase_ratio(br, w, ctl, p, e, a.tol, corrected, a.timeout_ns);
+        phase_ratio(br, w, ctl, p, e, a.tol, corrected, a.rule == LPB200_RULE_DEVEX, a.timeout_ns);
         grid.sync();
         reduce_partials(br, w, ctl, 1, key, var, flag);
         if (flag) return LPB200_STATUS_REF_TYPE_ERROR;
@@ -624,6 +666,10 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
     const int n = w.n, m = w.m, S = w.S, nv = n + m + 1;
     const double tol = a.tol;
     const bool corrected = (a.rule != LPB200_RULE_REFERENCE);
+    const bool devex = (a.rule == LPB200_RULE_DEVEX);
+    ctl.upd = false;
+    ctl.p_prev = 0;
+    ctl.wq = 1.0;
     ctl.epoch = (w.nranks > 1) ? (unsigned)w.xbuf[kXbEpoch] : 0u;
     ctl.kx = 0u;
     ctl.streak = 0;
@@ -703,6 +749,8 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
             w.colslot[k] = (n + k) & (isize - 1);
         }
         for (int q = gtid; q < (nv + 31) / 32; q += gsize) w.basis0[q] = 0u;
+        if (devex)
+            for (int kl = gtid; kl < S; kl += gsize) w.wts[kl] = 1.0;  // reference framework of the first pivot loop
         // set(range(n, n+ncols)) / set(range(0, n)) (:289-292): every key in its home slot
         for (int s = gtid; s < isize; s += gsize) {
             const int k = n + ((s - n) & (isize - 1));
@@ -726,7 +774,7 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
                 status = LPB200_STATUS_ITERATION_LIMIT;
             } else {
                 // forced pivot: x_aux enters, the most negative row leaves (:524)
-                phase_ratio(br, w, ctl, m, aux, tol, corrected, a.timeout_ns);  // column m -> fc[]; its partial is unused
+                phase_ratio(br, w, ctl, m, aux, tol, corrected, devex, a.timeout_ns);  // column m -> fc[]; its partial is unused
                 grid.sync();
                 single_pivot(grid, sm, w, a, ctl, m, idx0, aux, idx0);
                 status = single_run_loop(grid, br, sm, w, a, ctl);  // :526
@@ -740,6 +788,10 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
                         // x_aux is basic at level 0: pivot it out on the lowest-id column with a non-zero
                         // entry in its row, then let the loop run (the objective is -x_aux again: it ends at once)
                         const int r = ~w.varpos[aux];
+                        if (devex) {  // a new reference framework ahead of the forced pivot (grid.sync inside driveout_key)
+                            for (int kl = gtid; kl < S; kl += gsize) w.wts[kl] = 1.0;
+                            ctl.upd = false;
+                        }
                         const unsigned long long dk = driveout_key(grid, br, w, a, ctl, r);
                         if (dk != kKeyNone) {
                             if (ctl.npiv >= a.max_pivots) {
@@ -747,7 +799,7 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
                             } else {
                                 const int p = (int)(dk & 0xffffffffull);
                                 const int ev = w.colvar[p];
-                                phase_ratio(br, w, ctl, p, ev, tol, corrected, a.timeout_ns);  // column p -> fc[]
+                                phase_ratio(br, w, ctl, p, ev, tol, corrected, devex, a.timeout_ns);  // column p -> fc[]
                                 grid.sync();
                                 single_pivot(grid, sm, w, a, ctl, p, r, ev, aux);
                                 status = single_run_loop(grid, br, sm, w, a, ctl);
@@ -816,6 +868,10 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
                         w.basis0[q] = bits;
                     }
                     for (int i = gtid; i < n; i += gsize) w.untouched[i] = 1;
+                    if (devex) {  // phase 2 starts from a new reference framework
+                        for (int kl = gtid; kl < S; kl += gsize) w.wts[kl] = 1.0;
+                        ctl.upd = false;
+                    }
                     if (gtid == 0 && kaux >= 0) {  // independent.remove(nvars) (:574); the same sets live on
                         PySet s = {w.state[ST_ISIZE], w.state[ST_IFILL], w.state[ST_IUSED]};
                         pyset_remove_slot(w.tab_i, s, w.colslot[kaux]);
@@ -887,6 +943,7 @@ static size_t carve_single(SingleWS *w, int n, int m, int rank, int nranks, unsi
     CARVE(fc, double, n + 2 + kTileRows)
     CARVE(cstage, double, (n > m ? n : m) + 1)
     CARVE(scal, double, 4)
+    CARVE(wts, double, w->S)
     CARVE(rowvar, int, n)
     CARVE(nonecol, int, n)
     CARVE(untouched, int, n)
@@ -915,8 +972,9 @@ static int check_single_args(int n, int m, double tol, int max_pivots, int log_c
         set_error("lpb200_simplex_single: need n >= 1, m >= 1, tol >= 0, max_pivots >= 0");
         return LPB200_E_INVALID;
     }
-    if (rule != LPB200_RULE_REFERENCE && rule != LPB200_RULE_BLAND && rule != LPB200_RULE_DANTZIG) {
-        set_error("lpb200_simplex_single: rule must be LPB200_RULE_REFERENCE, LPB200_RULE_BLAND or LPB200_RULE_DANTZIG");
+    if (rule != LPB200_RULE_REFERENCE && rule != LPB200_RULE_BLAND && rule != LPB200_RULE_DANTZIG &&
+        rule != LPB200_RULE_DEVEX) {
+        set_error("lpb200_simplex_single: rule must be one of LPB200_RULE_*");
         return LPB200_E_INVALID;
     }
     if ((long long)n + m + 1 >= (1ll << 30)) {

@@ -109,8 +109,8 @@ def solve_batch(A, b, c, tol: float = DEFAULT_TOLERANCE, max_pivots: int | None 
     corrected mode (include/lp_b200.h LPB200_RULE_BLAND: Bland's rule, zero ratios kept, x_aux
     driven out, no crash classes) and "dantzig" the same with largest-coefficient pricing (far
     fewer pivots; Bland takes over on degenerate streaks) -- not reference behaviour; both kernels
-    serve these three rules with identical decisions.  "devex" prices by Devex reference-framework weights
-    (approximate steepest edge, about a third fewer pivots than "dantzig"); batch kernel only.
+    serve every rule with identical decisions.  "devex" prices by Devex reference-framework weights
+    (approximate steepest edge, about a third fewer pivots than "dantzig").
     mode: "batch" (one CTA per LP, tableau in shared memory), "single" (grid-wide kernel, one
     LP after the other), "auto" (batch when the tableau fits shared memory).
     """

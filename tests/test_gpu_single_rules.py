@@ -10,7 +10,7 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-RULES = ["bland", "dantzig"]
+RULES = ["bland", "dantzig", "devex"]
 
 
 def _same(res, g, o, cap):

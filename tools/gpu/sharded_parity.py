@@ -37,7 +37,7 @@ def main():
         A, b, c = A[0], b[0], c[0]
         lo, cnt = column_shard(m, world, rank)
         dA = torch.from_numpy(np.ascontiguousarray(A[:, lo:lo + cnt])).to(dev)
-        for rule in ("reference", "bland", "dantzig"):  # the corrected rules: Dantzig's key is two packets per rank
+        for rule in ("reference", "bland", "dantzig", "devex"):  # the corrected rules: Dantzig's key is two packets per rank
             want = oracle.simplex(A, b, c, max_pivots=cap, rule=rule)
             res = None
             for _ in range(2):  # twice on the same communicator: epochs carry over between solves
