@@ -13,7 +13,7 @@ stream, max over ranks, barrier on both sides) is the whole persistent kernel in
 tableau set-up, so the set-up cost is measured separately with max_pivots = 0 and subtracted.
 `pivot_crc` is a checksum of the (entering, leaving) sequence: it must not depend on N.
 
---rule bland|dantzig runs the corrected modes (lpb200_simplex_single_ex_device /
+--rule bland|dantzig|devex runs the corrected modes (lpb200_simplex_single_ex_device /
 lpb200_simplex_sharded_ex_device); with a generous --pivots the LP is solved TO OPTIMALITY and the
 line carries `solve_ms`, the status, the optimum and a size-independent check of the answer computed
 on the GPU outside the timed region: x >= 0, max(Ax - b) <= 1e-6 * max|b| and |c.x - optimum| <= 1e-9 * |optimum|
@@ -42,7 +42,7 @@ def main():
     ap.add_argument("--pivots", type=int, default=200)
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--dist", default="D1")
-    ap.add_argument("--rule", default="reference", choices=["reference", "bland", "dantzig"])
+    ap.add_argument("--rule", default="reference", choices=["reference", "bland", "dantzig", "devex"])
     ap.add_argument("--gpus", type=int, default=None, help="informational; the world size comes from torchrun")
     args = ap.parse_args()
     n, m = args.n, args.m
@@ -52,7 +52,7 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     L = _lib.lib()
-    rule = {"reference": 0, "bland": 1, "dantzig": 2}[args.rule]
+    rule = {"reference": 0, "bland": 1, "dantzig": 2, "devex": 3}[args.rule]
     comm = None
     if world > 1:
         import torch.distributed as dist
