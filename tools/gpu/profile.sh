@@ -1,5 +1,5 @@
 # ncu evidence for one kernel (one GPU; each ncu run only after the same command exited 0 without ncu).
-#   bash tools/gpu/profile.sh batched|single|gj <tag>      e.g.  ... batched r1g
+#   bash tools/gpu/profile.sh batched|single|gj|verify <tag>      e.g.  ... batched r1g
 # Writes gpurun_out/launches_<kernel>_<tag>.csv (per-launch gpu__time_duration) and
 # gpurun_out/prof_<kernel>_<tag>.ncu-rep (--set full, source imported); summarise the report here with
 #   python tools/ncu_summary.py gpurun_out/prof_<kernel>_<tag>.ncu-rep profiles/<tag>_<kernel>_ncu_summary.csv
@@ -9,6 +9,7 @@ case $K in
   batched) CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e"; RE=simplex_batched; SKIP=3;;
   single)  CMD="python tools/bench_single.py --pivots 4 --reps 1"; RE=simplex_single; SKIP=2;;
   gj)      CMD="python tools/bench_gj.py --batch 592 --reps 1 --cpu 0 --check 8"; RE=gauss_jordan; SKIP=1;;
+  verify)  CMD="python tools/gpu/verify_rate.py"; RE=verify_bounds; SKIP=1;;
   *) echo "unknown kernel $K"; exit 2;;
 esac
 $CMD > $O/prof_${K}_plain.log 2>&1 &&
