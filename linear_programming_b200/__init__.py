@@ -6,11 +6,11 @@ include/lp_b200.h); importing this package does not load it, the first solve doe
 raises if the library or a CUDA device is missing -- there is no CPU fallback.
 """
 from .simplex import (BatchResult, IterationLimitError, Simplex, allocate_ads, solve, solve_batch,
-                      solve_diet_problem)
+                      solve_diet_problem, verify_bounds_batch)
 from .gauss_jordan import solve_equation, solve_equation_batch
 from ._lib import EngineError
 from .sharded import ShardedComm, column_shard, problem_shard, solve_sharded_emulated
 
 __all__ = ["Simplex", "solve", "solve_batch", "BatchResult", "allocate_ads", "solve_diet_problem",
            "solve_equation", "solve_equation_batch", "EngineError", "IterationLimitError", "ShardedComm", "column_shard", "problem_shard",
-           "solve_sharded_emulated"]
+           "solve_sharded_emulated", "verify_bounds_batch"]

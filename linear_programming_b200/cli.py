@@ -21,7 +21,8 @@ so `stress.py`-style drivers (week-2/diet/stress.py:30) can pipe a whole run thr
 process instead of one subprocess per LP.
 
 ``--rule=bland`` (LP programs only) answers with the corrected mode instead of the reference's
-behaviour (include/lp_b200.h LPB200_RULE_BLAND): no crash classes, Bland's anti-cycling rule.
+behaviour (include/lp_b200.h LPB200_RULE_BLAND): no crash classes, Bland's anti-cycling rule;
+``--rule=dantzig`` / ``--rule=devex`` the same with largest-coefficient / Devex pricing.
 """
 from __future__ import annotations
 
