@@ -934,6 +934,14 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
 #ifndef LPB_SETUP_ATTR
 #define LPB_SETUP_ATTR __noinline__
 #endif
+// 16-byte loads of A in flight per thread while a problem is read (fp64 path).  The inputs were L2-prefetched
+// one queue round ahead, and the CTA that reads shares its SM's load/store path with the other CTA's sweep:
+// measured on one box (bench.py, D1): depth 1 3.93 M LPs/s, 2 3.80 M, 4 3.81 M, 8 3.73 M, 12 3.61 M -- a burst
+// of loads holds up the neighbour's shared-memory traffic for longer than the latency it hides.
+#ifndef LPB_LOAD_DEPTH
+#define LPB_LOAD_DEPTH 1
+#endif
+constexpr int kLoadDepth = LPB_LOAD_DEPTH;
 __device__ LPB_SETUP_ATTR void load_constraints(double *T, int S, const char *gAraw, int a_dtype, int a_esz,
                                                 int n, int m)
 {
@@ -971,19 +979,19 @@ __device__ LPB_SETUP_ATTR void load_constraints(double *T, int S, const char *gA
             }
         }
     } else if ((m & 1) == 0 && ((reinterpret_cast<uintptr_t>(gA) & 15) == 0)) {
-        // A as a flat stream of 128-bit loads, four in flight per thread; element pairs
+        // A as a flat stream of 128-bit loads, kLoadDepth in flight per thread; element pairs
         // never straddle a row because m is even
         const double2 *g2 = reinterpret_cast<const double2 *>(gA);
         const int total = (n * m) >> 1, hm = m >> 1;
-        for (int base = tid; base < total; base += 4 * kSweepThreads) {
-            double2 v[4];
+        for (int base = tid; base < total; base += kLoadDepth * kSweepThreads) {
+            double2 v[kLoadDepth];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < kLoadDepth; ++u) {
                 const int idx = base + u * kSweepThreads;
                 if (idx < total) v[u] = __ldcs(g2 + idx);
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < kLoadDepth; ++u) {
                 const int idx = base + u * kSweepThreads;
                 if (idx < total) {
                     const int i = idx / hm, j = (idx - i * hm) * 2;
