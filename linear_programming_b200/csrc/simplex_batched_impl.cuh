@@ -942,6 +942,10 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
 #define LPB_LOAD_DEPTH 1
 #endif
 constexpr int kLoadDepth = LPB_LOAD_DEPTH;
+#ifndef LPB_LOAD_DEPTH_TYPED
+#define LPB_LOAD_DEPTH_TYPED 4  // typed (int8 .. float32) reader: not yet A/B-measured, see DESIGN.md section 10
+#endif
+constexpr int kLoadDepthTyped = LPB_LOAD_DEPTH_TYPED;
 __device__ LPB_SETUP_ATTR void load_constraints(double *T, int S, const char *gAraw, int a_dtype, int a_esz,
                                                 int n, int m)
 {
@@ -951,17 +955,17 @@ __device__ LPB_SETUP_ATTR void load_constraints(double *T, int S, const char *gA
     if (a_dtype != LPB200_DTYPE_F64) {
         // typed A: widened to fp64 here, exactly (ints and float32 are subsets of fp64)
         if ((m & 3) == 0 && ((reinterpret_cast<uintptr_t>(gAraw) & (uintptr_t)(4 * a_esz - 1)) == 0)) {
-            // four consecutive elements per load (never straddling a row), four loads in flight
+            // four consecutive elements per load (never straddling a row), kLoadDepthTyped loads in flight
             const int total = (n * m) >> 2, qm = m >> 2;
-            for (int base = tid; base < total; base += 4 * kSweepThreads) {
-                double v[4][4];
+            for (int base = tid; base < total; base += kLoadDepthTyped * kSweepThreads) {
+                double v[kLoadDepthTyped][4];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < kLoadDepthTyped; ++u) {
                     const int idx = base + u * kSweepThreads;
                     if (idx < total) load_typed4(gAraw, a_dtype, idx, v[u]);
                 }
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < kLoadDepthTyped; ++u) {
                     const int idx = base + u * kSweepThreads;
                     if (idx < total) {
                         const int i = idx / qm, j = (idx - i * qm) * 4;
