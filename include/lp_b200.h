@@ -138,6 +138,21 @@ int lpb200_simplex_single(int n, int m, const double *A, const double *b, const 
                           int32_t *npivots, int32_t *pivot_log, int log_cap, double *stats);
 
 /*
+ * Export of the tableau a grid-wide (or column-sharded) solve stopped on, indexed by VARIABLE id (slack i = id i,
+ * x_j = id n + j, x_aux = id n + m), read from the `workspace` of that solve on the current device:
+ *   obj_by_var[n+m+2]    objective-row coefficient (the row pick_entering_idx scans, simplex.py:390-392) of every
+ *                        non-basic variable, 0 for basic ones; the last element is the row's constant (the value
+ *                        `v` of simplex.py:480).  After a sharded solve a rank reports the coefficients of the
+ *                        columns IT owns (0 elsewhere): the sum over ranks of elements [0, n+m+1) is the full row.
+ *   const_by_var[n+m+1]  constant-column entry (the b_i of the ratio test, simplex.py:414) of every basic
+ *                        variable's row, 0 for non-basic ones (replicated on every rank).
+ * Either pointer may be NULL.  With max_pivots = K this is the state after the first K pivots: how an LP of
+ * config-5 size, which no solver reaches the end of within a test, is compared with the CPU oracle.
+ */
+int lpb200_simplex_single_state_device(int n, int m, const void *workspace, double *obj_by_var,
+                                       double *const_by_var, void *stream);
+
+/*
  * Batched Simplex.verify_bounds (simplex.py:663-671; stress.py:21-87 runs it after every "Bounded solution"):
  * for every LP with status[p] == LPB200_STATUS_BOUNDED (status == NULL: every LP) and every constraint r, in
  * order: sum = 0; sum += A[r][i] * x[i] for i = 0..m-1 (product and sum rounded separately, left to right);
@@ -239,6 +254,13 @@ int lpb200_simplex_sharded_emulated_ex(int nranks, int n, int m, const double *A
                                        const double *c, double tol, int max_pivots, int rule, int32_t *status,
                                        double *x, double *objective, int32_t *npivots, int32_t *pivot_log,
                                        int log_cap);
+/* The emulated launch plus, per rank, the tableau export of lpb200_simplex_single_state_device (host memory):
+ * obj_by_var[nranks][n+m+2] (a rank reports the columns it owns; the sum over ranks of the first n+m+1 elements
+ * is the full objective row), const_by_var[nranks][n+m+1] (replicated).  Either may be NULL. */
+int lpb200_simplex_sharded_emulated_state(int nranks, int n, int m, const double *A, const double *b,
+                                          const double *c, double tol, int max_pivots, int rule, int32_t *status,
+                                          double *x, double *objective, int32_t *npivots, int32_t *pivot_log,
+                                          int log_cap, double *obj_by_var, double *const_by_var);
 
 /*
  * Batched Gauss-Jordan: B independent n x n systems a.x = b.

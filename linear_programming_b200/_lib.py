@@ -43,6 +43,7 @@ SIGNATURES = {
     "lpb200_host_threads": (ctypes.c_int, []),
     "lpb200_simplex_batch_last_lanes": (ctypes.c_int, [c_vp]),
     "lpb200_simplex_single_workspace_bytes": (ctypes.c_int64, [ctypes.c_int, ctypes.c_int]),
+    "lpb200_simplex_single_state_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp]),
     "lpb200_simplex_single_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, ctypes.c_double,
                                                     ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.c_int,
                                                     c_vp, ctypes.c_int64, c_vp]),
@@ -74,6 +75,9 @@ SIGNATURES = {
     "lpb200_simplex_sharded_emulated_ex": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp, c_vp,
                                                           c_vp, ctypes.c_double, ctypes.c_int, ctypes.c_int, c_vp,
                                                           c_vp, c_vp, c_vp, c_vp, ctypes.c_int]),
+    "lpb200_simplex_sharded_emulated_state": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp, c_vp,
+                                                             c_vp, ctypes.c_double, ctypes.c_int, ctypes.c_int, c_vp,
+                                                             c_vp, c_vp, c_vp, c_vp, ctypes.c_int, c_vp, c_vp]),
     "lpb200_gauss_jordan_workspace_bytes": (ctypes.c_int64, [ctypes.c_int, ctypes.c_int]),
     "lpb200_gauss_jordan_batch_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp,
                                                         ctypes.c_int64, c_vp]),

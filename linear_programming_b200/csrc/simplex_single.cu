@@ -64,11 +64,13 @@ constexpr int kMaxRanks = 32;
 constexpr int kDegenerateStreak = 8;  // Dantzig: degenerate pivots in a row before Bland takes over (as in the batch kernel)
 constexpr unsigned long long kKeyZeroRatio = 0x8000000000000000ull;  // order_key(+0.0)
 
-enum { ST_ISIZE = 0, ST_IFILL, ST_IUSED, ST_DSIZE, ST_DFILL, ST_DUSED, ST_NLIST, ST_COUNT = 16 };
+enum { ST_ISIZE = 0, ST_IFILL, ST_IUSED, ST_DSIZE, ST_DFILL, ST_DUSED, ST_NLIST, ST_NCOLS, ST_COUNT = 16 };
 
 // Exchange buffer of one rank, in 8-byte words.  Every payload word is an "LL" word:
 // low 32 bits data, high 32 bits the epoch of the exchange that wrote it.
 constexpr int kXbEpoch = 0;  // running epoch, persists across solves on the same communicator
+constexpr int kXbKx = 1;     // key exchanges so far (its parity selects the key buffer): persists too, so that the
+                             // "at most one exchange ahead" invariant of the double buffer holds ACROSS solves
 constexpr int kXbKeys = 8;   // [2][nranks] x (key packet, id packet) of 2 words each (double-buffered by exchange parity)
 __host__ __device__ inline int xb_fc(int nranks) { return kXbKeys + 8 * nranks; }  // [(n+2)] packets
 static inline size_t xbuf_bytes_for(int n, int nranks)
@@ -671,7 +673,7 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
     ctl.p_prev = 0;
     ctl.wq = 1.0;
     ctl.epoch = (w.nranks > 1) ? (unsigned)w.xbuf[kXbEpoch] : 0u;
-    ctl.kx = 0u;
+    ctl.kx = (w.nranks > 1) ? (unsigned)w.xbuf[kXbKx] : 0u;
     ctl.streak = 0;
 
     // ---- min_constant, idx = min_index(b) (:591): zeros count as +inf, first minimum wins ----
@@ -899,7 +901,33 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
         w.status[0] = status;
         w.npivots[0] = ctl.npiv;
         w.objective[0] = (status == 0) ? w.bcol[n] : 0.0;
-        if (w.nranks > 1) w.xbuf[kXbEpoch] = ctl.epoch;
+        if (w.nranks > 1) {
+            w.xbuf[kXbEpoch] = ctl.epoch;
+            w.xbuf[kXbKx] = ctl.kx;
+        }
+        w.state[ST_NCOLS] = (status == LPB200_STATUS_REF_ATTRIBUTE_ERROR) ? 0 : ctl.ncols;  // 0: no tableau was built
+    }
+}
+
+// ---- tableau export by variable id (lpb200_simplex_single_state_device) ----
+__global__ void simplex_single_state_kernel(const SingleWS *__restrict__ hdr, double *__restrict__ obj_by_var,
+                                            double *__restrict__ const_by_var)
+{
+    const SingleWS &w = *hdr;
+    const int n = w.n, nv = w.n + w.m + 1;
+    const bool built = w.state[ST_NCOLS] != 0;
+    const double *obj = w.T + (size_t)n * w.S;
+    for (int v = blockIdx.x * blockDim.x + threadIdx.x; v <= nv; v += gridDim.x * blockDim.x) {
+        double o = 0.0, cst = 0.0;
+        if (v == nv) {
+            o = built ? w.bcol[n] : 0.0;
+        } else if (built) {
+            const int pos = w.varpos[v];
+            if (pos < 0) cst = w.bcol[~pos];
+            else if (pos >= w.c_lo && pos < w.c_lo + w.wloc) o = obj[pos - w.c_lo];
+        }
+        if (obj_by_var) obj_by_var[v] = o;
+        if (const_by_var && v < nv) const_by_var[v] = cst;
     }
 }
 
@@ -1036,6 +1064,24 @@ extern "C" int64_t lpb200_simplex_single_workspace_bytes(int n, int m)
     if (n < 1 || m < 1) return 0;
     SingleWS w;
     return (int64_t)(kWsHeader + carve_single(&w, n, m, 0, 1, nullptr));
+}
+
+extern "C" int lpb200_simplex_single_state_device(int n, int m, const void *workspace, double *obj_by_var,
+                                                  double *const_by_var, void *stream_v)
+{
+    if (n < 1 || m < 1 || workspace == nullptr) {
+        set_error("lpb200_simplex_single_state_device: need n >= 1, m >= 1 and the workspace of a finished solve");
+        return LPB200_E_INVALID;
+    }
+    DeviceInfo di;
+    int rc = get_device_info(&di);
+    if (rc) return rc;
+    const int nv = n + m + 1;
+    const int blocks = (nv + 1 + 255) / 256 < 1024 ? (nv + 1 + 255) / 256 : 1024;
+    simplex_single_state_kernel<<<blocks, 256, 0, (cudaStream_t)stream_v>>>(static_cast<const SingleWS *>(workspace),
+                                                                             obj_by_var, const_by_var);
+    LPB_CUDA(cudaGetLastError());
+    return 0;
 }
 
 extern "C" int lpb200_simplex_single_device(int n, int m, const double *A, const double *b, const double *c,
@@ -1347,6 +1393,18 @@ extern "C" int lpb200_simplex_sharded_emulated_ex(int nranks, int n, int m, cons
                                                   int32_t *status, double *x, double *objective,
                                                   int32_t *npivots, int32_t *pivot_log, int log_cap)
 {
+    return lpb200_simplex_sharded_emulated_state(nranks, n, m, A, b, c, tol, max_pivots, rule, status, x, objective,
+                                                 npivots, pivot_log, log_cap, nullptr, nullptr);
+}
+
+// The emulated launch plus the tableau export of lpb200_simplex_single_state_device, per rank (host memory):
+// obj_by_var[nranks][n+m+2] (a rank reports the columns it owns), const_by_var[nranks][n+m+1] (replicated).
+extern "C" int lpb200_simplex_sharded_emulated_state(int nranks, int n, int m, const double *A, const double *b,
+                                                     const double *c, double tol, int max_pivots, int rule,
+                                                     int32_t *status, double *x, double *objective,
+                                                     int32_t *npivots, int32_t *pivot_log, int log_cap,
+                                                     double *obj_by_var, double *const_by_var)
+{
     int rc = check_single_args(n, m, tol, max_pivots, log_cap, rule);
     if (rc) return rc;
     if (nranks < 1 || nranks > kMaxRanks) {
@@ -1418,6 +1476,20 @@ extern "C" int lpb200_simplex_sharded_emulated_ex(int nranks, int n, int m, cons
         LPB_TRY(cudaMemcpy(status + g, w.status, 4, cudaMemcpyDeviceToHost));
         LPB_TRY(cudaMemcpy(npivots + g, w.npivots, 4, cudaMemcpyDeviceToHost));
         if (nlog) LPB_TRY(cudaMemcpy(pivot_log + (size_t)g * log_cap * 2, w.pivot_log, nlog, cudaMemcpyDeviceToHost));
+    }
+    if (rc == 0 && (obj_by_var || const_by_var)) {
+        const size_t nv = (size_t)n + m + 1;
+        double *dov = nullptr, *dcv = nullptr;
+        LPB_TRY(cudaMalloc((void **)&dov, (nv + 1) * 8));
+        LPB_TRY(cudaMalloc((void **)&dcv, nv * 8));
+        for (int g = 0; g < G && rc == 0; ++g) {
+            rc = lpb200_simplex_single_state_device(n, m, d_ranks + g, dov, dcv, nullptr);
+            if (rc) break;
+            if (obj_by_var) LPB_TRY(cudaMemcpy(obj_by_var + (size_t)g * (nv + 1), dov, (nv + 1) * 8, cudaMemcpyDeviceToHost));
+            if (const_by_var) LPB_TRY(cudaMemcpy(const_by_var + (size_t)g * nv, dcv, nv * 8, cudaMemcpyDeviceToHost));
+        }
+        cudaFree(dov);
+        cudaFree(dcv);
     }
 #undef LPB_TRY
     cudaFree(ws); cudaFree(outs); cudaFree(xbufs); cudaFree(dA); cudaFree(db); cudaFree(dc);

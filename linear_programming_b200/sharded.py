@@ -112,10 +112,13 @@ class ShardedComm:
 
 
 def solve_sharded_emulated(A, b, c, nranks: int, tol: float = DEFAULT_TOLERANCE, max_pivots=None,
-                           log_cap: int = 0, rule: str = "reference"):
+                           log_cap: int = 0, rule: str = "reference", state: bool = False):
     """The nranks-way column-sharded protocol with every rank emulated as a CTA group of one
     cooperative launch on the current GPU.  Returns one BatchResult whose leading axis is the
-    RANK (all ranks must agree); used by the parity tests and on boxes with fewer GPUs."""
+    RANK (all ranks must agree); used by the parity tests and on boxes with fewer GPUs.
+    state=True also exports the tableau the solve stopped on (lpb200_simplex_sharded_emulated_state):
+    ``res.obj_by_var[rank, n+m+2]`` (each rank reports the columns it owns) and
+    ``res.const_by_var[rank, n+m+1]`` (replicated)."""
     L = _lib.lib()
     A = np.ascontiguousarray(A, dtype=np.float64)
     b = np.ascontiguousarray(b, dtype=np.float64).reshape(-1)
@@ -134,6 +137,17 @@ def solve_sharded_emulated(A, b, c, nranks: int, tol: float = DEFAULT_TOLERANCE,
 
     def vp(a):
         return ctypes.c_void_p(a.ctypes.data)
+    if state:
+        nv = n + m + 1
+        ov = np.zeros((G, nv + 1), dtype=np.float64)
+        cv = np.zeros((G, nv), dtype=np.float64)
+        _lib.check(L.lpb200_simplex_sharded_emulated_state(G, n, m, vp(A), vp(b), vp(c), tol, max_pivots,
+                                                           _rule_code(rule), vp(status), vp(x), vp(obj), vp(npiv),
+                                                           vp(log) if log is not None else None, log_cap, vp(ov),
+                                                           vp(cv)))
+        res = BatchResult(status, x, obj, npiv, log)
+        res.obj_by_var, res.const_by_var = ov, cv
+        return res
     _lib.check(L.lpb200_simplex_sharded_emulated_ex(G, n, m, vp(A), vp(b), vp(c), tol, max_pivots, _rule_code(rule),
                                                     vp(status), vp(x), vp(obj), vp(npiv),
                                                     vp(log) if log is not None else None, log_cap))

@@ -67,6 +67,10 @@ def lib():
         L.lp_oracle_simplex_rule.restype = ctypes.c_int
         L.lp_oracle_simplex_rule.argtypes = [ctypes.c_int, ctypes.c_int, _dp, _dp, _dp, ctypes.c_double,
                                              ctypes.c_int, ctypes.c_int, _dp, _dp, _ip, _ip, ctypes.c_int]
+        L.lp_oracle_simplex_state.restype = ctypes.c_int
+        L.lp_oracle_simplex_state.argtypes = [ctypes.c_int, ctypes.c_int, _dp, _dp, _dp, ctypes.c_double,
+                                              ctypes.c_int, ctypes.c_int, ctypes.c_int, _dp, _dp, _ip, _ip,
+                                              ctypes.c_int, _dp, _dp]
         L.lp_oracle_simplex_batch_rule.restype = ctypes.c_int
         L.lp_oracle_simplex_batch_rule.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, _dp, _dp, _dp,
                                                    ctypes.c_double, ctypes.c_int, ctypes.c_int, _ip, _dp, _dp,
@@ -118,6 +122,32 @@ def simplex(A, b, c, tol: float = 1e-9, max_pivots: int = 1_000_000, log_cap: in
     k = int(npiv[0])
     return {"status": int(st), "x": x, "objective": float(obj[0]), "npivots": k,
             "pivots": [tuple(int(v) for v in r) for r in log[:min(k, log_cap)]]}
+
+
+def simplex_state(A, b, c, tol: float = 1e-9, max_pivots: int = 1_000_000, log_cap: int | None = None,
+                  rule: str = "reference", threads: int = 0):
+    """One LP with the rows of every pivot swept on `threads` host threads (0 = all cores; the bits do not
+    depend on the count) and the tableau it stopped on exported by variable id.  Returns the dict of
+    simplex() plus obj_by_var[n+m+1], obj_const and const_by_var[n+m+1] (see simplex_oracle.c).  With
+    max_pivots = K: the state after the first K pivots -- how a config-5-size LP is checked."""
+    A, b, c = _d(A), _d(b), _d(c)
+    n, m = b.shape[0], c.shape[0]
+    assert A.shape == (n, m), (A.shape, n, m)
+    if log_cap is None:
+        log_cap = min(max_pivots, 1 << 16)
+    nv = n + m + 1
+    x = np.zeros(m)
+    obj = np.zeros(1)
+    npiv = np.zeros(1, dtype=np.int32)
+    log = np.zeros((max(log_cap, 1), 2), dtype=np.int32)
+    ov = np.zeros(nv + 1)
+    cv = np.zeros(nv)
+    st = lib().lp_oracle_simplex_state(n, m, _p(A), _p(b), _p(c), tol, max_pivots, RULES[rule], threads, _p(x),
+                                       _p(obj), _p(npiv, _ip), _p(log, _ip), log_cap, _p(ov), _p(cv))
+    k = int(npiv[0])
+    return {"status": int(st), "x": x, "objective": float(obj[0]), "npivots": k,
+            "pivots": [tuple(int(v) for v in r) for r in log[:min(k, log_cap)]],
+            "obj_by_var": ov[:nv], "obj_const": float(ov[nv]), "const_by_var": cv}
 
 
 def verify_bounds(A, b, x, tolerance: float = 1e-3) -> int:

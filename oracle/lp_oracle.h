@@ -76,6 +76,12 @@ int lp_oracle_simplex(int n, int m, const double *A, const double *b, const doub
 int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const double *c, double tol,
                            int max_pivots, int rule, double *x, double *objective, int32_t *npivots,
                            int32_t *pivot_log, int log_cap);
+/* The same with the rows of each pivot swept on `threads` host threads (bit-identical for any count) and an
+ * export of the final tableau by variable id: obj_by_var[n+m+2], const_by_var[n+m+1] (see simplex_oracle.c). */
+int lp_oracle_simplex_state(int n, int m, const double *A, const double *b, const double *c, double tol,
+                            int max_pivots, int rule, int threads, double *x, double *objective,
+                            int32_t *npivots, int32_t *pivot_log, int log_cap, double *obj_by_var,
+                            double *const_by_var);
 int lp_oracle_simplex_batch_rule(int B, int n, int m, const double *A, const double *b, const double *c,
                                  double tol, int max_pivots, int rule, int32_t *status, double *x,
                                  double *objective, int32_t *npivots, int threads);

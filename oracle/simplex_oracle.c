@@ -80,6 +80,7 @@ typedef struct {
     int logcap;
     double *newrow;
     double *wts; /* LP_RULE_DEVEX: reference-framework weight of non-basic position k, [m+1] */
+    int threads; /* 1 = scalar; otherwise the rows of one pivot are swept by this many host threads (0 = all cores) */
 } lp_t;
 
 static void devex_reset(lp_t *s)
@@ -108,6 +109,47 @@ static void log_pivot(lp_t *s, int e, int l)
     s->npiv++;
 }
 
+/* Constraint.substitute / sexp (simplex.py:185-214) applied to rows [lo, hi) of the tableau for the pivot
+ * (entering position p, leaving row r, entering id e); newrow = the scaled pivot row. */
+static void sweep_rows(lp_t *s, int p, int r, int e, int W, int lo, int hi)
+{
+    const int n = s->n, S = s->stride;
+    const double tol = s->tol;
+    const double *nr = s->newrow;
+    for (int i = lo; i < hi; ++i) {
+        if (i == r) continue;
+        double *Ti = s->T + (size_t)i * S;
+        const double f = Ti[1 + p];
+        if (fabs(f) <= tol) { /* "not coeff or iszero(coeff)": row returned unchanged, :203-205 */
+            Ti[1 + p] = 0.0;  /* A[i][l] stays None */
+            continue;
+        }
+        for (int k = 0; k < W; ++k) {
+            const double a = (k == 1 + p) ? 0.0 : Ti[k];
+            const double prod = f * nr[k]; /* rounded multiply ... */
+            Ti[k] = snap(a + prod, tol);   /* ... then rounded add, then snap (sexp, :185-194) */
+        }
+        if (i < n) {
+            s->none_col[i] = e;
+            s->untouched[i] = 0;
+        }
+    }
+}
+
+#define SWEEP_ROWS 32 /* rows per work item of the threaded sweep */
+typedef struct {
+    lp_t *s;
+    int p, r, e, W;
+} sweep_job_t;
+
+static void sweep_job(void *arg, int item)
+{
+    sweep_job_t *j = (sweep_job_t *)arg;
+    const int lo = item * SWEEP_ROWS;
+    const int hi = lo + SWEEP_ROWS < j->s->n + 1 ? lo + SWEEP_ROWS : j->s->n + 1;
+    sweep_rows(j->s, j->p, j->r, j->e, j->W, lo, hi);
+}
+
 /* SlackForm.pivot(entering e, leaving l), simplex.py:348-385 */
 static void do_pivot(lp_t *s, int e, int l)
 {
@@ -134,24 +176,14 @@ static void do_pivot(lp_t *s, int e, int l)
         }
     }
 
-    /* substitute into every other basic row and into the objective (row n) */
-    for (int i = 0; i <= n; ++i) {
-        if (i == r) continue;
-        double *Ti = s->T + (size_t)i * S;
-        const double f = Ti[1 + p];
-        if (fabs(f) <= tol) { /* "not coeff or iszero(coeff)": row returned unchanged, :203-205 */
-            Ti[1 + p] = 0.0;  /* A[i][l] stays None */
-            continue;
-        }
-        for (int k = 0; k < W; ++k) {
-            const double a = (k == 1 + p) ? 0.0 : Ti[k];
-            const double prod = f * nr[k]; /* rounded multiply ... */
-            Ti[k] = snap(a + prod, tol);   /* ... then rounded add, then snap (sexp, :185-194) */
-        }
-        if (i < n) {
-            s->none_col[i] = e;
-            s->untouched[i] = 0;
-        }
+    /* substitute into every other basic row and into the objective (row n).  Rows are independent of each
+     * other (each reads only itself and nr[]), so sweeping them on several host threads gives the same
+     * bits as the scalar loop whatever the thread count (tests/test_oracle_big.py asserts it). */
+    if (s->threads != 1 && (size_t)(n + 1) * (size_t)W >= ((size_t)1 << 16)) {
+        sweep_job_t job = {s, p, r, e, W};
+        lp_oracle_parallel_for((n + 1 + SWEEP_ROWS - 1) / SWEEP_ROWS, s->threads, sweep_job, &job);
+    } else {
+        sweep_rows(s, p, r, e, W, 0, n + 1);
     }
     memcpy(Tr, nr, sizeof(double) * (size_t)W); /* store(entering_idx, row), :352 */
     s->none_col[r] = e;
@@ -272,8 +304,27 @@ int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const
                            int max_pivots, int rule, double *x, double *objective, int32_t *npivots,
                            int32_t *pivot_log, int log_cap)
 {
+    return lp_oracle_simplex_state(n, m, A, b, c, tol, max_pivots, rule, 1, x, objective, npivots, pivot_log,
+                                   log_cap, NULL, NULL);
+}
+
+/* The same solve with (a) the rows of every pivot swept by `threads` host threads (1 = scalar, 0 = all
+ * cores; bit-identical for any count, rows are independent) so that a config-5-size tableau
+ * (16384 x 32768, 8.6 GB moved per pivot) is checkable in seconds per pivot, and (b) an export of the
+ * tableau the solve stopped on, indexed by VARIABLE id so that it does not depend on how an engine lays
+ * its columns out (both nullable, nv = n + m + 1):
+ *   obj_by_var[v]    objective-row coefficient of v if v is non-basic, else 0;  obj_by_var[nv] = the
+ *                    objective row's constant (the value v of simplex.py:480)
+ *   const_by_var[v]  constant-column entry of v's row if v is basic, else 0
+ * With max_pivots = K this is the state after the first K pivots (status LP_STATUS_ITERATION_LIMIT). */
+int lp_oracle_simplex_state(int n, int m, const double *A, const double *b, const double *c, double tol,
+                            int max_pivots, int rule, int threads, double *x, double *objective,
+                            int32_t *npivots, int32_t *pivot_log, int log_cap, double *obj_by_var,
+                            double *const_by_var)
+{
     lp_t s;
     memset(&s, 0, sizeof(s));
+    s.threads = threads;
     const int nv = n + m + 1;
     int status = LP_STATUS_BOUNDED;
     s.n = n;
@@ -427,9 +478,23 @@ int lp_oracle_simplex_rule(int n, int m, const double *A, const double *b, const
         *objective = s.T[(size_t)n * s.stride]; /* opt_value = v, :480 */
     }
 done:
+    if (obj_by_var) {
+        const double *obj = s.T + (size_t)n * s.stride;
+        for (int v = 0; v <= nv; ++v) obj_by_var[v] = 0.0;
+        for (int k = 0; k < s.ncols; ++k) obj_by_var[s.colvar[k]] = obj[1 + k];
+        obj_by_var[nv] = obj[0];
+    }
+    if (const_by_var) {
+        for (int v = 0; v < nv; ++v) const_by_var[v] = 0.0;
+        for (int i = 0; i < n; ++i) const_by_var[s.rowvar[i]] = s.T[(size_t)i * s.stride];
+    }
     pyset_free(&s.dep);
     pyset_free(&s.indep);
+    goto release;
 done_noset:
+    if (obj_by_var) for (int v = 0; v <= nv; ++v) obj_by_var[v] = 0.0;
+    if (const_by_var) for (int v = 0; v < nv; ++v) const_by_var[v] = 0.0;
+release:
     *npivots = s.npiv;
     free(s.T); free(s.newrow); free(s.rowvar); free(s.colvar); free(s.varpos);
     free(s.wts);

@@ -82,9 +82,13 @@ def test_two_processes_two_gpus_vs_oracle():
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs >= 2 GPUs")
+    import socket
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with socket.socket() as sk:  # a free rendezvous port instead of a fixed one
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
-           "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.join(root, "tools", "gpu", "sharded_parity.py")]
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(root, "tools", "gpu", "sharded_parity.py")]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert '"all_ranks_match_oracle": true' in out.stdout
