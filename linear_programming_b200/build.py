@@ -18,9 +18,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJDIR = os.path.join(CSRC, "_obj")
 LIB_PATH = os.path.join(HERE, "liblp_b200.so")
-SOURCES = ["lp_api.cu", "simplex_batched.cu", "simplex_batched_rules.cu", "simplex_single.cu",
+SOURCES = ["lp_api.cu", "simplex_batched.cu", "simplex_batched_variants.cu", "simplex_single.cu",
            "gauss_jordan_batched.cu", "verify_bounds.cu", "host_narrow.cpp"]
-HEADERS = ["lp_common.cuh", "lp_host.h", "host_narrow.h", "simplex_batched_impl.cuh", "simplex_batched_host.cuh",
+HEADERS = ["lp_common.cuh", "lp_host.h", "host_narrow.h", "simplex_batched_impl.cuh", "simplex_batched_variants.h",
            os.path.join("..", "..", "include", "lp_b200.h")]
 
 NVCC_FLAGS = [

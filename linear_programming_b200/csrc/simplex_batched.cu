@@ -43,6 +43,7 @@
 #include "lp_common.cuh"
 #include "lp_host.h"
 #include "host_narrow.h"
+#include "simplex_batched_variants.h"
 
 
 // ---- kernel variants (same source, different parameters) ----
@@ -54,137 +55,6 @@
 #define LPB_REG_ROWS 0
 #define LPB_MIN_BLOCKS 2
 #define LPB_RULE 0
-#include "simplex_batched_impl.cuh"
-#undef LPB_NS
-#undef LPB_SWEEP_WARPS
-#undef LPB_REG_ROWS
-#undef LPB_MIN_BLOCKS
-#undef LPB_RULE
-
-#define LPB_NS reg15
-#define LPB_SWEEP_WARPS 15
-#define LPB_REG_ROWS 12
-#define LPB_MIN_BLOCKS 1
-#define LPB_RULE 0
-#include "simplex_batched_impl.cuh"
-#undef LPB_NS
-#undef LPB_SWEEP_WARPS
-#undef LPB_REG_ROWS
-#undef LPB_MIN_BLOCKS
-#undef LPB_RULE
-
-// Small problems: one sweep warp + the bookkeeping warp per LP.  A 64-thread CTA needs a fraction of
-// the registers of the 288-thread one, so 8-16 LPs are resident per SM instead of 2 (measured on
-// B200, tools/gpu/variant_grid.py: 3x the pivots/s at 30x30, 1.8x at 50x50).  Two register budgets:
-// tiny1 (64 registers, 16 CTAs/SM) for diet-size problems, small1 (120 registers, 8 CTAs/SM) where
-// shared memory limits the residency anyway.
-#define LPB_NS tiny1
-#define LPB_SWEEP_WARPS 1
-#define LPB_REG_ROWS 0
-#define LPB_MIN_BLOCKS 16
-#define LPB_RULE 0
-#include "simplex_batched_impl.cuh"
-#undef LPB_NS
-#undef LPB_SWEEP_WARPS
-#undef LPB_REG_ROWS
-#undef LPB_MIN_BLOCKS
-#undef LPB_RULE
-
-#define LPB_NS small1
-#define LPB_SWEEP_WARPS 1
-#define LPB_REG_ROWS 0
-#define LPB_MIN_BLOCKS 8
-#define LPB_RULE 0
-#include "simplex_batched_impl.cuh"
-#undef LPB_NS
-#undef LPB_SWEEP_WARPS
-#undef LPB_REG_ROWS
-#undef LPB_MIN_BLOCKS
-#undef LPB_RULE
-
-// course-size problems (ad_allocation: up to 50 x 100): four sweep warps + the bookkeeping warp
-#define LPB_NS mid4
-#define LPB_SWEEP_WARPS 4
-#define LPB_REG_ROWS 0
-#define LPB_MIN_BLOCKS 4
-#define LPB_RULE 0
-#include "simplex_batched_impl.cuh"
-#undef LPB_NS
-#undef LPB_SWEEP_WARPS
-#undef LPB_REG_ROWS
-#undef LPB_MIN_BLOCKS
-#undef LPB_RULE
-
-// the corrected (non-reference) mode, LPB200_RULE_BLAND: same kernel, other pivoting decisions
-#define LPB_NS bland8
-#define LPB_SWEEP_WARPS 8
-#define LPB_REG_ROWS 0
-#define LPB_MIN_BLOCKS 2
-#define LPB_RULE 1
-#include "simplex_batched_impl.cuh"
-#undef LPB_NS
-#undef LPB_SWEEP_WARPS
-#undef LPB_REG_ROWS
-#undef LPB_MIN_BLOCKS
-#undef LPB_RULE
-
-
-// LPB200_RULE_DANTZIG: largest-coefficient pricing with a Bland fallback on degenerate streaks
-#define LPB_NS dantzig8
-#define LPB_SWEEP_WARPS 8
-#define LPB_REG_ROWS 0
-#define LPB_MIN_BLOCKS 2
-#define LPB_RULE 2
-#include "simplex_batched_impl.cuh"
-#undef LPB_NS
-#undef LPB_SWEEP_WARPS
-#undef LPB_REG_ROWS
-#undef LPB_MIN_BLOCKS
-#undef LPB_RULE
-
-// LPB200_RULE_DEVEX: Devex reference-framework weights (approximate steepest edge), same Bland fallback
-#define LPB_NS devex8
-#define LPB_SWEEP_WARPS 8
-#define LPB_REG_ROWS 0
-#define LPB_MIN_BLOCKS 2
-#define LPB_RULE 3
-#include "simplex_batched_impl.cuh"
-#undef LPB_NS
-#undef LPB_SWEEP_WARPS
-#undef LPB_REG_ROWS
-#undef LPB_MIN_BLOCKS
-#undef LPB_RULE
-
-#define LPB_NS devex_tiny1
-#define LPB_SWEEP_WARPS 1
-#define LPB_REG_ROWS 0
-#define LPB_MIN_BLOCKS 16
-#define LPB_RULE 3
-#include "simplex_batched_impl.cuh"
-#undef LPB_NS
-#undef LPB_SWEEP_WARPS
-#undef LPB_REG_ROWS
-#undef LPB_MIN_BLOCKS
-#undef LPB_RULE
-
-// the corrected rules on diet-size problems (n, m <= 30): the two-warp CTA
-#define LPB_NS bland_tiny1
-#define LPB_SWEEP_WARPS 1
-#define LPB_REG_ROWS 0
-#define LPB_MIN_BLOCKS 16
-#define LPB_RULE 1
-#include "simplex_batched_impl.cuh"
-#undef LPB_NS
-#undef LPB_SWEEP_WARPS
-#undef LPB_REG_ROWS
-#undef LPB_MIN_BLOCKS
-#undef LPB_RULE
-
-#define LPB_NS dantzig_tiny1
-#define LPB_SWEEP_WARPS 1
-#define LPB_REG_ROWS 0
-#define LPB_MIN_BLOCKS 16
-#define LPB_RULE 2
 #include "simplex_batched_impl.cuh"
 #undef LPB_NS
 #undef LPB_SWEEP_WARPS
@@ -228,14 +98,14 @@ extern "C" int64_t lpb200_simplex_batch_smem_bytes(int n, int m)
 // LPB_BATCH_KERNEL=smem|tiny|small|mid|reg forces one (A/B measurements, tests); reg is the
 // register-resident experiment: bit-exact but slower on B200 (32 M vs 81 M pivots/s on Config 4 D2:
 // with one CTA per SM nothing overlaps the serial stage/ratio chain).
-enum { V_SMEM8 = 0, V_REG15, V_TINY1, V_SMALL1, V_MID4 };
+enum { V_SMEM8 = LPB_V_SMEM8, V_REG15 = LPB_V_REG15, V_TINY1 = LPB_V_TINY1, V_SMALL1 = LPB_V_SMALL1, V_MID4 = LPB_V_MID4 };
 static int pick_variant(int B, int n, int m, const DeviceInfo &di)
 {
     const int npairs = (m + 3) / 2, nphys = n + 2;
     const bool one_warp_ok = npairs <= 32;
     if (const char *force = getenv("LPB_BATCH_KERNEL")) {
         switch (force[0]) {
-        case 'r': return reg15::eligible(n, m) && reg15::make_batch_shape(n, m).bytes <= di.max_smem_optin ? V_REG15 : V_SMEM8;
+        case 'r': return lpb_batch_variant_eligible(LPB_V_REG15, n, m) && lpb_batch_variant_smem_bytes(LPB_V_REG15, n, m) <= di.max_smem_optin ? V_REG15 : V_SMEM8;
         case 't': return one_warp_ok ? V_TINY1 : V_SMEM8;
         case 'm': return V_MID4;
         case 's': return force[1] == 'm' && force[2] == 'a' ? (one_warp_ok ? V_SMALL1 : V_SMEM8) : V_SMEM8;
@@ -247,7 +117,7 @@ static int pick_variant(int B, int n, int m, const DeviceInfo &di)
     // (a lone 50x50 LP: 2.7 us per pivot on smem8, 3.7 on small1)
     if (B <= 2 * di.sm_count) return V_SMEM8;
     if (one_warp_ok && nphys * npairs <= 1500) return V_SMALL1;
-    if ((long long)mid4::make_batch_shape(n, m).bytes * 3 + 3 * 1024 <= (long long)di.max_smem_per_sm) return V_MID4;
+    if (lpb_batch_variant_smem_bytes(LPB_V_MID4, n, m) * 3 + 3 * 1024 <= (long long)di.max_smem_per_sm) return V_MID4;
     return V_SMEM8;
 }
 
@@ -272,21 +142,18 @@ extern "C" int lpb200_simplex_batch_ex_device(int B, int n, int m, const void *A
     DeviceInfo di;
     rc = get_device_info(&di);
     if (rc) return rc;
-#define LPB_LAUNCH(ns) \
-    ns::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots, pivot_log, log_cap, stream)
+#define LPB_LAUNCH(v) \
+    lpb_batch_variant_launch(v, di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots, pivot_log, log_cap, stream)
     if (rule != LPB200_RULE_REFERENCE) {  // corrected modes: the two-warp CTA for diet-size problems, else 8+1 warps
         const char *force = getenv("LPB_BATCH_KERNEL");
         const bool tiny = (n <= 30 && m <= 30 && !(force && force[0] == 's' && force[1] == 'm' && force[2] == 'e'));
-        if (rule == LPB200_RULE_DEVEX) return tiny ? LPB_LAUNCH(devex_tiny1) : LPB_LAUNCH(devex8);
-        if (rule == LPB200_RULE_DANTZIG) return tiny ? LPB_LAUNCH(dantzig_tiny1) : LPB_LAUNCH(dantzig8);
-        return tiny ? LPB_LAUNCH(bland_tiny1) : LPB_LAUNCH(bland8);
+        if (rule == LPB200_RULE_DEVEX) return tiny ? LPB_LAUNCH(LPB_V_DEVEX_TINY1) : LPB_LAUNCH(LPB_V_DEVEX8);
+        if (rule == LPB200_RULE_DANTZIG) return tiny ? LPB_LAUNCH(LPB_V_DANTZIG_TINY1) : LPB_LAUNCH(LPB_V_DANTZIG8);
+        return tiny ? LPB_LAUNCH(LPB_V_BLAND_TINY1) : LPB_LAUNCH(LPB_V_BLAND8);
     }
-    switch (pick_variant(B, n, m, di)) {
-    case V_TINY1: return LPB_LAUNCH(tiny1);
-    case V_SMALL1: return LPB_LAUNCH(small1);
-    case V_MID4: return LPB_LAUNCH(mid4);
-    case V_REG15: return LPB_LAUNCH(reg15);
-    default: break;
+    {
+        const int v = pick_variant(B, n, m, di);
+        if (v != V_SMEM8) return LPB_LAUNCH(v);
     }
 #undef LPB_LAUNCH
     return smem8::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots, pivot_log,
