@@ -95,5 +95,39 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB_PATH
 
 
+def build_variant(name: str, defines, verbose: bool = False) -> str:
+    """An experiment library next to the product one: variants/liblp_b200_<name>.so built with extra -D flags
+    (A/B on one box through LPB_LIB_PATH, see tools/gpu/ab_variants.sh).  Always rebuilt."""
+    nvcc = find_nvcc()
+    vdir = os.path.join(HERE, "variants")
+    odir = os.path.join(vdir, "_obj_" + name)
+    os.makedirs(odir, exist_ok=True)
+    out = os.path.join(vdir, "liblp_b200_%s.so" % name)
+
+    def compile_one(src: str):
+        obj = os.path.join(odir, os.path.splitext(src)[0] + ".o")
+        cmd = [nvcc] + NVCC_FLAGS + list(defines) + (["-Xptxas", "-v"] if verbose else []) + \
+              ["-c", "-o", obj, os.path.join(CSRC, src)]
+        return src, obj, subprocess.run(cmd, capture_output=True, text=True)
+
+    objs = []
+    with ThreadPoolExecutor(max_workers=os.cpu_count() or 1) as pool:
+        for src, obj, res in pool.map(compile_one, _sources()):
+            if res.returncode != 0:
+                raise RuntimeError("nvcc failed on %s:\n%s%s" % (src, res.stdout, res.stderr))
+            if verbose:
+                sys.stderr.write(res.stderr)
+            objs.append(obj)
+    res = subprocess.run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC",
+                          "-o", out] + objs, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc link failed:\n" + res.stdout + res.stderr)
+    return out
+
+
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--variant" in sys.argv:  # python -m linear_programming_b200.build --variant timing -DLPB_TIMING
+        i = sys.argv.index("--variant")
+        print(build_variant(sys.argv[i + 1], [a for a in sys.argv[i + 2:] if a.startswith("-D")], verbose="-v" in sys.argv))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -62,6 +62,24 @@
 #undef LPB_MIN_BLOCKS
 #undef LPB_RULE
 
+// The same kernel with every sweep warp owning whole rows and the next pivot's ratio test fused into the sweep:
+// one block barrier per pivot (simplex_batched_impl.cuh "warp-owns-rows").  Opt-in (LPB_BATCH_KERNEL=w), bit-exact,
+// a measured experiment: 74 M pivots/s against the 83 M of smem8 on the D2 batch -- the barrier it removes was not
+// what the pivot waits for (stores and the per-warp fixed work are).
+#define LPB_NS rows8
+#define LPB_SWEEP_WARPS 8
+#define LPB_REG_ROWS 0
+#define LPB_MIN_BLOCKS 2
+#define LPB_RULE 0
+#define LPB_WARP_ROWS 1
+#include "simplex_batched_impl.cuh"
+#undef LPB_NS
+#undef LPB_SWEEP_WARPS
+#undef LPB_REG_ROWS
+#undef LPB_MIN_BLOCKS
+#undef LPB_RULE
+#undef LPB_WARP_ROWS
+
 // ======================================================================================
 // Host side: C ABI
 // ======================================================================================
@@ -98,7 +116,7 @@ extern "C" int64_t lpb200_simplex_batch_smem_bytes(int n, int m)
 // LPB_BATCH_KERNEL=smem|tiny|small|mid|reg forces one (A/B measurements, tests); reg is the
 // register-resident experiment: bit-exact but slower on B200 (32 M vs 81 M pivots/s on Config 4 D2:
 // with one CTA per SM nothing overlaps the serial stage/ratio chain).
-enum { V_SMEM8 = LPB_V_SMEM8, V_REG15 = LPB_V_REG15, V_TINY1 = LPB_V_TINY1, V_SMALL1 = LPB_V_SMALL1, V_MID4 = LPB_V_MID4 };
+enum { V_ROWS8 = 100, V_SMEM8 = LPB_V_SMEM8, V_REG15 = LPB_V_REG15, V_TINY1 = LPB_V_TINY1, V_SMALL1 = LPB_V_SMALL1, V_MID4 = LPB_V_MID4 };
 static int pick_variant(int B, int n, int m, const DeviceInfo &di)
 {
     const int npairs = (m + 3) / 2, nphys = n + 2;
@@ -108,6 +126,7 @@ static int pick_variant(int B, int n, int m, const DeviceInfo &di)
         case 'r': return lpb_batch_variant_eligible(LPB_V_REG15, n, m) && lpb_batch_variant_smem_bytes(LPB_V_REG15, n, m) <= di.max_smem_optin ? V_REG15 : V_SMEM8;
         case 't': return one_warp_ok ? V_TINY1 : V_SMEM8;
         case 'm': return V_MID4;
+        case 'w': return V_ROWS8;  // "warp-owns-rows"
         case 's': return force[1] == 'm' && force[2] == 'a' ? (one_warp_ok ? V_SMALL1 : V_SMEM8) : V_SMEM8;
         default: break;
         }
@@ -153,6 +172,9 @@ extern "C" int lpb200_simplex_batch_ex_device(int B, int n, int m, const void *A
     }
     {
         const int v = pick_variant(B, n, m, di);
+        if (v == V_ROWS8)
+            return rows8::launch(di, B, n, m, A, a_dtype, b, c, tol, max_pivots, status, x, objective, npivots,
+                                 pivot_log, log_cap, stream);
         if (v != V_SMEM8) return LPB_LAUNCH(v);
     }
 #undef LPB_LAUNCH

@@ -7,7 +7,13 @@
 //                     R > 0: tableau held in REGISTERS during the pivot loop, R rows x one
 //                     column pair per thread (1 CTA per SM), shared memory keeps the vectors
 //   LPB_MIN_BLOCKS    __launch_bounds__ minimum resident CTAs per SM
+//   LPB_WARP_ROWS     1: every sweep warp OWNS a block of whole tableau rows and the next pivot's ratio test is
+//                     fused into the sweep -- ONE block barrier per pivot (see "warp-owns-rows" below);
+//                     0 (default): column-pair lanes x row groups, two block barriers per pivot
 // See simplex_batched.cu for the design notes and the reference map.
+#ifndef LPB_WARP_ROWS
+#define LPB_WARP_ROWS 0
+#endif
 
 namespace lpb {
 namespace LPB_NS {
@@ -67,6 +73,7 @@ static BatchShape make_batch_shape(int n, int m)
     s.rpg = align_up((nphys + s.groups - 1) / s.groups, kRowChunk);
     s.rpt = (nphys + s.groups - 1) / s.groups;
     s.nfc = s.groups * s.rpg + kRowChunk;
+    if (s.nfc < align_up(nphys, kRowChunk) + kRowChunk) s.nfc = align_up(nphys, kRowChunk) + kRowChunk;
     if (const char *g = getenv("LPB_DEBUG_SPAD")) s.S = W + 2 * (atoi(g) / 2);
     s.size_i0 = pyset_initial_size(m);
     s.size_i1 = pyset_initial_size(m + 1);
@@ -81,7 +88,7 @@ static BatchShape make_batch_shape(int n, int m)
     s.off_fc = o;         o += s.nfc * 8;
     s.off_pinvs = o;      o += s.nfc * 8;
     s.off_bcol = o;       o += s.nfc * 8;
-    s.off_redkey = o;     o += kSweepWarps * 16;
+    s.off_redkey = o;     o += 3 * kSweepWarps * 16;  // sets of per-warp ratio partials: [0],[1] fused (by pivot parity), [2] stand-alone
     s.off_rowvar = o;     o += align_up(nphys, 4) * 4;
     s.off_nonecol = o;    o += align_up(nphys, 4) * 4;
     s.off_untouched = o;  o += align_up(nphys, 4) * 4;
@@ -92,7 +99,7 @@ static BatchShape make_batch_shape(int n, int m)
     s.off_basis0 = o;     o += align_up((nv + 31) / 32, 4) * 4;
     s.off_redvar = o;     o += align_up(kSweepWarps, 4) * 4;
     s.off_redu32 = o;     o += ((kSweepWarps + 2 + 3) / 4) * 16;
-    s.off_misc = o;       o += 16 * 4;
+    s.off_misc = o;       o += 16 * 4 + 16;  // 16 ints + two mbarriers (LPB_WARP_ROWS)
     s.off_tab_i = o;      o += align_up(s.cap_i * (int)sizeof(tab_t), 16);
     s.off_tab_d = o;      o += align_up(s.cap_d * (int)sizeof(tab_t), 16);
     s.off_tab_s = o;      o += align_up(s.cap_s * (int)sizeof(tab_t), 16);
@@ -132,6 +139,11 @@ struct Ctx {
     int n, m, S, npairs, cx, rpg, rpt;
     int cxi, row0, row1;  // this thread's column-pair lane and physical row block [row0, row1)
     int spare;  // physical row slot currently unused (uniform across the CTA)
+    // LPB_WARP_ROWS: rows [r_lo, r_hi) belong to this thread's warp (rpw per warp, nw warps own rows), warp `ow`
+    // owns the objective row; nfused counts the fused pivots of this CTA (parity of the two mbarriers below)
+    int rpw, r_lo, r_hi, ow, nw;
+    unsigned nfused;
+    unsigned long long *mbar;  // [0] "objective key published" (warp ow -> 9th warp), [1] "next entering column published"
     double tol;
     bool track_dep;  // the `dependent` set order only matters when phase 1 runs (:538)
     unsigned long long *timing;
@@ -311,7 +323,7 @@ __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool 
     int crash = 0;
     // only the warps that own rows take part (4 of 8 at n = 100)
     const int nsw = min(kSweepWarps, (nphys + 31) >> 5);
-    RatioPartial *part = reinterpret_cast<RatioPartial *>(c.redkey);
+    RatioPartial *part = reinterpret_cast<RatioPartial *>(c.redkey) + 2 * kSweepWarps;  // the stand-alone set
     if (tid < nsw * 32) {
         unsigned long long key = kKeyNone;
         int var = 0x7fffffff;
@@ -517,10 +529,13 @@ __device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, 
                         a2y = __dadd_rn(a2y, __dmul_rn(fb.x, r2.y));
                         a3x = __dadd_rn(a3x, __dmul_rn(fb.y, r2.x));
                         a3y = __dadd_rn(a3y, __dmul_rn(fb.y, r2.y));
+#ifndef LPB_EXP_NOSTORE
                         sts_f64x2(qa, a0x, a0y);
                         sts_f64x2(qa + rsb, a1x, a1y);
                         sts_f64x2(qa + 2 * rsb, a2x, a2y);
                         sts_f64x2(qa + 3 * rsb, a3x, a3y);
+#endif
+#ifndef LPB_EXP_NOSNAP
                         sts_zero_if_snapped(qa, a0x, tol);
                         sts_zero_if_snapped(qa + 8, a0y, tol);
                         sts_zero_if_snapped(qa + rsb, a1x, tol);
@@ -529,6 +544,7 @@ __device__ __forceinline__ void sweep(Ctx &c, int ncols, int p, int src, int e, 
                         sts_zero_if_snapped(qa + 2 * rsb + 8, a2y, tol);
                         sts_zero_if_snapped(qa + 3 * rsb, a3x, tol);
                         sts_zero_if_snapped(qa + 3 * rsb + 8, a3y, tol);
+#endif
                     } else {
 #ifdef LPB_TIMING
                         const long long ts0 = clock64();
@@ -615,6 +631,406 @@ __device__ __forceinline__ int next_entering(const Ctx &c, int ncols)
     for (int q = 1; q < kKeySlots; ++q) best = min(best, u[q]);
     return best == 0xffffffffu ? -1 : (int)(best & 0xffffu);
 }
+
+
+#if LPB_WARP_ROWS
+// =========================================================================================
+// Warp-owns-rows pivot loop: ONE block barrier per pivot.
+//
+// Every sweep warp owns a contiguous block of whole physical rows (13 of the 102 at 100x100); its 32 lanes
+// cover the column pairs in passes of 32 (two passes at m = 100: 32 + 19 lanes).  Consequences:
+//   * every per-row decision (pivot row / spare slot / zero factor) is warp-uniform: no divergence;
+//   * a row is only ever written by its own warp, so the NEXT pivot's ratio test of a row -- read its entry
+//     in the next entering column, zero it in place, divide the row's constant by it (pick_leaving_idx,
+//     simplex.py:394-436) -- can be done by that warp right behind its own part of the sweep, ordered by a
+//     __syncwarp() alone.  The stage_and_ratio() pass between two block barriers disappears;
+//   * the warp that owns the objective row updates it FIRST and publishes its entering key; the 9th warp
+//     (set bookkeeping, simplex.py:369-381) merges in the key of the column that changed hands and publishes
+//     the next entering column.  Both hand-overs are mbarriers in shared memory: the producer arrives once,
+//     the consumers only wait -- they never wait for each other.
+// Per pivot and warp:  [block barrier] reduce 8 ratio partials -> sweep own rows -> wait(next column) ->
+// ratio test of own rows -> partial -> [block barrier].
+// Same operations on the same operands as the two-barrier path: bit-identical results (the parity tests run
+// both).
+// =========================================================================================
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_addr(bar)), "r"(parity) : "memory");
+}
+
+// Ratio test of the rows this warp owns for the NEXT pivot (entering column position p2), fused behind the
+// warp's part of the sweep.  Same per-row work as stage_and_ratio(); leaves the warp's partial in part[w].
+__device__ __forceinline__ void stage_rows(const Ctx &c, int p2, RatioPartial *part)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int e2 = c.colvar[p2];
+    unsigned long long key = kKeyNone;
+    int var = 0x7fffffff;
+    int crash = 0;
+#if !LPB_CORRECTED
+    const bool e_in_basis0 = (c.basis0[e2 >> 5] >> (e2 & 31)) & 1u;
+    const bool e_is_slack = e2 < c.n;
+#endif
+    for (int i = c.r_lo + lane; i < c.r_hi; i += 32) {
+        const int v = c.rowvar[i];
+        double f = 0.0;
+        if (v >= 0 || i == c.n) {
+            double *q = c.T + (size_t)i * c.S + 1 + p2;
+            f = *q;
+            *q = 0.0;
+            if (fabs(f) <= c.tol) f = 0.0;  // substitute() returns the row unchanged (:203-205)
+        }
+        c.fc[i] = f;
+        if (v >= 0) {
+#if !LPB_CORRECTED
+            const int nc = c.nonecol[i];
+            crash |= (nc == kNoneInitial && e_is_slack) || (nc == e2) || (c.untouched[i] && e_in_basis0);
+#endif
+            if (f != 0.0) {  // row is rewritten by this pivot: its only None is column e
+                c.nonecol[i] = e2;
+                c.untouched[i] = 0;
+            }
+            const double coeff = -f;
+            if (coeff > c.tol) {
+                c.pinvs[i] = pivot_inverse(f, c.tol);
+                const double ratio = snap(__ddiv_rn(c.T[(size_t)i * c.S], coeff), c.tol);
+                if (ratio != 0.0 || LPB_CORRECTED) {  // zero ratios count as +inf in min_index (:161)
+                    const unsigned long long k = order_key(ratio);
+                    const int vi = (v << 16) | i;
+                    if (k < key || (k == key && vi < var)) {
+                        key = k;
+                        var = vi;
+                    }
+                }
+            }
+        }
+    }
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    const unsigned mh = __reduce_min_sync(0xffffffffu, hi);
+    const unsigned ml = __reduce_min_sync(0xffffffffu, hi == mh ? lo : 0xffffffffu);
+    const unsigned mi = __reduce_min_sync(0xffffffffu, (hi == mh && lo == ml) ? (unsigned)var : 0x7fffffffu);
+    crash = __any_sync(0xffffffffu, crash);
+    if (lane == 0) {
+        RatioPartial r;
+        r.key = ((unsigned long long)mh << 32) | ml;
+        r.id = (int)mi;
+        r.pad = crash;
+        part[w] = r;
+    }
+}
+
+// After the block barrier: the leaving row from the warps' partials -- lane w of every warp takes part[w], three
+// redux.sync steps give the lexicographic (ratio key, id) minimum.  Same return value as stage_and_ratio().
+__device__ __forceinline__ int reduce_rows(const Ctx &c, const RatioPartial *part, unsigned long long *best_key = nullptr)
+{
+    const int lane = threadIdx.x & 31;
+    unsigned long long key = kKeyNone;
+    unsigned var = 0x7fffffffu;
+    int crash = 0;
+    if (lane < c.nw) {
+        const RatioPartial r = part[lane];
+        key = r.key;
+        var = (unsigned)r.id;
+        crash = r.pad;
+    }
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    const unsigned mh = __reduce_min_sync(0xffffffffu, hi);
+    const unsigned ml = __reduce_min_sync(0xffffffffu, hi == mh ? lo : 0xffffffffu);
+    const unsigned mi = __reduce_min_sync(0xffffffffu, (hi == mh && lo == ml) ? var : 0x7fffffffu);
+    crash = __any_sync(0xffffffffu, crash);
+    if (best_key) *best_key = ((unsigned long long)mh << 32) | ml;
+    if (crash) return -2;
+    return (mh == 0xffffffffu && ml == 0xffffffffu) ? -1 : (int)mi;
+}
+
+// R rows (warp-uniform indices ri[] relative to the block base q0) x the two column-pair passes of this lane:
+// all loads first, then T[i][k] = snap(T[i][k] + f_i * r_k) with two roundings (sexp, simplex.py:185-194).
+// The factor of row ri[j] sits in lane ri[j]'s register.
+template <int R>
+__device__ __forceinline__ void sweep_chunk(uint32_t q0, uint32_t rsb, const int (&ri)[kRowChunk], double fmine,
+                                            const double2 rA, const double2 rB, bool hasA, bool hasB, double tol)
+{
+    double f[R];
+#pragma unroll
+    for (int j = 0; j < R; ++j) f[j] = __shfl_sync(0xffffffffu, fmine, ri[j]);
+#pragma unroll
+    for (int pass = 0; pass < 2; ++pass) {
+        const bool has = pass ? hasB : hasA;
+        const double2 r2 = pass ? rB : rA;
+        const uint32_t qb = q0 + (pass ? 512u : 0u);
+        if (has) {
+            double vx[R], vy[R];
+#pragma unroll
+            for (int j = 0; j < R; ++j) lds_f64x2(qb + (uint32_t)ri[j] * rsb, vx[j], vy[j]);
+            double px[R], py[R];
+#pragma unroll
+            for (int j = 0; j < R; ++j) {  // the products do not depend on the loads: they run while those are in flight
+                px[j] = __dmul_rn(f[j], r2.x);
+                py[j] = __dmul_rn(f[j], r2.y);
+            }
+#ifndef LPB_EXP_NOMATH  // (LPB_EXP_*: timing experiments only, tools/gpu/pivot_rate.py -- the answers are wrong)
+#pragma unroll
+            for (int j = 0; j < R; ++j) {
+                vx[j] = __dadd_rn(vx[j], px[j]);
+                vy[j] = __dadd_rn(vy[j], py[j]);
+            }
+#endif
+#ifndef LPB_EXP_NOSTORE
+#pragma unroll
+            for (int j = 0; j < R; ++j) sts_f64x2(qb + (uint32_t)ri[j] * rsb, vx[j], vy[j]);
+#endif
+#ifndef LPB_EXP_NOSNAP
+#pragma unroll
+            for (int j = 0; j < R; ++j) {
+                sts_zero_if_snapped(qb + (uint32_t)ri[j] * rsb, vx[j], tol);
+                sts_zero_if_snapped(qb + (uint32_t)ri[j] * rsb + 8u, vy[j], tol);
+            }
+#endif
+        }
+    }
+}
+
+// SlackForm.pivot(e, l) (:348-385) with every warp sweeping the rows it owns; with do_next also the selection of
+// the next entering column and the ratio test on it.  Returns (uniform across the CTA) the published next key:
+// 0xffffffff = no candidate, bit 31 of *resel set = the set table was rebuilt (every slot moved): reselect.
+__device__ __forceinline__ unsigned sweep_rows(Ctx &c, int ncols, int p, int src, int e, int l, int32_t *log,
+                                               int log_cap, int npiv, bool do_next, unsigned *resel)
+{
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int n = c.n, S = c.S;
+    const int dest = c.spare;
+    const double tol = c.tol;
+    const double pinv = c.pinvs[src];  // snap(-1 * (1.0 / pivot)), left by the row's own ratio test
+    const uint32_t par = c.nfused & 1u;
+    RatioPartial *part = reinterpret_cast<RatioPartial *>(c.redkey) + (do_next ? par * kSweepWarps : 0u);
+    unsigned nk = 0xffffffffu, rs = 0u;
+#ifdef LPB_TIMING
+    const long long tt0 = clock64();
+    long long tt1 = tt0, tt2 = tt0, tt3 = tt0, tt4 = tt0;
+#endif
+    if (tid < kSweepThreads) {
+        const int npairs = c.npairs;
+        const double2 *Tsrc = reinterpret_cast<const double2 *>(c.T + (size_t)src * S);
+        const double dpiv = snap(-pinv, tol);  // coefficient of l in the new row of e (:343-344)
+        const int pp = 1 + p;
+        // ---- the objective row first: its owner publishes the entering key of every column but p ----
+        if (w == c.ow) {
+            const double fobj = c.fc[n];
+            unsigned mykey = 0xffffffffu;
+            double2 *Tobj = reinterpret_cast<double2 *>(c.T + (size_t)n * S);
+            for (int cp = lane; cp < npairs; cp += 32) {
+                double2 r2 = Tsrc[cp];
+                r2.x = (2 * cp == pp) ? dpiv : snap(__dmul_rn(pinv, r2.x), tol);
+                r2.y = (2 * cp + 1 == pp) ? dpiv : snap(__dmul_rn(pinv, r2.y), tol);
+                double2 a = Tobj[cp];
+                if (fobj != 0.0) {
+                    a.x = axpy_snap(a.x, fobj, r2.x, tol);
+                    a.y = axpy_snap(a.y, fobj, r2.y, tol);
+                    Tobj[cp] = a;
+                }
+                const int k0 = 2 * cp - 1;  // column position of a.x (-1 is the constant)
+                if (k0 >= 0 && k0 < ncols && k0 != p && a.x > tol)
+                    mykey = min(mykey, ((unsigned)c.colslot[k0] << 16) | (unsigned)k0);
+                if (k0 + 1 < ncols && k0 + 1 != p && a.y > tol)
+                    mykey = min(mykey, ((unsigned)c.colslot[k0 + 1] << 16) | (unsigned)(k0 + 1));
+            }
+            if (do_next) {
+                mykey = __reduce_min_sync(0xffffffffu, mykey);
+                if (lane == 0) {
+                    c.redu32[0] = mykey;
+                    mbar_arrive(&c.mbar[0]);  // release: the key is visible to whoever sees the phase flip
+                }
+            }
+        }
+#ifdef LPB_TIMING
+        tt1 = clock64();
+#endif
+        // ---- the rows of this warp, 64 column pairs (two passes of the 32 lanes) at a time ----
+        // Blocks of up to 32 rows: lane j keeps the factor of row rb + j in a register; the rows that take the
+        // plain update (non-zero factor, not the old pivot row, not the slot of the new one, not the objective
+        // row) are a bit mask, walked four at a time -- every decision is warp-uniform, there is no slow path.
+        const uint32_t tbase = smem_addr(c.T);
+        const uint32_t rsb = (uint32_t)S * 8u;  // row stride in bytes
+        for (int rb = c.r_lo; rb < c.r_hi; rb += 32) {
+            const int nrows = min(32, c.r_hi - rb);
+            const double fmine = (lane < nrows) ? c.fc[rb + lane] : 0.0;
+            unsigned live = __ballot_sync(0xffffffffu, fmine != 0.0);
+            if ((unsigned)(src - rb) < 32u) live &= ~(1u << (src - rb));
+            if ((unsigned)(dest - rb) < 32u) live &= ~(1u << (dest - rb));
+            if ((unsigned)(n - rb) < 32u) live &= ~(1u << (n - rb));
+            const bool dest_here = (unsigned)(dest - rb) < (unsigned)nrows;
+            for (int g0 = 0; g0 < npairs; g0 += 64) {
+                const int cpA = g0 + lane, cpB = cpA + 32;
+                const bool hasA = cpA < npairs, hasB = cpB < npairs;
+                double2 rA = make_double2(0.0, 0.0), rB = make_double2(0.0, 0.0);
+                if (hasA) {  // this lane's entries of the scaled pivot row (make_pivot_constraint :325-345)
+                    rA = Tsrc[cpA];
+                    rA.x = (2 * cpA == pp) ? dpiv : snap(__dmul_rn(pinv, rA.x), tol);
+                    rA.y = (2 * cpA + 1 == pp) ? dpiv : snap(__dmul_rn(pinv, rA.y), tol);
+                }
+                if (hasB) {
+                    rB = Tsrc[cpB];
+                    rB.x = (2 * cpB == pp) ? dpiv : snap(__dmul_rn(pinv, rB.x), tol);
+                    rB.y = (2 * cpB + 1 == pp) ? dpiv : snap(__dmul_rn(pinv, rB.y), tol);
+                }
+                const uint32_t q0 = tbase + (uint32_t)rb * rsb + (uint32_t)cpA * 16u;  // pass B sits 512 bytes further
+                if (dest_here) {  // store(entering_idx, entering_constraint) (:352)
+                    const uint32_t qd = q0 + (uint32_t)(dest - rb) * rsb;
+                    if (hasA) sts_f64x2(qd, rA.x, rA.y);
+                    if (hasB) sts_f64x2(qd + 512u, rB.x, rB.y);
+                }
+                unsigned m = live;
+                while (m) {
+                    const int cnt = min(__popc(m), kRowChunk);
+                    int ri[kRowChunk];
+#pragma unroll
+                    for (int j = 0; j < kRowChunk; ++j) {
+                        ri[j] = m ? (__ffs(m) - 1) : 0;
+                        m &= m - 1u;  // (0 stays 0)
+                    }
+                    if (cnt == 4) {
+                        sweep_chunk<4>(q0, rsb, ri, fmine, rA, rB, hasA, hasB, tol);
+                    } else {  // the tail of the list: 1 .. 3 rows, one at a time
+#pragma unroll
+                        for (int j = 0; j < kRowChunk - 1; ++j) {
+                            if (j < cnt) {
+                                const int one[kRowChunk] = {ri[j], 0, 0, 0};
+                                sweep_chunk<1>(q0, rsb, one, fmine, rA, rB, hasA, hasB, tol);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+#ifdef LPB_TIMING
+        tt2 = tt3 = tt4 = clock64();
+#endif
+        if (do_next) {
+            __syncwarp();                // the lanes' stores to this warp's rows are ordered before the reads below
+            mbar_wait(&c.mbar[1], par);  // acquire: the 9th warp's bookkeeping and the key it published
+#ifdef LPB_TIMING
+            tt3 = tt4 = clock64();
+#endif
+            nk = *reinterpret_cast<const volatile unsigned *>(c.redu32 + kSweepWarps);
+            rs = *reinterpret_cast<const volatile unsigned *>(c.redu32 + kSweepWarps + 1);
+#ifdef LPB_EXP_NOSTAGE
+            if (rs == 0u && nk != 0xffffffffu && lane == 0) {  // keep the loop alive: any candidate row of this warp
+                RatioPartial r;
+                r.key = (c.rowvar[c.r_lo] >= 0 && c.r_lo != c.spare) ? 0x8000000000000001ull : kKeyNone;
+                r.id = (c.rowvar[c.r_lo] << 16) | c.r_lo;
+                r.pad = 0;
+                part[w] = r;
+                c.pinvs[c.r_lo] = -0.5;
+            }
+#else
+            if (rs == 0u && nk != 0xffffffffu) stage_rows(c, (int)(nk & 0xffffu), part);
+#endif
+#ifdef LPB_TIMING
+            tt4 = clock64();
+#endif
+        }
+    } else {
+        if (lane == 0) {
+            if (log != nullptr && npiv < log_cap) {
+                log[2 * npiv] = e;
+                log[2 * npiv + 1] = l;
+            }
+            bookkeeping(c, p, src, dest, e, l, pinv);  // leaves (key of column p, reselect) in redu32[kSweepWarps..+1]
+        }
+#ifdef LPB_TIMING
+        tt1 = tt2 = tt3 = tt4 = clock64();
+#endif
+        if (do_next) {
+            __syncwarp();
+            mbar_wait(&c.mbar[0], par);  // the objective row's key
+#ifdef LPB_TIMING
+            tt2 = tt3 = tt4 = clock64();
+#endif
+            if (lane == 0) {
+                const unsigned kp = c.redu32[kSweepWarps];
+                nk = min(kp, *reinterpret_cast<const volatile unsigned *>(c.redu32));
+                rs = c.redu32[kSweepWarps + 1];
+                c.redu32[kSweepWarps] = nk;
+                mbar_arrive(&c.mbar[1]);  // release: row/column maps, set tables and the key
+            }
+            nk = __shfl_sync(0xffffffffu, nk, 0);
+            rs = __shfl_sync(0xffffffffu, rs, 0);
+        }
+    }
+    if (do_next) ++c.nfused;
+    c.spare = src;
+    *resel = rs;
+    __syncthreads();
+#ifdef LPB_TIMING
+    if (c.timing != nullptr && lane == 0 && do_next) {
+        // [warp][0] objective pre-pass / bookkeeping, [1] own rows / wait for the objective key, [2] wait for the
+        // next column, [3] ratio test of own rows, [4] block barrier, [5] pivots
+        unsigned long long *t = c.timing + 192 + w * 6;
+        const long long tt5 = clock64();
+        atomicAdd(t + 0, (unsigned long long)(tt1 - tt0));
+        atomicAdd(t + 1, (unsigned long long)(tt2 - tt1));
+        atomicAdd(t + 2, (unsigned long long)(tt3 - tt2));
+        atomicAdd(t + 3, (unsigned long long)(tt4 - tt3));
+        atomicAdd(t + 4, (unsigned long long)(tt5 - tt4));
+        atomicAdd(t + 5, 1ull);
+    }
+#endif
+    return nk;
+}
+
+__device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pivots, int32_t *log,
+                                        int log_cap, int forced_p, int forced_lr)
+{
+    bool forced = forced_lr >= 0;
+    int p = forced ? forced_p : select_entering(c, ncols);
+    int status = 0;
+    int lr = 0;
+    bool staged = false;  // the ratio test on column p was done inside the previous sweep
+    for (;;) {
+        if (p < 0) break;
+        const int e = c.colvar[p];
+        if (!staged) lr = stage_and_ratio(c, p, e, forced);
+        if (forced) lr = forced_lr;
+        if (lr == -2) { status = LPB200_STATUS_REF_TYPE_ERROR; break; }
+        if (lr < 0) { status = LPB200_STATUS_INFINITY; break; }
+        if (npiv >= max_pivots) { status = LPB200_STATUS_ITERATION_LIMIT; break; }
+        const int l = lr >> 16, src = lr & 0xffff;
+        const RatioPartial *part = reinterpret_cast<const RatioPartial *>(c.redkey) + (c.nfused & 1u) * kSweepWarps;
+        unsigned resel = 0u;
+        const unsigned nk = sweep_rows(c, ncols, p, src, e, l, log, log_cap, npiv, !forced, &resel);
+        ++npiv;
+        if (forced || resel != 0u) {
+            // after a forced pivot, or when the set table was rebuilt (every slot moved, the keys are stale):
+            // a stand-alone pass over the objective row, then the stand-alone ratio test
+            forced = false;
+            staged = false;
+            p = select_entering(c, ncols);
+        } else {
+            p = (nk == 0xffffffffu) ? -1 : (int)(nk & 0xffffu);
+            staged = true;
+            if (p >= 0) lr = reduce_rows(c, part);
+        }
+    }
+    return status;
+}
+#endif  // LPB_WARP_ROWS
 
 #if LPB_REG_ROWS > 0
 // =========================================================================================
@@ -843,7 +1259,7 @@ __device__ __forceinline__ int run_loop(Ctx &c, int ncols, int &npiv, int max_pi
     __syncthreads();
     return status;
 }
-#else
+#elif !LPB_WARP_ROWS
 // SlackForm.solve loop (:442-466).  Returns 0 when optimal, else a terminal status code.
 // forced_lr >= 0: the first pivot is forced -- the variable at column position forced_p enters,
 // the basic variable forced_lr >> 16 in physical row forced_lr & 0xffff leaves (phase 1, :524:
@@ -1060,6 +1476,25 @@ simplex_batched_kernel(const BatchShape sh, const BatchArgs a)
     c.timing = a.timing;
     const double tol = a.tol;
     const int nfc = sh.nfc;
+#if LPB_WARP_ROWS
+    c.mbar = reinterpret_cast<unsigned long long *>(smem + sh.off_misc + 64);
+    {
+        const int rpw = (nphys + kSweepWarps - 1) / kSweepWarps;
+        const int w = tid >> 5;
+        c.rpw = rpw;
+        c.r_lo = min(w * rpw, nphys);
+        c.r_hi = min(c.r_lo + rpw, nphys);
+        c.ow = n / rpw;
+        c.nw = (nphys + rpw - 1) / rpw;
+    }
+    c.nfused = 0u;
+    if (tid == 0) {
+        mbar_init(&c.mbar[0], 1);
+        mbar_init(&c.mbar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+#endif
     {
         const int ry = tid / sh.cx;
         c.cxi = tid - ry * sh.cx;
@@ -1390,6 +1825,16 @@ static int launch(const DeviceInfo &di, int B, int n, int m, const void *A, int 
                 fprintf(stderr, "[lpb timing] warp %d: stage+bar %.0f  own sweep %.0f  sweep+bar %.0f cycles/pivot (%llu pivots)\n",
                         w, (double)h[w * 4] / h[w * 4 + 3], (double)h[w * 4 + 1] / h[w * 4 + 3],
                         (double)h[w * 4 + 2] / h[w * 4 + 3], h[w * 4 + 3]);
+#if LPB_WARP_ROWS
+        for (int w = 0; w <= kSweepWarps; ++w) {
+            const unsigned long long *t = h + 192 + w * 6;
+            if (t[5])
+                fprintf(stderr, "[lpb timing] warp %d: %s %.0f  %s %.0f  wait-next %.0f  ratio-own-rows %.0f  barrier %.0f  "
+                                "cycles/pivot (%llu fused pivots)\n", w, w < kSweepWarps ? "objective-row" : "bookkeeping",
+                        (double)t[0] / t[5], w < kSweepWarps ? "own-rows" : "wait-objective-key", (double)t[1] / t[5],
+                        (double)t[2] / t[5], (double)t[3] / t[5], (double)t[4] / t[5], t[5]);
+        }
+#endif
         for (int w = 0; w < kSweepWarps; ++w)
             if (h[w * 4 + 3])
                 fprintf(stderr, "[lpb timing] warp %d sweep: prologue %.0f  general path %.0f cycles/pivot in %.2f chunks/pivot\n", w,

@@ -339,7 +339,7 @@ def test_register_resident_variant_vs_oracle(oracle_lib, monkeypatch, dist, n, m
     assert np.array_equal(res.objective.view(np.int64), obj.view(np.int64))
 
 
-@pytest.mark.parametrize("variant", ["tiny", "small", "mid", "smem"])
+@pytest.mark.parametrize("variant", ["tiny", "small", "mid", "smem", "w"])
 def test_every_kernel_variant_is_bit_exact(oracle_lib, simplex_golden, monkeypatch, variant):
     """The library picks a CTA size per shape and batch size (1+1 warps for small problems, 4+1 for
     course-size ones, 8+1 for the 100x100 batch); every variant, forced through LPB_BATCH_KERNEL, gives
