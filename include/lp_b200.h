@@ -17,6 +17,14 @@
  *     on `stream` (a cudaStream_t passed as void*, NULL = default stream) without
  *     synchronising; the caller owns every buffer.  Entry points without that suffix take
  *     HOST pointers, copy in, run, copy out and synchronise (the end-to-end path).
+ *   - Domain of the bit-exact claim (status, pivot sequence, x, objective identical to the reference): integer
+ *     inputs (what the reference's parser produces, simplex.py:712-717), and floating-point inputs in which no
+ *     non-zero entry of A has magnitude <= tol.  The engine does not distinguish "coefficient is None" from
+ *     "coefficient is 0.0"; the reference's substitute() (simplex.py:203-205) keeps a sub-tolerance coefficient in
+ *     place where the engine zeroes it.  On such inputs status and pivot sequence still match and x / objective agree
+ *     within 1e-9 relative (tests/test_subtolerance_inputs.py, vectors produced by the reference).
+ *   - max_pivots is the one deliberate deviation from the drop-in behaviour: the reference has no cap (and can
+ *     cycle); the Python mirror defaults to max(10000, 50(n+m)), the CLI takes --max-pivots=N.
  *   - Per-problem outcome codes (status[]): the reference's anst values plus the classes in
  *     which the reference itself does not return:
  */
@@ -285,6 +293,19 @@ int lpb200_gauss_jordan_batch(int B, int n, const double *a, const double *b, do
 int lpb200_gauss_jordan_batch_ex_device(int B, int n, const double *a, const double *b, double *x, int pivoting,
                                         void *workspace, int64_t workspace_bytes, void *stream);
 int lpb200_gauss_jordan_batch_ex(int B, int n, const double *a, const double *b, double *x, int pivoting);
+
+/*
+ * The same two calls with a per-system outcome.  The reference has none: when SelectPivotElement
+ * (energy_values.cc:100-110) finds no row to swap a zero pivot with, it divides by zero and prints inf/nan; x[]
+ * reproduces that, and a batch caller would have to scan it.  status[B] (device / host memory like x):
+ *   -1   every step found a non-zero pivot
+ *   k    the first step k whose column holds no non-zero at or below the diagonal (the matrix is singular to the
+ *        arithmetic performed); x of that system is the reference's inf/nan output
+ */
+int lpb200_gauss_jordan_batch_status_device(int B, int n, const double *a, const double *b, double *x, int pivoting,
+                                            int32_t *status, void *workspace, int64_t workspace_bytes, void *stream);
+int lpb200_gauss_jordan_batch_status(int B, int n, const double *a, const double *b, double *x, int pivoting,
+                                     int32_t *status);
 
 #ifdef __cplusplus
 }

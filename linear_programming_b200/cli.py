@@ -23,6 +23,16 @@ process instead of one subprocess per LP.
 ``--rule=bland`` (LP programs only) answers with the corrected mode instead of the reference's
 behaviour (include/lp_b200.h LPB200_RULE_BLAND): no crash classes, Bland's anti-cycling rule;
 ``--rule=dantzig`` / ``--rule=devex`` the same with largest-coefficient / Devex pricing.
+
+``--max-pivots=N`` (LP programs) raises or lowers the one deliberate deviation from the reference: the
+engine stops an LP after max(10000, 50(n+m)) pivots (IterationLimitError / "IterationLimit") where the
+reference, which has no cap, would keep pivoting -- its set-order entering rule needs thousands of pivots
+on mixed-sign data and can cycle.
+
+The `simplex` program also runs the reference's post-condition (simplex.py:745: verify_bounds after every
+"Bounded solution"): when it fails the answer has been printed and the process then dies with
+AssertionError like the reference does; in --stream mode such a problem prints "AssertionError" on a line
+of its own instead of its answer (a per-process exit code has no meaning there).
 """
 from __future__ import annotations
 
@@ -96,17 +106,22 @@ def iter_equations(text: str):
         pos += 1 + need
 
 
-def _solve_lp_batch(A, b, c, rule="reference"):
+def _solve_lp_batch(A, b, c, rule="reference", max_pivots=None):
     """One shape group on the engine; separated out so CPU tests can substitute the checker."""
-    r = _simplex.solve_batch(A, b, c, rule=rule)
+    r = _simplex.solve_batch(A, b, c, rule=rule, max_pivots=max_pivots)
     return r.status, r.x
+
+
+def _verify_lp_batch(A, b, x, status):
+    """Simplex.verify_bounds (simplex.py:663-671) on one shape group: first failing row per LP, -1 = passes."""
+    return _simplex.verify_bounds_batch(A, b, x, status)
 
 
 def _solve_eq_batch(a, b):
     return gauss_jordan.solve_equation_batch(a, b)
 
 
-def solve_lp_stream(text: str, integer: bool, rule: str = "reference") -> str:
+def solve_lp_stream(text: str, integer: bool, rule: str = "reference", max_pivots=None, verify: bool = False) -> str:
     problems = list(iter_lp_problems(text, integer))
     groups = {}
     for idx, (n, m, _, _, _) in enumerate(problems):
@@ -116,10 +131,18 @@ def solve_lp_stream(text: str, integer: bool, rule: str = "reference") -> str:
         A = np.stack([problems[i][2] for i in idxs])
         b = np.stack([problems[i][3] for i in idxs])
         c = np.stack([problems[i][4] for i in idxs])
-        status, x = _solve_lp_batch(A, b, c, rule) if rule != "reference" else _solve_lp_batch(A, b, c)
+        kw = {}
+        if rule != "reference":
+            kw["rule"] = rule
+        if max_pivots is not None:
+            kw["max_pivots"] = max_pivots
+        status, x = _solve_lp_batch(A, b, c, **kw)
+        bad = _verify_lp_batch(A, b, x, status) if verify else None
         for k, i in enumerate(idxs):
             st = int(status[k])
-            if st in (-1, 0, 1):
+            if bad is not None and st == 0 and int(bad[k]) >= 0:
+                out[i] = "AssertionError\n"   # simplex.py:745 -> :671
+            elif st in (-1, 0, 1):
                 out[i] = format_answer(st, [float(v) for v in x[k]])
             else:
                 out[i] = _CRASH_NAMES.get(st, "Status%d" % st) + "\n"
@@ -149,10 +172,13 @@ def main(argv=None) -> int:
     argv = list(sys.argv[1:] if argv is None else argv)
     stream = "--stream" in argv
     rule = "reference"
+    max_pivots = None
     for t in argv:
         if t.startswith("--rule="):
             rule = t.split("=", 1)[1]
-    argv = [t for t in argv if t != "--stream" and not t.startswith("--rule=")]
+        if t.startswith("--max-pivots="):
+            max_pivots = int(t.split("=", 1)[1])
+    argv = [t for t in argv if t != "--stream" and not t.startswith("--rule=") and not t.startswith("--max-pivots=")]
     prog = argv[0] if argv else "simplex"
     if prog not in ("simplex", "ad_allocation", "diet", "energy_values"):
         sys.stderr.write("unknown program %r\n" % prog)
@@ -162,17 +188,23 @@ def main(argv=None) -> int:
         if prog == "energy_values":
             sys.stdout.write(solve_equation_stream(text))
         else:
-            sys.stdout.write(solve_lp_stream(text, integer=(prog == "simplex"), rule=rule))
+            sys.stdout.write(solve_lp_stream(text, integer=(prog == "simplex"), rule=rule, max_pivots=max_pivots,
+                                             verify=(prog == "simplex")))
         return 0
     if prog == "simplex":
         s = Simplex.parse(sys.stdin)
         s.rule = rule
+        s.max_pivots = max_pivots
         anst, ansx = s.solve()
         sys.stdout.write(format_answer(anst, ansx))
+        if anst == 0:  # simplex.py:745: the reference asserts its own answer after printing it
+            sys.stdout.flush()
+            s.verify_bounds()
     elif prog in ("ad_allocation", "diet"):
         n, m, A, b, c = parse_lp_floats(sys.stdin.read())
         s = Simplex(A, b, c, n, m)
         s.rule = rule
+        s.max_pivots = max_pivots
         anst, ansx = s.solve()
         sys.stdout.write(format_answer(anst, ansx))
     else:

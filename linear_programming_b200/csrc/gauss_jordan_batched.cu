@@ -107,7 +107,8 @@ __device__ __forceinline__ void gj_factor_rows(double *P, int n, int k, int tid)
 // 128 registers, two per SM.  Same operations per element in the same order: bit-identical.
 template <bool kPartial, int kGjThreads, bool kPairs = false>
 __global__ void __launch_bounds__(kGjThreads, (kPairs ? 2 : (kGjThreads == kGjMaxThreads ? LPB_GJ_MINB : 1024 / kGjThreads)))
-gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restrict__ x_all)
+gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restrict__ x_all,
+                            int32_t *__restrict__ status_all)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     double *P = reinterpret_cast<double *>(smem);                 // [n][kGjPS]
@@ -119,6 +120,9 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
     const int tid = threadIdx.x;
     double *a = a_all + (size_t)blockIdx.x * n * n;
     double *bx = x_all + (size_t)blockIdx.x * n;
+    // first step whose pivot column holds no non-zero at or below the diagonal (the reference then divides by
+    // zero and returns inf/nan, energy_values.cc:100-110 finds no row to swap with); -1: every pivot was non-zero
+    int first_singular = -1;
 
 #ifdef LPB_GJ_TIMING
     long long tacc[5] = {0, 0, 0, 0, 0}, tlast = clock64();
@@ -139,7 +143,10 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
             if (a[(size_t)k0 * n + k0] == 0.0) {
                 sw = k0;
                 while (sw < n && a[(size_t)sw * n + k0] == 0.0) ++sw;
-                if (sw >= n) sw = -1;  // the reference carries on and divides by zero
+                if (sw >= n) {  // the reference carries on and divides by zero
+                    sw = -1;
+                    if (first_singular < 0) first_singular = k0;
+                }
             }
             flag[0] = sw;
         }
@@ -206,7 +213,14 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
                         }
                     }
                 }
-                if (tid == 0) perm[q] = r;
+                if (tid == 0) {
+                    perm[q] = r;
+                    if (first_singular < 0) {
+                        unsigned long long bk = wkey[0];
+                        for (int w = 1; w < kGjThreads / 32; ++w) bk = wkey[w] > bk ? wkey[w] : bk;
+                        if (bk == 0ull) first_singular = k;  // the whole column is zero: no pivot exists
+                    }
+                }
                 if (r != k && tid < K) {  // the whole panel row moves, earlier scales included
                     const double t = P[(size_t)k * kGjPS + tid];
                     P[(size_t)k * kGjPS + tid] = P[(size_t)r * kGjPS + tid];
@@ -457,6 +471,7 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
         LPB_GJ_T(4);
         k0 += Kp;
     }
+    if (tid == 0 && status_all != nullptr) status_all[blockIdx.x] = first_singular;
 #ifdef LPB_GJ_TIMING
     if (tid == 0 && (blockIdx.x == 0 || blockIdx.x == 300))
         printf("gj timing cta %d: select+load %lld  factor %lld  pass1 %lld  pass2 %lld  pass3 %lld cycles\n", blockIdx.x,
@@ -471,7 +486,8 @@ using namespace lpb;
 
 static inline int gj_smem_bytes(int n) { return n * kGjPS * 8 + 288; }  // panel + flag, perm, argmax slots
 
-static int gj_launch(int B, int n, double *wa, double *x, int pivoting, const DeviceInfo &di, cudaStream_t stream)
+static int gj_launch(int B, int n, double *wa, double *x, int pivoting, int32_t *status, const DeviceInfo &di,
+                     cudaStream_t stream)
 {
     const int smem = gj_smem_bytes(n);
     if (smem > di.max_smem_optin) {
@@ -485,7 +501,7 @@ static int gj_launch(int B, int n, double *wa, double *x, int pivoting, const De
     do {                                                                                                             \
         LPB_CUDA(cudaFuncSetAttribute(gauss_jordan_batched_kernel<PP, T, ##__VA_ARGS__>,                             \
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));                           \
-        gauss_jordan_batched_kernel<PP, T, ##__VA_ARGS__><<<B, T, smem, stream>>>(n, wa, x);                        \
+        gauss_jordan_batched_kernel<PP, T, ##__VA_ARGS__><<<B, T, smem, stream>>>(n, wa, x, status);                \
     } while (0)
     const bool pp = (pivoting == LPB200_PIVOT_PARTIAL);
     int threads = n <= 64 ? 64 : (n <= 128 ? 128 : (n <= 256 ? 256 : kGjMaxThreads));  // measured: tools/gpu/gj_small_rates.py
@@ -534,6 +550,14 @@ extern "C" int lpb200_gauss_jordan_batch_ex_device(int B, int n, const double *a
                                                    int pivoting, void *workspace, int64_t workspace_bytes,
                                                    void *stream_v)
 {
+    return lpb200_gauss_jordan_batch_status_device(B, n, a, b, x, pivoting, nullptr, workspace, workspace_bytes,
+                                                   stream_v);
+}
+
+extern "C" int lpb200_gauss_jordan_batch_status_device(int B, int n, const double *a, const double *b, double *x,
+                                                       int pivoting, int32_t *status, void *workspace,
+                                                       int64_t workspace_bytes, void *stream_v)
+{
     int rc = gj_check(B, n, pivoting);
     if (rc) return rc;
     if (B == 0 || n == 0) return 0;  // size 0 prints nothing (week-2/energy_values/tests/01)
@@ -548,7 +572,7 @@ extern "C" int lpb200_gauss_jordan_batch_ex_device(int B, int n, const double *a
     double *wa = static_cast<double *>(workspace);
     LPB_CUDA(cudaMemcpyAsync(wa, a, (size_t)B * n * n * 8, cudaMemcpyDeviceToDevice, stream));
     if (x != b) LPB_CUDA(cudaMemcpyAsync(x, b, (size_t)B * n * 8, cudaMemcpyDeviceToDevice, stream));
-    return gj_launch(B, n, wa, x, pivoting, di, stream);
+    return gj_launch(B, n, wa, x, pivoting, status, di, stream);
 }
 
 extern "C" int lpb200_gauss_jordan_batch_device(int B, int n, const double *a, const double *b, double *x,
@@ -561,6 +585,12 @@ extern "C" int lpb200_gauss_jordan_batch_device(int B, int n, const double *a, c
 extern "C" int lpb200_gauss_jordan_batch_ex(int B, int n, const double *a, const double *b, double *x,
                                             int pivoting)
 {
+    return lpb200_gauss_jordan_batch_status(B, n, a, b, x, pivoting, nullptr);
+}
+
+extern "C" int lpb200_gauss_jordan_batch_status(int B, int n, const double *a, const double *b, double *x,
+                                                int pivoting, int32_t *status)
+{
     int rc = gj_check(B, n, pivoting);
     if (rc) return rc;
     if (B == 0 || n == 0) return 0;
@@ -568,18 +598,24 @@ extern "C" int lpb200_gauss_jordan_batch_ex(int B, int n, const double *a, const
     rc = get_device_info(&di);
     if (rc) return rc;
     double *da = nullptr, *dx = nullptr;
+    int32_t *dst = nullptr;
     const size_t na = (size_t)B * n * n * 8, nx = (size_t)B * n * 8;
     cudaError_t e;
+    if (status != nullptr && (e = cudaMalloc((void **)&dst, (size_t)B * 4)) != cudaSuccess)
+        return cuda_fail(e, "cudaMalloc(status)");
     // the host copy of `a` lands directly in the working buffer: no device-to-device copy
-    if ((e = cudaMalloc((void **)&da, na)) != cudaSuccess) return cuda_fail(e, "cudaMalloc(a)");
-    if ((e = cudaMalloc((void **)&dx, nx)) != cudaSuccess) { cudaFree(da); return cuda_fail(e, "cudaMalloc(x)"); }
+    if ((e = cudaMalloc((void **)&da, na)) != cudaSuccess) { cudaFree(dst); return cuda_fail(e, "cudaMalloc(a)"); }
+    if ((e = cudaMalloc((void **)&dx, nx)) != cudaSuccess) { cudaFree(da); cudaFree(dst); return cuda_fail(e, "cudaMalloc(x)"); }
     rc = 0;
     if ((e = cudaMemcpy(da, a, na, cudaMemcpyHostToDevice)) != cudaSuccess) rc = cuda_fail(e, "cudaMemcpy(a)");
     if (!rc && (e = cudaMemcpy(dx, b, nx, cudaMemcpyHostToDevice)) != cudaSuccess) rc = cuda_fail(e, "cudaMemcpy(b)");
-    if (!rc) rc = gj_launch(B, n, da, dx, pivoting, di, 0);
+    if (!rc) rc = gj_launch(B, n, da, dx, pivoting, dst, di, 0);
     if (!rc && (e = cudaMemcpy(x, dx, nx, cudaMemcpyDeviceToHost)) != cudaSuccess) rc = cuda_fail(e, "cudaMemcpy(x)");
+    if (!rc && dst && (e = cudaMemcpy(status, dst, (size_t)B * 4, cudaMemcpyDeviceToHost)) != cudaSuccess)
+        rc = cuda_fail(e, "cudaMemcpy(status)");
     cudaFree(da);
     cudaFree(dx);
+    cudaFree(dst);
     return rc;
 }
 

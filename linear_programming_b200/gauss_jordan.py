@@ -23,12 +23,14 @@ PIVOT_REFERENCE, PIVOT_PARTIAL = 0, 1
 _PIVOTING = {"reference": PIVOT_REFERENCE, "partial": PIVOT_PARTIAL}
 
 
-def solve_equation_batch(a, b, pivoting: str = "reference"):
+def solve_equation_batch(a, b, pivoting: str = "reference", return_status: bool = False):
     """a[B,n,n], b[B,n] -> x[B,n].  numpy in -> numpy out (host path); CUDA float64 torch
     tensors in -> CUDA tensor out (zero-copy, current stream).  Inputs are not modified.
     pivoting: "reference" = the reference's rule (diagonal pivot, swap on an exact zero only,
     energy_values.cc:85-114); "partial" = largest |a[i][k]| in the column (not reference
-    behaviour; for ill-conditioned systems)."""
+    behaviour; for ill-conditioned systems).
+    return_status=True returns (x, status): status[B] int32 is -1 when every step found a non-zero pivot, else
+    the first step at which none existed (the reference then divides by zero: that system's x is inf/nan)."""
     if pivoting not in _PIVOTING:
         raise ValueError("pivoting must be 'reference' or 'partial'")
     pv = _PIVOTING[pivoting]
@@ -46,18 +48,22 @@ def solve_equation_batch(a, b, pivoting: str = "reference"):
             wsb = int(L.lpb200_gauss_jordan_workspace_bytes(B, n))
             ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=a.device)
             stream = torch.cuda.current_stream(a.device).cuda_stream
-            _lib.check(L.lpb200_gauss_jordan_batch_ex_device(B, n, a.data_ptr(), b.data_ptr(), x.data_ptr(), pv,
-                                                             ws.data_ptr(), wsb, stream))
-        return x
+            status = torch.empty(B, dtype=torch.int32, device=a.device) if return_status else None
+            _lib.check(L.lpb200_gauss_jordan_batch_status_device(
+                B, n, a.data_ptr(), b.data_ptr(), x.data_ptr(), pv, status.data_ptr() if return_status else None,
+                ws.data_ptr(), wsb, stream))
+        return (x, status) if return_status else x
     a = np.ascontiguousarray(a, dtype=np.float64)
     b = np.ascontiguousarray(b, dtype=np.float64)
     if a.ndim != 3 or b.ndim != 2 or a.shape[1] != a.shape[2] or b.shape != a.shape[:2]:
         raise ValueError("expected a[B,n,n], b[B,n]")
     B, n = b.shape
     x = np.zeros((B, n), dtype=np.float64)
-    _lib.check(L.lpb200_gauss_jordan_batch_ex(B, n, ctypes.c_void_p(a.ctypes.data), ctypes.c_void_p(b.ctypes.data),
-                                              ctypes.c_void_p(x.ctypes.data), pv))
-    return x
+    status = np.full(B, -1, dtype=np.int32)
+    _lib.check(L.lpb200_gauss_jordan_batch_status(B, n, ctypes.c_void_p(a.ctypes.data), ctypes.c_void_p(b.ctypes.data),
+                                                  ctypes.c_void_p(x.ctypes.data), pv,
+                                                  ctypes.c_void_p(status.ctypes.data) if return_status else None))
+    return (x, status) if return_status else x
 
 
 def solve_equation(a, b, pivoting: str = "reference"):

@@ -10,12 +10,24 @@ import numpy as np
 import pytest
 
 
-def _expected_stdout(case):
+def _assertion_fires(case):
+    """Would the reference's own post-condition (simplex.py:745 -> verify_bounds :663-671) kill the process?"""
+    import oracle
+    if case["status"] != 0:
+        return False
+    A = np.array(case["A"], dtype=np.float64).reshape(case["n"], case["m"])
+    x = np.array([float.fromhex(h) for h in case["x"]])
+    return oracle.verify_bounds(A, np.array(case["b"], dtype=np.float64), x) >= 0
+
+
+def _expected_stdout(case, verify=False):
     from linear_programming_b200.cli import format_answer
     names = {3: "AttributeError\n", 4: "IndexError\n", 5: "TypeError\n"}
     st = case["status"]
     if st in names:
         return names[st]
+    if verify and _assertion_fires(case):
+        return "AssertionError\n"
     x = [float.fromhex(h) for h in case["x"]] if case["x"] is not None else None
     return format_answer(st, x)
 
@@ -70,8 +82,8 @@ def test_stream_cli_on_gpu_matches_reference_answers(monkeypatch, capsys, simple
     cases = _fixture_cases(simplex_golden)
     monkeypatch.setattr(sys, "stdin", io.StringIO("\n".join(c["stdin"] for c in cases)))
     assert cli.main(["simplex", "--stream"]) == 0
-    assert capsys.readouterr().out == "".join(_expected_stdout(c) for c in cases)
-    # the same stream through the C++-stub reader (doubles)
+    assert capsys.readouterr().out == "".join(_expected_stdout(c, verify=True) for c in cases)
+    # the same stream through the C++-stub reader (doubles; the stubs' main() asserts nothing)
     monkeypatch.setattr(sys, "stdin", io.StringIO("\n".join(c["stdin"] for c in cases)))
     assert cli.main(["ad_allocation", "--stream"]) == 0
     assert capsys.readouterr().out == "".join(_expected_stdout(c) for c in cases)
@@ -89,7 +101,11 @@ def test_single_problem_cli_is_byte_compatible(monkeypatch, capsys, simplex_gold
         if case["status"] not in (-1, 0, 1):
             continue
         monkeypatch.setattr(sys, "stdin", io.StringIO(case["stdin"]))
-        assert cli.main(["simplex"]) == 0
+        if _assertion_fires(case):  # the answer is printed, then the process dies like the reference's (:745)
+            with pytest.raises(AssertionError):
+                cli.main(["simplex"])
+        else:
+            assert cli.main(["simplex"]) == 0
         assert capsys.readouterr().out == _expected_stdout(case)
 
 
@@ -104,6 +120,7 @@ def test_rule_flag_reaches_the_batch_call(monkeypatch, oracle_lib):
         st, x, _, _, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=100000, rule=rule)
         return st, x
     monkeypatch.setattr(cli, "_solve_lp_batch", checker)
+    monkeypatch.setattr(cli, "_verify_lp_batch", lambda A, b, x, status: np.full(len(status), -1, dtype=np.int32))
     text = "2 2\n1 1\n1 -1\n0 0\n1 1\n"          # b == 0: the reference raises (simplex.py:626)
     assert cli.solve_lp_stream(text, integer=True) == "AttributeError\n"
     out = cli.solve_lp_stream(text, integer=True, rule="bland")
@@ -115,3 +132,56 @@ def test_rule_flag_reaches_the_batch_call(monkeypatch, oracle_lib):
     monkeypatch.setattr(sys, "stdout", buf)
     assert cli.main(["simplex", "--stream", "--rule=dantzig"]) == 0
     assert buf.getvalue() == out
+
+
+def _text_of(A, b, c):
+    n, m = A.shape
+    rows = ["%d %d" % (n, m)] + [" ".join(str(int(v)) for v in r) for r in A]
+    return "\n".join(rows + [" ".join(str(int(v)) for v in b), " ".join(str(int(v)) for v in c)]) + "\n"
+
+
+def test_stream_runs_the_reference_post_condition_and_max_pivots_reaches_the_engine(monkeypatch, oracle_lib):
+    """(1) the reference's __main__ asserts verify_bounds after every "Bounded solution"
+    (simplex.py:745 -> :663-671) -- on answers its buggy ratio test gets wrong the process dies with AssertionError;
+    the `simplex` shim does the same, and in --stream mode prints "AssertionError" for that problem.
+    (2) --max-pivots=N reaches the batch call (the reference has no cap; the engine's default is documented)."""
+    from linear_programming_b200 import cli, workloads
+    seen = {}
+
+    def checker(A, b, c, rule="reference", max_pivots=None):
+        seen["max_pivots"] = max_pivots
+        st, x, _, _, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=max_pivots or 100000, rule=rule)
+        return st, x
+
+    def verifier(A, b, x, status):
+        return np.array([oracle_lib.verify_bounds(A[i], b[i], x[i]) if int(status[i]) == 0 else -1
+                         for i in range(len(status))], dtype=np.int32)
+    monkeypatch.setattr(cli, "_solve_lp_batch", checker)
+    monkeypatch.setattr(cli, "_verify_lp_batch", verifier)
+    # find, in the stress.py distribution, answers on which the reference's own assertion fires (SURVEY A.8)
+    bad, good = None, None
+    for A, b, c in workloads.stress_batch(4000, seed=3):
+        r = oracle_lib.simplex(A, b, c, max_pivots=10000)
+        if r["status"] != 0:
+            continue
+        if oracle_lib.verify_bounds(A, b, r["x"]) >= 0:
+            bad = bad or (A, b, c)
+        else:
+            good = good or (A, b, c, r["x"])
+        if bad and good:
+            break
+    assert bad is not None and good is not None
+    text = _text_of(*bad) + _text_of(*good[:3])
+    out = cli.solve_lp_stream(text, integer=True, verify=True)
+    assert out == "AssertionError\n" + cli.format_answer(0, [float(v) for v in good[3]])
+    assert cli.solve_lp_stream(text, integer=True).startswith("Bounded solution\n")   # the C++ stubs assert nothing
+    # --max-pivots through main()
+    monkeypatch.setattr(sys, "stdin", io.StringIO(_text_of(*good[:3])))
+    buf = io.StringIO()
+    monkeypatch.setattr(sys, "stdout", buf)
+    assert cli.main(["simplex", "--stream", "--max-pivots=777"]) == 0
+    assert seen["max_pivots"] == 777
+    monkeypatch.setattr(sys, "stdin", io.StringIO(_text_of(*good[:3])))
+    monkeypatch.setattr(sys, "stdout", io.StringIO())
+    assert cli.main(["simplex", "--stream", "--max-pivots=1"]) == 0 and seen["max_pivots"] == 1
+    assert sys.stdout.getvalue() in ("IterationLimit\n", buf.getvalue())

@@ -114,3 +114,30 @@ def test_column_pair_variant_vs_oracle(oracle_lib, monkeypatch, pairs, n, count,
     x = lp.solve_equation_batch(a, b, pivoting=pivoting)
     want, _ = oracle_lib.gauss_jordan_batch(a, b, full_sweep=False, pivoting=pivoting)
     assert np.array_equal(x.view(np.int64), want.view(np.int64))
+
+
+@pytest.mark.parametrize("n", [6, 20, 100, 300, 512])
+@pytest.mark.parametrize("pivoting", ["reference", "partial"])
+def test_per_system_status_finds_the_singular_systems(oracle_lib, n, pivoting):
+    """lpb200_gauss_jordan_batch_status: -1 for a system whose every step found a pivot, else the first step whose
+    column holds no non-zero at or below the diagonal -- where the reference's SelectPivotElement finds nothing
+    to swap with (energy_values.cc:100-110) and SolveEquation goes on to divide by zero."""
+    import linear_programming_b200 as lp
+    count = 9
+    a, b = workloads.gauss_jordan_batch(count, n=n, seed=5, swap_frac=0.4)
+    want_status = np.full(count, -1, dtype=np.int32)
+    for s, k in ((1, 0), (4, n // 2), (7, n - 1)):
+        a[s, :, k] = 0.0  # column k is zero and stays zero under every earlier step: step k has no pivot
+        want_status[s] = k
+    x, status = lp.solve_equation_batch(a, b, pivoting=pivoting, return_status=True)
+    assert np.array_equal(status, want_status)
+    good = want_status < 0
+    want, _ = oracle_lib.gauss_jordan_batch(a[good], b[good], pivoting=pivoting)
+    assert np.array_equal(x[good].view(np.int64), want.view(np.int64))
+    assert all((~np.isfinite(x[s])).any() for s in np.nonzero(~good)[0])
+    # the device entry point reports the same
+    import torch
+    xd, sd = lp.solve_equation_batch(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda(), pivoting=pivoting,
+                                     return_status=True)
+    assert np.array_equal(sd.cpu().numpy(), want_status)
+    assert np.array_equal(xd.cpu().numpy()[good].view(np.int64), want.view(np.int64))
