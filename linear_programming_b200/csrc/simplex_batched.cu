@@ -37,8 +37,10 @@
 #include <stdlib.h>
 
 #include <atomic>
+#include <chrono>
 #include <string>
 #include <thread>
+#include <vector>
 
 #include "lp_common.cuh"
 #include "lp_host.h"
@@ -279,6 +281,21 @@ struct HostArena {
 static thread_local HostArena g_arena;
 static thread_local long long g_last_lanes[4] = {0, 0, 0, 0};
 
+// Whether the host-narrowing lane pays is MEASURED per calling thread, not guessed from the pool size: ranks that
+// share one host compete for its memory bandwidth, and then the cores' reads only take bandwidth from the copy
+// engines (round 1: 8 GPUs x 4 threads lost 9 %, 4 GPUs x 8 threads were never measured and regressed).  A probe call
+// lets the copy-engine lane run alone for its first kProbeChunks chunks and only then starts the narrowing lane:
+//   r1 = chunk rate of the copy engine alone,   r2 = aggregate chunk rate of both lanes afterwards;
+// the second lane is kept while r2 > 1.05 * r1.  The verdict holds for the thread's next kGateEvery large calls, then
+// one call probes again.  LPB_HOST_NARROW=0 / 1 forces the lane off / on (no probe); LPB_DEBUG_GATE=1 prints the rates.
+constexpr int kProbeChunks = 4, kGateEvery = 64;
+struct LaneGate {
+    int verdict = 0;  // 0: not measured yet, +1: both lanes, -1: copy engine only
+    int age = 0;      // large calls since the last probe
+    double r1 = 0.0, r2 = 0.0;
+};
+static thread_local LaneGate g_gate;
+
 // Host-pointer entry point: the batch is cut into chunks that are copied in, solved and
 // copied out on two alternating streams, so the PCIe copy of chunk k+1 overlaps the solve of
 // chunk k and device memory stays bounded (two chunk-sized buffer sets).
@@ -340,18 +357,18 @@ extern "C" int lpb200_simplex_batch_ex(int B, int n, int m, const void *A_v, int
     if (chunk < 1) chunk = 1;
     if (chunk > B) chunk = B;
     const int nset = (chunk < B) ? 2 : 1;
-    // second lane: fp64 A, enough chunks to share, more than the calling thread to narrow with
-    bool two_lanes = (a_dtype == LPB200_DTYPE_F64) && (B + chunk - 1) / chunk >= 8;
+    // second lane: fp64 A, enough chunks to share; whether it pays is measured (LaneGate above)
+    bool two_lanes = (a_dtype == LPB200_DTYPE_F64) && (B + chunk - 1) / chunk >= 8 && HostPool::instance().threads() >= 2;
+    bool probe = false;
     if (two_lanes) {
-        // LPB_HOST_NARROW: 0 = off, 1 = on, unset = on when this process has at least kMinNarrowThreads pool
-        // threads.  Measured on the 8-GPU box (32 cores shared by 8 ranks, 4 pool threads each): the cores'
-        // reads starve the eight copy engines of host memory bandwidth -- 2.04 M LPs/s with the second lane
-        // against 2.23 M without; with 12 threads per rank (2 GPUs) 1.89 M against 1.33 M, with 16 (1 GPU)
-        // 1.31 M against 0.67 M.
-        constexpr int kMinNarrowThreads = 10;
         const char *e = getenv("LPB_HOST_NARROW");
-        if (e && e[0] == '0') two_lanes = false;
-        else if (!(e && e[0] == '1') && HostPool::instance().threads() < kMinNarrowThreads) two_lanes = false;
+        if (e && e[0] == '0') {
+            two_lanes = false;
+        } else if (!(e && e[0] == '1')) {
+            if (g_gate.verdict == 0 || g_gate.age >= kGateEvery) probe = true;
+            else if (g_gate.verdict < 0) two_lanes = false;
+            ++g_gate.age;
+        }
     }
     const int nsets_used = two_lanes ? kMaxSets : nset;
     struct Set {
@@ -421,6 +438,11 @@ extern "C" int lpb200_simplex_batch_ex(int B, int n, int m, const void *A_v, int
     HostArena *const arena = &g_arena;  // thread_local: the copier thread must use the CALLER's arena
     std::atomic<long long> next_chunk{0};
     const long long nchunks = (B + chunk - 1) / chunk;
+    // probe bookkeeping (LaneGate): when the copy-engine lane saw each of its chunks leave the GPU
+    std::atomic<int> copy_done{0};
+    std::atomic<bool> copy_finished{false};
+    std::vector<std::chrono::steady_clock::time_point> copy_times;
+    if (probe) copy_times.reserve((size_t)nchunks);
     auto run_lane = [&](int lane, bool narrow, bool backpressure, LaneResult *out) {
         int rc = 0;
 #define LPB_TRY(call)                                                 \
@@ -440,6 +462,10 @@ extern "C" int lpb200_simplex_batch_ex(int B, int n, int m, const void *A_v, int
             // the set's previous chunk has left the GPU: bounds the lane to two chunks in flight (so the other
             // lane gets its share of the counter) and frees the set's pinned staging buffer
             if (backpressure) LPB_TRY(cudaEventSynchronize(arena->done[si]));
+            if (probe && lane == 0 && k > kCopySets) {  // the chunk this set carried two rounds ago has left the GPU
+                copy_times.push_back(std::chrono::steady_clock::now());
+                copy_done.fetch_add(1, std::memory_order_release);
+            }
             int dtype = a_dtype;
             const char *srcA = A + lo * lpA * esz;
             size_t bytesA = (size_t)cnt * lpA * esz;
@@ -474,15 +500,50 @@ extern "C" int lpb200_simplex_batch_ex(int B, int n, int m, const void *A_v, int
             ++out->chunks;
             out->a_bytes += (long long)bytesA;
         }
+        if (probe && lane == 0) {
+            for (int s = 0; s < kCopySets && rc == 0; ++s) {  // the last chunks in flight
+                if (k > s) {
+                    LPB_TRY(cudaEventSynchronize(arena->done[(k - 1 - s) % kCopySets]));
+                    copy_times.push_back(std::chrono::steady_clock::now());
+                }
+            }
+            copy_finished.store(true, std::memory_order_release);
+        }
 #undef LPB_TRY
         out->rc = rc;
         if (rc) out->error = lpb200_last_error();
     };
     LaneResult lane_res[2];
     if (two_lanes) {
+        using clk = std::chrono::steady_clock;
         std::thread copier(run_lane, 0, false, true, &lane_res[0]);  // the copy-engine lane only enqueues and waits
+        clk::time_point t_narrow = clk::now();
+        if (probe) {  // the copy engine alone for its first chunks: that is the rate the second lane has to beat
+            while (copy_done.load(std::memory_order_acquire) < kProbeChunks && !copy_finished.load(std::memory_order_acquire))
+                std::this_thread::sleep_for(std::chrono::microseconds(50));
+            t_narrow = clk::now();
+        }
         run_lane(1, true, true, &lane_res[1]);                       // the caller drives the host pool
         copier.join();
+        if (probe && rc == 0) {
+            for (int s = 0; s < nsets_used; ++s)
+                if (set[s].stream) cudaStreamSynchronize(set[s].stream);
+            const clk::time_point t_end = clk::now();
+            // completions of the copy lane before the narrowing lane started
+            size_t k1 = 0;
+            while (k1 < copy_times.size() && copy_times[k1] <= t_narrow) ++k1;
+            if (k1 >= 3 && nchunks > (long long)k1 + 4) {
+                const double d1 = std::chrono::duration<double>(copy_times[k1 - 1] - copy_times[0]).count();
+                const double d2 = std::chrono::duration<double>(t_end - copy_times[k1 - 1]).count();
+                g_gate.r1 = d1 > 0 ? (double)(k1 - 1) / d1 : 0.0;
+                g_gate.r2 = d2 > 0 ? (double)(nchunks - (long long)k1) / d2 : 0.0;
+                g_gate.verdict = (g_gate.r2 > 1.05 * g_gate.r1) ? 1 : -1;
+                g_gate.age = 0;
+                if (getenv("LPB_DEBUG_GATE"))
+                    fprintf(stderr, "[lpb gate] copy engine alone %.1f chunks/s, both lanes %.1f chunks/s -> narrowing lane %s\n",
+                            g_gate.r1, g_gate.r2, g_gate.verdict > 0 ? "on" : "off");
+            }
+        }
     } else {
         run_lane(0, false, false, &lane_res[0]);
     }

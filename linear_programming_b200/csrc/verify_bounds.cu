@@ -10,6 +10,7 @@
 // LPs whose status is not LPB200_STATUS_BOUNDED have no x and are skipped (-1).
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "lp_common.cuh"
 #include "lp_host.h"
@@ -103,6 +104,165 @@ verify_bounds_kernel(int B, int n, int m, const double *__restrict__ A, const do
     }
 }
 
+
+// ---- pipelined variant (n <= 256): the default for course / Config-4 shapes ----
+// One thread per constraint keeps its running sum in a register while A streams through shared memory in
+// BLOCKS OF 32 COLUMNS (n x 32 doubles, double-buffered, filled with cp.async straight from global memory): the
+// next block -- of this LP or of the CTA's next one -- is in flight while the current one is summed, so a CTA never
+// alternates between a load phase and a latency-bound summing phase, and at 2 x 26 KB per CTA four CTAs share an SM
+// (the staged kernel above holds a whole LP, 81 KB, two CTAs per SM: 0.48 of the HBM peak).  The chain of additions
+// of a row is walked strictly left to right, product and sum rounded separately: the reference's bits.
+// kVec16 (m even, 16-byte aligned inputs): 16-byte cp.async.cg (L2 only: with 218 KB of the SM's 256 KB carved out as
+// shared memory the L1 left over is too small to stream through), rows 32 doubles apart with the 16-byte granules of
+// row r XOR-swizzled by r & 15, so that both the copies and the one-row-per-thread 128-bit reads are conflict-free.
+// Otherwise 8-byte cp.async.ca into rows 33 doubles apart.
+constexpr int kVpThreads = 256;
+constexpr int kVpCols = 32;  // columns per block
+
+__device__ __forceinline__ void cp_async8(void *dst_smem, const void *src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async16(void *dst_smem, const void *src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory"); }
+
+template <bool kVec16>
+__global__ void __launch_bounds__(kVpThreads)
+verify_bounds_pipelined_kernel(int B, int n, int m, const double *__restrict__ A, const double *__restrict__ b,
+                               const double *__restrict__ x, const int32_t *__restrict__ status, double tolerance,
+                               int32_t *__restrict__ first_bad)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    constexpr int kStride = kVec16 ? kVpCols : kVpCols + 1;  // doubles per buffered row
+    const int tid = threadIdx.x;
+    const int mpad = (m + 1) & ~1;
+    double *xs = reinterpret_cast<double *>(smem);  // [2][mpad]: x of the LP being summed / of the next one
+    double *buf = xs + 2 * mpad;                     // [2][n][kStride]
+    __shared__ int bad;
+    const int nblk = (m + kVpCols - 1) / kVpCols;
+    const size_t bufsz = (size_t)n * kStride;
+
+    // the CTA's stream of work units: (LP, column block), LPs blockIdx.x, blockIdx.x + gridDim.x, ...; an LP without
+    // an answer (status != bounded) reports -1 and is skipped when the stream is built
+    auto next_lp = [&](int lp) {
+        lp += (int)gridDim.x;
+        while (lp < B && status != nullptr && status[lp] != LPB200_STATUS_BOUNDED) {
+            if (tid == 0) first_bad[lp] = -1;
+            lp += (int)gridDim.x;
+        }
+        return lp;
+    };
+    // block k of LP lp -> buf[slot]; with block 0 also the LP's x -> xs[xslot]; one cp.async group
+    auto issue = [&](int lp, int k, int slot, int xslot) {
+        const int j0 = k * kVpCols;
+        const int cb = min(kVpCols, m - j0);
+        const double *src = A + (size_t)lp * n * m + j0;
+        double *dst = buf + (size_t)slot * bufsz;
+        if (kVec16) {
+            const int ng = (cb + 1) >> 1;  // 16-byte granules per row (cb is even: m is)
+            if (ng == 16) {
+                for (int e = tid; e < n * 16; e += kVpThreads) {
+                    const int r = e >> 4, g = e & 15;
+                    cp_async16(dst + (size_t)r * kStride + ((g ^ (r & 15)) << 1), src + (size_t)r * m + 2 * g);
+                }
+            } else {
+                for (int e = tid; e < n * ng; e += kVpThreads) {
+                    const int r = e / ng, g = e - r * ng;
+                    cp_async16(dst + (size_t)r * kStride + ((g ^ (r & 15)) << 1), src + (size_t)r * m + 2 * g);
+                }
+            }
+            if (k == 0)
+                for (int g = tid; g < (m >> 1); g += kVpThreads)
+                    cp_async16(xs + (size_t)xslot * mpad + 2 * g, x + (size_t)lp * m + 2 * g);
+        } else {
+            for (int e = tid; e < n * cb; e += kVpThreads) {
+                const int r = e / cb, j = e - r * cb;
+                cp_async8(dst + (size_t)r * kStride + j, src + (size_t)r * m + j);
+            }
+            if (k == 0)
+                for (int j = tid; j < m; j += kVpThreads) cp_async8(xs + (size_t)xslot * mpad + j, x + (size_t)lp * m + j);
+        }
+        cp_async_commit();
+    };
+
+    int lp = next_lp((int)blockIdx.x - (int)gridDim.x);
+    if (lp >= B) return;
+    int slot = 0, xpar = 0;
+    issue(lp, 0, 0, 0);
+    while (lp < B) {
+        const int lp_next = next_lp(lp);
+        double sum = 0.0;  // int 0 + float in the reference: the same value
+        if (tid == 0) bad = 0x7fffffff;
+        for (int k = 0; k < nblk; ++k) {
+            // put the following unit in flight, then wait for this one
+            bool more = true;
+            if (k + 1 < nblk) issue(lp, k + 1, slot ^ 1, xpar);
+            else if (lp_next < B) issue(lp_next, 0, slot ^ 1, xpar ^ 1);
+            else more = false;
+            if (more) cp_async_wait<1>(); else cp_async_wait<0>();
+            __syncthreads();
+            if (tid < n) {
+                const int j0 = k * kVpCols;
+                const int cb = min(kVpCols, m - j0);
+                const double *row = buf + (size_t)slot * bufsz + (size_t)tid * kStride;
+                const double *xv = xs + (size_t)xpar * mpad + j0;
+                if (kVec16) {
+                    const double2 *row2 = reinterpret_cast<const double2 *>(row);
+                    const double2 *xv2 = reinterpret_cast<const double2 *>(xv);
+                    const int sw = tid & 15;
+                    int g = 0;
+                    for (; g + 4 <= (cb >> 1); g += 4) {  // eight products ahead of the (inherently serial) additions
+                        double pr[8];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const double2 a2 = row2[(g + q) ^ sw];
+                            const double2 x2 = xv2[g + q];
+                            pr[2 * q] = __dmul_rn(a2.x, x2.x);
+                            pr[2 * q + 1] = __dmul_rn(a2.y, x2.y);
+                        }
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) sum = __dadd_rn(sum, pr[q]);
+                    }
+                    for (; g < (cb >> 1); ++g) {
+                        const double2 a2 = row2[g ^ sw];
+                        const double2 x2 = xv2[g];
+                        sum = __dadd_rn(sum, __dmul_rn(a2.x, x2.x));
+                        sum = __dadd_rn(sum, __dmul_rn(a2.y, x2.y));
+                    }
+                } else {
+                    int i = 0;
+                    for (; i + 8 <= cb; i += 8) {
+                        double pr[8];
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) pr[q] = __dmul_rn(row[i + q], xv[i + q]);
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) sum = __dadd_rn(sum, pr[q]);
+                    }
+                    for (; i < cb; ++i) sum = __dadd_rn(sum, __dmul_rn(row[i], xv[i]));
+                }
+            }
+            __syncthreads();  // buf[slot] is refilled two units from now
+            slot ^= 1;
+        }
+        int mine = 0x7fffffff;
+        if (tid < n && !(sum <= __dadd_rn(b[(size_t)lp * n + tid], tolerance))) mine = tid;
+        mine = __reduce_min_sync(0xffffffffu, mine);
+        if ((tid & 31) == 0 && mine != 0x7fffffff) atomicMin(&bad, mine);
+        __syncthreads();
+        if (tid == 0) first_bad[lp] = (bad == 0x7fffffff) ? -1 : bad;
+        __syncthreads();
+        lp = lp_next;
+        xpar ^= 1;
+    }
+}
+
 }  // namespace lpb
 
 using namespace lpb;
@@ -125,8 +285,32 @@ extern "C" int lpb200_verify_bounds_batch_device(int B, int n, int m, const doub
     if (rc) return rc;
     cudaStream_t stream = (cudaStream_t)stream_v;
     const size_t xs_bytes = (size_t)((m + 1) & ~1) * 8;
+    // n <= 256: the pipelined kernel (column blocks through a double buffer, several CTAs per SM)
+    const bool vec16 = (m & 1) == 0 && ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(x)) & 15) == 0;
+    const size_t piped_bytes = 2 * xs_bytes + 2 * (size_t)n * (vec16 ? kVpCols : kVpCols + 1) * 8;
+    const char *force = getenv("LPB_DEBUG_VERIFY");  // "staged" / "direct": the round-1 kernels (A/B, tests)
+    if (n <= kVpThreads && piped_bytes <= (size_t)di.max_smem_optin && force == nullptr) {
+        int per_sm = (int)((size_t)di.max_smem_per_sm / (piped_bytes + 1024));
+        if (per_sm < 1) per_sm = 1;
+        if (per_sm > 8) per_sm = 8;
+        long long grid = (long long)di.sm_count * per_sm;
+        if (grid > B) grid = B;
+        if (vec16) {
+            LPB_CUDA(cudaFuncSetAttribute(verify_bounds_pipelined_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)piped_bytes));
+            verify_bounds_pipelined_kernel<true><<<(int)grid, kVpThreads, piped_bytes, stream>>>(
+                B, n, m, A, b, x, status, tolerance, first_bad_row);
+        } else {
+            LPB_CUDA(cudaFuncSetAttribute(verify_bounds_pipelined_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)piped_bytes));
+            verify_bounds_pipelined_kernel<false><<<(int)grid, kVpThreads, piped_bytes, stream>>>(
+                B, n, m, A, b, x, status, tolerance, first_bad_row);
+        }
+        LPB_CUDA(cudaGetLastError());
+        return 0;
+    }
     const size_t staged_bytes = xs_bytes + (size_t)n * (m | 1) * 8;
-    const bool staged = staged_bytes <= (size_t)di.max_smem_optin;
+    const bool staged = staged_bytes <= (size_t)di.max_smem_optin && !(force && force[0] == 'd');
     if (!staged && xs_bytes > (size_t)di.max_smem_optin) {
         set_error("lpb200_verify_bounds_batch: m too large for the shared-memory copy of x");
         return LPB200_E_TOO_LARGE;

@@ -422,8 +422,14 @@ def test_two_lane_host_path_is_bit_identical(oracle_lib, monkeypatch, kind):
         assert 0 <= narrowed <= nl
     else:
         assert narrowed == 0 and abytes == A.nbytes
+    # no override: the MEASURED gate decides (a probe call runs the copy engine alone for its first chunks, then both
+    # lanes; the verdict holds for the next calls) -- whichever way it falls, every chunk is served exactly once
+    monkeypatch.delenv("LPB_HOST_NARROW")
+    gated = [lp.solve_batch(A, b, c, max_pivots=20000, log_cap=16) for _ in range(3)]
+    cl, nl, _, _ = _lanes()
+    assert cl + nl == _ceil_div(700, (64 * 1024) // _lp_bytes(24, 31, 16)) and cl > 0
     st, x, obj, npiv, _ = oracle_lib.simplex_batch(A, b, c, max_pivots=20000)
-    for r in (one, two):
+    for r in [one, two] + gated:
         assert np.array_equal(r.status, st) and np.array_equal(r.npivots, npiv)
         assert np.array_equal(r.x.view(np.int64), x.view(np.int64))
         assert np.array_equal(r.objective.view(np.int64), obj.view(np.int64))

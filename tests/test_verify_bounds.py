@@ -64,11 +64,16 @@ def test_oracle_boundary_is_inclusive(oracle_lib):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("kernel", ["default", "staged", "direct"])
 @pytest.mark.parametrize("n,m,count", [(7, 9, 300), (100, 100, 200), (1, 1, 64), (3, 257, 40), (160, 170, 12),
-                                       (300, 310, 6)])
-def test_gpu_kernel_vs_oracle(oracle_lib, n, m, count):
-    """(300, 310) does not fit shared memory: the direct-from-global variant."""
+                                       (300, 310, 6), (256, 33, 9), (100, 32, 50), (100, 31, 1500)])
+def test_gpu_kernel_vs_oracle(oracle_lib, monkeypatch, kernel, n, m, count):
+    """Three kernels: the pipelined one (default for n <= 256: column blocks of 32 through a cp.async double buffer),
+    and the two of round 1 forced through LPB_DEBUG_VERIFY -- whole LP staged in shared memory / rows read straight
+    from global memory ((300, 310) fits neither the pipelined nor the staged kernel)."""
     import linear_programming_b200 as lp
+    if kernel != "default":
+        monkeypatch.setenv("LPB_DEBUG_VERIFY", kernel)
     A, b, x = _cases(7 + n, count, n, m, 3)
     status = np.zeros(count, dtype=np.int32)
     status[1::4] = 1     # "Infinity": no x, skipped
