@@ -39,7 +39,10 @@
 
 namespace lpb {
 
-constexpr int kGjK = 16;            // pivots per panel
+#ifndef LPB_GJ_K
+#define LPB_GJ_K 16
+#endif
+constexpr int kGjK = LPB_GJ_K;      // pivots per panel
 constexpr int kGjPS = kGjK + 2;     // panel row stride in shared memory (16-byte aligned rows)
 constexpr int kGjMaxThreads = 512;  // CTA size for large systems; small ones get 64 or 128 threads (more systems per SM)
 #ifndef LPB_GJ_ROWS
@@ -484,7 +487,7 @@ gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restric
 
 using namespace lpb;
 
-static inline int gj_smem_bytes(int n) { return n * kGjPS * 8 + 288; }  // panel + flag, perm, argmax slots
+static inline int gj_smem_bytes(int n) { return n * kGjPS * 8 + 224 + 4 * kGjK; }  // panel + flag, perm, argmax slots
 
 static int gj_launch(int B, int n, double *wa, double *x, int pivoting, int32_t *status, const DeviceInfo &di,
                      cudaStream_t stream)
@@ -492,7 +495,7 @@ static int gj_launch(int B, int n, double *wa, double *x, int pivoting, int32_t 
     const int smem = gj_smem_bytes(n);
     if (smem > di.max_smem_optin) {
         set_error("lpb200_gauss_jordan_batch: n too large for the shared-memory panel (n <= " +
-                  std::to_string((di.max_smem_optin - 288) / (kGjPS * 8)) + ")");
+                  std::to_string((di.max_smem_optin - 224 - 4 * kGjK) / (kGjPS * 8)) + ")");
         return LPB200_E_TOO_LARGE;
     }
     // CTA size by system size: a 512-thread CTA idles on the small systems the course feeds this solver
