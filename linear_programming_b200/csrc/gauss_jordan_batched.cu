@@ -109,7 +109,10 @@ __device__ __forceinline__ void gj_factor_rows(double *P, int n, int k, int tid)
 // instructions per fp64 operation.  Needs 2 x K pivot-row values in registers, hence 256-thread CTAs at
 // 128 registers, two per SM.  Same operations per element in the same order: bit-identical.
 template <bool kPartial, int kGjThreads, bool kPairs = false>
-__global__ void __launch_bounds__(kGjThreads, (kPairs ? 2 : (kGjThreads == kGjMaxThreads ? LPB_GJ_MINB : 1024 / kGjThreads)))
+#ifndef LPB_GJ_MINB256
+#define LPB_GJ_MINB256 4
+#endif
+__global__ void __launch_bounds__(kGjThreads, (kPairs ? 2 : (kGjThreads == kGjMaxThreads ? LPB_GJ_MINB : (kGjThreads == 256 ? LPB_GJ_MINB256 : 1024 / kGjThreads))))
 gauss_jordan_batched_kernel(int n, double *__restrict__ a_all, double *__restrict__ x_all,
                             int32_t *__restrict__ status_all)
 {
