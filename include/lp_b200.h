@@ -307,6 +307,26 @@ int lpb200_gauss_jordan_batch_status_device(int B, int n, const double *a, const
 int lpb200_gauss_jordan_batch_status(int B, int n, const double *a, const double *b, double *x, int pivoting,
                                      int32_t *status);
 
+/*
+ * Batched Gauss-Jordan that ALLOCATES NOTHING and needs no caller workspace.  This entry point has no counterpart in
+ * the reference: it was added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels, same arithmetic and the
+ * same outputs as lpb200_gauss_jordan_batch_status_device (x bit-identical, status as described there; `status` may
+ * be NULL); device pointers on the current device, enqueued on `stream`, no synchronisation, no cudaMalloc / cudaFree
+ * / pool allocation on any path.
+ *   The working copy of `a` (which the elimination destroys) lives in a file-scope __device__ array of
+ *   LPB200_GJ_STATIC_SCRATCH_BYTES inside the library -- every GPU that loads liblp_b200.so holds these bytes until
+ *   the process exits.  Limit: B * n * n * 8 <= LPB200_GJ_STATIC_SCRATCH_BYTES (16 systems of 512 x 512, 4096 of
+ *   32 x 32, 10485 of the course's 20 x 20); a larger batch is rejected with LPB200_E_TOO_LARGE and a message that
+ *   states both sizes.
+ *   All calls share that one array per GPU.  It keeps the last call's contents (nothing needs clearing: a call
+ *   overwrites what it uses before reading it).  Calls that OVERLAP on the GPU -- different streams, or several host
+ *   threads on one device -- race on it and corrupt each other's answers; calls on one stream are ordered and safe.
+ */
+#define LPB200_GJ_STATIC_SCRATCH_BYTES (32 * 1024 * 1024)
+int lpb200_gauss_jordan_batch_static_device(int B, int n, const double *a, const double *b, double *x, int pivoting,
+                                            int32_t *status, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

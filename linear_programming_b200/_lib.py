@@ -87,6 +87,8 @@ SIGNATURES = {
     "lpb200_gauss_jordan_batch_ex": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, ctypes.c_int]),
     "lpb200_gauss_jordan_batch_status_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp,
                                                                ctypes.c_int, c_vp, c_vp, ctypes.c_int64, c_vp]),
+    "lpb200_gauss_jordan_batch_static_device": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp,
+                                                               ctypes.c_int, c_vp, c_vp]),
     "lpb200_gauss_jordan_batch_status": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, ctypes.c_int,
                                                         c_vp]),
 }

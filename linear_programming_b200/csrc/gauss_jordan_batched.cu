@@ -34,6 +34,9 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <atomic>
+#include <string>
+
 #include "lp_common.cuh"
 #include "lp_host.h"
 
@@ -628,4 +631,77 @@ extern "C" int lpb200_gauss_jordan_batch_status(int B, int n, const double *a, c
 extern "C" int lpb200_gauss_jordan_batch(int B, int n, const double *a, const double *b, double *x)
 {
     return lpb200_gauss_jordan_batch_ex(B, n, a, b, x, LPB200_PIVOT_REFERENCE);
+}
+
+// ======================================================================================
+// lpb200_gauss_jordan_batch_static_device: the same kernels with NO allocation anywhere and no caller workspace.
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+//
+// The elimination destroys its working copy of `a`; the other device entry points take that copy as a caller-owned
+// `workspace`.  Here it lives in a file-scope __device__ array of LPB200_GJ_STATIC_SCRATCH_BYTES (32 MiB), which every
+// GPU that loads the library holds until the process exits.  In HOST code the array's name is only a host-side
+// stand-in for the symbol, not a device address (a kernel handed it would fault, or silently use the wrong memory where
+// the GPU can reach host memory): the device address is looked up with cudaGetSymbolAddress once per device, with that
+// device current, and cached.  Every call shares the array: it keeps the last call's contents (nothing here has to
+// start at zero -- the whole region a call uses is overwritten by its copy of `a` before the kernel reads it), and two
+// calls that overlap on the GPU (different streams, or different host threads on one device) RACE on it; calls on one
+// stream are ordered and safe.
+// ======================================================================================
+constexpr size_t kGjStaticBytes = (size_t)LPB200_GJ_STATIC_SCRATCH_BYTES;
+static __device__ __align__(256) double g_gj_static_scratch[kGjStaticBytes / sizeof(double)];
+
+// Device address of g_gj_static_scratch on the CURRENT device (must be `device`).  Once per device.
+static int gj_static_scratch_address(int device, double **out)
+{
+    constexpr int kMaxDevices = 64;
+    static std::atomic<double *> cache[kMaxDevices];
+    if (device < 0 || device >= kMaxDevices) {
+        set_error("lpb200_gauss_jordan_batch_static_device: unsupported device ordinal");
+        return LPB200_E_INVALID;
+    }
+    double *p = cache[device].load(std::memory_order_acquire);
+    if (p == nullptr) {
+        void *sym = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&sym, g_gj_static_scratch);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_gj_static_scratch)");
+        if (sym == nullptr || (reinterpret_cast<uintptr_t>(sym) & 255) != 0) {
+            set_error("lpb200_gauss_jordan_batch_static_device: the static scratch has no usable device address");
+            return LPB200_E_CUDA;
+        }
+        p = static_cast<double *>(sym);
+        cache[device].store(p, std::memory_order_release);  // racing first calls look up the same address
+    }
+    *out = p;
+    return 0;
+}
+
+extern "C" int lpb200_gauss_jordan_batch_static_device(int B, int n, const double *a, const double *b, double *x,
+                                                       int pivoting, int32_t *status, void *stream_v)
+{
+    int rc = gj_check(B, n, pivoting);
+    if (rc) return rc;
+    if (B == 0 || n == 0) return 0;  // size 0 prints nothing (week-2/energy_values/tests/01)
+    if (a == nullptr || b == nullptr || x == nullptr) {
+        set_error("lpb200_gauss_jordan_batch_static_device: null argument");
+        return LPB200_E_INVALID;
+    }
+    const unsigned long long need = (unsigned long long)B * (unsigned long long)n * (unsigned long long)n * 8ull;
+    if (need > (unsigned long long)kGjStaticBytes) {
+        set_error("lpb200_gauss_jordan_batch_static_device: B*n*n*8 = " + std::to_string(need) +
+                  " bytes of working copy exceed the static scratch of " + std::to_string(kGjStaticBytes) +
+                  " bytes (LPB200_GJ_STATIC_SCRATCH_BYTES); split the batch, or use lpb200_gauss_jordan_batch_status_device "
+                  "with a workspace of your own");
+        return LPB200_E_TOO_LARGE;
+    }
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    DeviceInfo di;
+    rc = get_device_info(&di);  // the current device
+    if (rc) return rc;
+    double *wa = nullptr;
+    rc = gj_static_scratch_address(di.device, &wa);
+    if (rc) return rc;
+    LPB_CUDA(cudaMemcpyAsync(wa, a, (size_t)need, cudaMemcpyDeviceToDevice, stream));
+    if (x != b) LPB_CUDA(cudaMemcpyAsync(x, b, (size_t)B * n * 8, cudaMemcpyDeviceToDevice, stream));
+    return gj_launch(B, n, wa, x, pivoting, status, di, stream);
 }
