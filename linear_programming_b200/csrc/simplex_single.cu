@@ -46,6 +46,7 @@
 #include <cuda_runtime.h>
 #include <math_constants.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include <vector>
 
@@ -64,7 +65,12 @@ constexpr int kMaxRanks = 32;
 constexpr int kDegenerateStreak = 8;  // Dantzig: degenerate pivots in a row before Bland takes over (as in the batch kernel)
 constexpr unsigned long long kKeyZeroRatio = 0x8000000000000000ull;  // order_key(+0.0)
 
-enum { ST_ISIZE = 0, ST_IFILL, ST_IUSED, ST_DSIZE, ST_DFILL, ST_DUSED, ST_NLIST, ST_NCOLS, ST_COUNT = 16 };
+enum { ST_ISIZE = 0, ST_IFILL, ST_IUSED, ST_DSIZE, ST_DFILL, ST_DUSED, ST_NLIST, ST_NCOLS,
+       ST_TCUR,                               // 1: the tableau the solve stopped on is T2 (pipelined loop, see below)
+       ST_LA_STATUS,                          // look-ahead hand-over, [2][4] by pivot parity: outcome of the NEXT pivot's
+                                              // selection (LA_* code, entering position, leaving variable, its row)
+       ST_COUNT = 32 };
+enum { LA_PIVOT = 0, LA_OPTIMAL, LA_INFINITY, LA_TYPE_ERROR };
 
 // Exchange buffer of one rank, in 8-byte words.  Every payload word is an "LL" word:
 // low 32 bits data, high 32 bits the epoch of the exchange that wrote it.
@@ -86,9 +92,11 @@ struct SingleWS {
     const double *A;              // this rank's columns of A: A[i*lda + (k - c_lo)]
     long long lda;
     double *T;                    // [(n+1)][S]  owned non-basic columns; row n = objective
+    double *T2;                   // [(n+1)][S]  second tableau buffer: the pipelined loop sweeps T -> T2 -> T ...
     double *bcol;                 // [n+1]       constant column (b, then v at index n), replicated
     double *nr;                   // [S]         scaled pivot row, owned columns
     double *fc;                   // [n+1]       pivot column factors, replicated
+    double *fc2;                  // [n+1]       the NEXT pivot's column (written by the look-ahead while fc is in use)
     double *cstage;               // scratch: factors of the objective rebuild
     double *scal;                 // [4]         nr constant
     double *wts;                  // [S]         LPB200_RULE_DEVEX: reference-framework weights of the owned columns
@@ -115,6 +123,7 @@ struct SingleArgs {
     int log_cap;
     int cpr;  // CTAs per rank in this launch
     int rule; // LPB200_RULE_*: 0 = the reference's decisions, 1 = Bland, 2 = Dantzig (corrected modes)
+    int pipelined;  // 1: rules 0/1 run the pipelined loop (one barrier per pivot); 0: step by step (LPB_DEBUG_SINGLE_PIPELINE=0)
     unsigned long long timeout_ns;
 };
 
@@ -225,6 +234,7 @@ struct LoopCtl {
     unsigned epoch;   // exchange epoch (continues across solves)
     unsigned kx;      // key exchanges so far (parity selects the key buffer)
     int streak;       // LPB200_RULE_DANTZIG / DEVEX: degenerate pivots in a row in the current loop
+    int tcur;         // 1: the kernel's w.T is the workspace's T2 (the pipelined loop ended on an odd pivot count)
     // LPB200_RULE_DEVEX: the last pivot (entering position, its weight) still has to update the weights
     bool upd;
     int p_prev;
@@ -561,17 +571,42 @@ __device__ __forceinline__ void phase_sweep(SweepSmem &sm, const SingleWS &w, Lo
     }
 }
 
+#ifdef LPB_TIMING
+// per-phase wall time of the pivot loop, accumulated by thread 0 of CTA 0 of each rank (globaltimer, ns):
+// [0] P1 entering scan  [1] grid.sync  [2] reduce + key exchange  [3] P2 column gather / broadcast / ratio
+// [4] grid.sync  [5] reduce  [6] P3 pivot row  [7] grid.sync  [8] bookkeeping + sweep  [9] grid.sync  [10] pivots
+__device__ unsigned long long g_single_timing[32][12];
+#define LPB_ST(slot)                                                             \
+    do {                                                                         \
+        if (ctl.bid == 0 && threadIdx.x == 0) {                                  \
+            const unsigned long long _t = globaltimer_ns();                      \
+            g_single_timing[w.rank][slot] += _t - tlast;                         \
+            tlast = _t;                                                          \
+        }                                                                        \
+    } while (0)
+#else
+#define LPB_ST(slot) do { } while (0)
+#endif
+
 // P3 + P4 of one pivot: e sits at column position p, l owns row r.
 __device__ __forceinline__ void single_pivot(cg::grid_group &grid, SweepSmem &sm, const SingleWS &w,
-                                             const SingleArgs &a, LoopCtl &ctl, int p, int r, int e, int l)
+                                             const SingleArgs &a, LoopCtl &ctl, int p, int r, int e, int l,
+                                             unsigned long long *tl = nullptr)
 {
+#ifdef LPB_TIMING
+    unsigned long long tlast = tl ? *tl : globaltimer_ns();
+#else
+    (void)tl;
+#endif
     if (a.rule == LPB200_RULE_DEVEX) {  // fc[n+1] carries the entering column's weight (phase_ratio)
         ctl.wq = w.fc[w.n + 1];
         ctl.p_prev = p;
         ctl.upd = true;
     }
     phase_pivot_row(w, ctl, p, r, e, a.tol);
+    LPB_ST(6);
     grid.sync();
+    LPB_ST(7);
     if (ctl.bid == ctl.nblk - 1 && threadIdx.x == kSgThreads - 32) {
         if (w.pivot_log != nullptr && ctl.npiv < a.log_cap) {
             w.pivot_log[2 * ctl.npiv] = e;
@@ -580,7 +615,9 @@ __device__ __forceinline__ void single_pivot(cg::grid_group &grid, SweepSmem &sm
         single_bookkeeping(w, ctl.track_dep, p, r, e, l);
     }
     phase_sweep(sm, w, ctl, r, a.tol);
+    LPB_ST(8);
     grid.sync();
+    LPB_ST(9);
     ++ctl.npiv;
 }
 
@@ -596,16 +633,24 @@ __device__ __forceinline__ int single_run_loop(cg::grid_group &grid, BlockRed &b
         // Dantzig prices by coefficient until more than kDegenerateStreak pivots in a row made no progress
         const int pricing = (a.rule >= LPB200_RULE_DANTZIG && ctl.streak > kDegenerateStreak) ? LPB200_RULE_BLAND : a.rule;
         const bool with_id = pricing >= LPB200_RULE_DANTZIG;  // (value key, variable id) instead of (priority, position)
+#ifdef LPB_TIMING
+        unsigned long long tlast = globaltimer_ns();
+#endif
         phase_entering(br, w, ctl, a.tol, pricing, a.rule);
         ctl.upd = false;  // the Devex weights are up to date with the last pivot
+        LPB_ST(0);
         grid.sync();
+        LPB_ST(1);
         reduce_partials(br, w, ctl, 0, key, var, flag);
         key = exchange_key(br, w, ctl, key, var, with_id, a.timeout_ns);
+        LPB_ST(2);
         if (key == kKeyNone) return 0;
         const int p = with_id ? w.varpos[var] : (int)(key & 0xffffffffull);
         const int e = w.colvar[p];
         phase_ratio(br, w, ctl, p, e, a.tol, corrected, a.rule == LPB200_RULE_DEVEX, a.timeout_ns);
+        LPB_ST(3);
         grid.sync();
+        LPB_ST(4);
         reduce_partials(br, w, ctl, 1, key, var, flag);
         if (flag) return LPB200_STATUS_REF_TYPE_ERROR;
         if (key == kKeyNone) return LPB200_STATUS_INFINITY;
@@ -613,7 +658,13 @@ __device__ __forceinline__ int single_run_loop(cg::grid_group &grid, BlockRed &b
         if (ctl.npiv >= a.max_pivots) return LPB200_STATUS_ITERATION_LIMIT;
         const int l = var;
         const int r = ~w.varpos[l];
+        LPB_ST(5);
+#ifdef LPB_TIMING
+        single_pivot(grid, sm, w, a, ctl, p, r, e, l, &tlast);
+        if (ctl.bid == 0 && threadIdx.x == 0) g_single_timing[w.rank][10] += 1;
+#else
         single_pivot(grid, sm, w, a, ctl, p, r, e, l);
+#endif
     }
 }
 
@@ -639,6 +690,331 @@ __device__ __forceinline__ unsigned long long driveout_key(cg::grid_group &grid,
     grid.sync();
     reduce_partials(br, w, ctl, 0, key, var, flag);
     return exchange_key(br, w, ctl, key, var, false, a.timeout_ns);
+}
+
+// ======================================================================================
+// Pipelined pivot loop (LPB200_RULE_REFERENCE / LPB200_RULE_BLAND, two or more CTAs per rank): ONE grid barrier
+// per pivot instead of four.
+//
+// The selection of the next pivot needs very little of the tableau the current pivot produces: the objective row
+// (entering column, simplex.py:390-392), one column of it (the ratio test, :394-436) and the constant column.  All of
+// it can be computed from the OLD tableau, the pivot column fc[] and the old pivot row -- provided the old values are
+// still there.  So the sweep is not done in place: pivot k reads tableau buffer A and writes buffer B, pivot k+1
+// reads B and writes A (same HBM traffic: every element is read once and written once either way; 2 x 4.3 GB at
+// 16384 x 32768 is small change next to 180 GB).  While CTAs 1 .. nblk-1 of a rank sweep A -> B, CTA 0 of the rank --
+// the control CTA -- performs pivot k's set bookkeeping, updates the constant column and the objective row, picks the
+// next entering column (key exchange with the other ranks' control CTAs), computes that column of B from A (the owner)
+// and broadcasts it, and runs the ratio test: by the time the sweep ends, pivot k+1 is decided.  The fixed cost of a
+// pivot (four grid barriers, three selection phases, two NVLink exchanges: 20 us on one GPU, 23-27 us on eight, measured
+// with tools/gpu/single_phases.py) overlaps the sweep; what is left on the critical path is one barrier.
+// Every value is produced by the same operations on the same operands as in the step-by-step loop: same bits.
+// ======================================================================================
+
+// Sweep of pivot (entering position p, leaving row r) from tableau A into tableau B by the sweeper CTAs (bid >= 1).
+// Rows 0 .. n-1 only: the objective row belongs to the control CTA.  The tile's slice of the OLD pivot row (A, row r)
+// and of the pivot column are staged by TMA; every thread scales its double2 of the row into the new pivot row
+// (make_pivot_constraint :325-345) in registers.  Unlike the in-place sweep every row is written (a row with a zero
+// factor is copied) and the old pivot row is never overwritten, so no CTA ever reads what another one writes.
+__device__ __forceinline__ void sweep_issue_pp(SweepSmem &sm, const SingleWS &w, const double *A, const double *fcA,
+                                               int r, int stage, int tile, int nstrips)
+{
+    const int strip = tile % nstrips, rb = tile / nstrips;
+    const int c0 = strip * kTileCols, r0 = rb * kTileRows;
+    const int cols = min(kTileCols, w.S - c0);                 // even (S is a multiple of 16)
+    const int rows = (min(kTileRows, w.n - r0) + 1) & ~1;      // fc[] is padded: reading one element past is harmless
+    const uint32_t bnr = (uint32_t)cols * 8u, bfc = (uint32_t)rows * 8u;
+    mbar_expect_tx(&sm.bar[stage], bnr + bfc);
+    tma_load_1d(sm.nr[stage], A + (size_t)r * w.S + c0, bnr, &sm.bar[stage]);
+    tma_load_1d(sm.fc[stage], fcA + r0, bfc, &sm.bar[stage]);
+}
+
+__device__ __forceinline__ void phase_sweep_pp(SweepSmem &sm, const SingleWS &w, LoopCtl &ctl, const double *A,
+                                               double *B, const double *fcA, int p, int r, double tol)
+{
+    const int tid = threadIdx.x;
+    const int n = w.n, S = w.S;
+    const int sb = ctl.bid - 1, nsb = ctl.nblk - 1;  // this CTA among the sweepers
+    const int lcols = max(0, min(w.wloc, ctl.ncols - w.c_lo));
+    const int nstrips = (lcols + kTileCols - 1) / kTileCols;
+    const int nrb = (n + kTileRows - 1) / kTileRows;
+    const int ntiles = nstrips * nrb;
+    const double pinv = pivot_inverse(fcA[r], tol);
+    const double dpiv = snap(-pinv, tol);
+    const int pl = p - w.c_lo;  // local position of the entering column; outside [0, S) on the ranks that do not own it
+    int tile = sb;
+    if (tile < ntiles && tid == 0) {
+        fence_proxy_async();
+        sweep_issue_pp(sm, w, A, fcA, r, 0, tile, nstrips);
+    }
+    for (int it = 0; tile < ntiles; tile += nsb, ++it) {
+        const int stage = it & 1;
+        if (tid == 0 && tile + nsb < ntiles) sweep_issue_pp(sm, w, A, fcA, r, stage ^ 1, tile + nsb, nstrips);
+        mbar_wait(&sm.bar[stage], (ctl.parity >> stage) & 1u);
+        ctl.parity ^= 1u << stage;
+        const int strip = tile % nstrips, rb = tile / nstrips;
+        const int c0 = strip * kTileCols, r0 = rb * kTileRows;
+        const int rows = min(kTileRows, n - r0);
+        const int col = c0 + 2 * tid;
+        if (col < S) {
+            const double2 raw = reinterpret_cast<const double2 *>(sm.nr[stage])[tid];
+            const bool zx = (col == pl), zy = (col + 1 == pl);  // column p now belongs to the leaving variable (None -> 0)
+            double2 r2;
+            r2.x = (col < lcols) ? (zx ? dpiv : snap(__dmul_rn(pinv, raw.x), tol)) : 0.0;
+            r2.y = (col + 1 < lcols) ? (zy ? dpiv : snap(__dmul_rn(pinv, raw.y), tol)) : 0.0;
+            const double2 *abase = reinterpret_cast<const double2 *>(A + (size_t)r0 * S + col);
+            double2 *bbase = reinterpret_cast<double2 *>(B + (size_t)r0 * S + col);
+            const size_t rs = (size_t)S / 2;  // row stride in double2
+            for (int ii = 0; ii < rows; ii += kRowUnroll) {
+                double2 v[kRowUnroll];
+                double f[kRowUnroll];
+#pragma unroll
+                for (int j = 0; j < kRowUnroll; ++j) {
+                    const int q = ii + j;
+                    f[j] = (q < rows) ? sm.fc[stage][q] : 0.0;
+                    if (q < rows && r0 + q != r) v[j] = __ldcs(abase + (size_t)q * rs);
+                }
+#pragma unroll
+                for (int j = 0; j < kRowUnroll; ++j) {
+                    const int q = ii + j;
+                    if (q < rows) {
+                        double2 o;
+                        if (r0 + q == r) {
+                            o = r2;  // store(entering_idx, row) (:352)
+                        } else {
+                            o = v[j];
+                            if (zx) o.x = 0.0;
+                            if (zy) o.y = 0.0;
+                            if (f[j] != 0.0) {  // substitute() (:185-214); a zero factor returns the row unchanged
+                                o.x = axpy_snap(o.x, f[j], r2.x, tol);
+                                o.y = axpy_snap(o.y, f[j], r2.y, tol);
+                            }
+                        }
+                        __stcs(bbase + (size_t)q * rs, o);
+                    }
+                }
+            }
+        }
+        __syncthreads();  // everyone is done with sm.*[stage] before it is refilled
+    }
+    fence_proxy_async();  // B's rows are read through the async proxy (TMA) by the next pivot's sweep
+}
+
+// Look-ahead of the control CTA (bid == 0) while the sweepers apply pivot (p, r, e, l), A -> B.  Leaves the outcome of
+// the NEXT pivot's selection in desc[] (LA_* code, entering position, leaving variable, its row) and that pivot's
+// column in fcB[].  In the order of the step-by-step loop: the None records of this pivot (P3), its set bookkeeping
+// (:369-381), the constant column, the objective row (:314-318) with the entering keys (:390-392), the key exchange,
+// the entering column of B computed from A, its broadcast, the ratio test (:394-436).
+__device__ __forceinline__ void lookahead(BlockRed &br, const SingleWS &w, const SingleArgs &a, LoopCtl &ctl,
+                                          const double *A, double *B, const double *fcA, double *fcB, int *desc, int p,
+                                          int r, int e, int l)
+{
+    const int tid = threadIdx.x;
+    const int n = w.n, S = w.S, G = w.nranks;
+    const double tol = a.tol;
+    const bool corrected = (a.rule != LPB200_RULE_REFERENCE);
+    const double pinv = pivot_inverse(fcA[r], tol);
+    const double dpiv = snap(-pinv, tol);
+    const double nrc = snap(__dmul_rn(pinv, w.bcol[r]), tol);  // the pivot row's constant (:331-336)
+    __syncthreads();  // every thread has read bcol[r] before it is rewritten
+    constexpr int kWorkers = kSgThreads - 32;  // thread kWorkers does the (serial) set bookkeeping meanwhile
+    if (tid == kWorkers) {
+        if (w.pivot_log != nullptr && ctl.npiv < a.log_cap) {
+            w.pivot_log[2 * ctl.npiv] = e;
+            w.pivot_log[2 * ctl.npiv + 1] = l;
+        }
+        single_bookkeeping(w, ctl.track_dep, p, r, e, l);
+    } else if (tid < kWorkers) {
+        for (int i = tid; i <= n; i += kWorkers) {
+            const double f = fcA[i];
+            if (i < n && (f != 0.0 || i == r)) {  // the row is rewritten by this pivot: its only None is column e
+                w.nonecol[i] = e;
+                w.untouched[i] = 0;
+            }
+            if (i == r) w.bcol[i] = nrc;
+            else if (f != 0.0) w.bcol[i] = axpy_snap(w.bcol[i], f, nrc, tol);
+        }
+    }
+    __syncthreads();
+    // ---- objective row of B, and the entering key of every owned column ----
+    unsigned long long key = kKeyNone;
+    int var = 0x7fffffff, flag = 0;
+    {
+        const double fobj = fcA[n];
+        const int lim = min(w.wloc, ctl.ncols - w.c_lo);
+        const int pl = p - w.c_lo;
+        const int *prio = corrected ? w.colvar : w.colslot;  // Bland: variable id; reference: CPython-set slot
+        const double *Ar = A + (size_t)r * S, *An = A + (size_t)n * S;
+        double *Bn = B + (size_t)n * S;
+        for (int kl = tid; kl < S; kl += kSgThreads) {
+            double r2 = 0.0;
+            if (kl < lim) r2 = (kl == pl) ? dpiv : snap(__dmul_rn(pinv, Ar[kl]), tol);
+            double o = (kl == pl) ? 0.0 : An[kl];
+            if (fobj != 0.0) o = axpy_snap(o, fobj, r2, tol);
+            Bn[kl] = o;
+            if (kl < lim && o > tol) {
+                const int k = w.c_lo + kl;
+                const unsigned long long kk = ((unsigned long long)(unsigned)prio[k] << 32) | (unsigned)k;
+                key = kk < key ? kk : key;
+            }
+        }
+    }
+    block_argmin(br, key, var, flag);
+    key = exchange_key(br, w, ctl, key, var, false, a.timeout_ns);
+    if (key == kKeyNone) {
+        if (tid == 0) desc[0] = LA_OPTIMAL;
+        return;
+    }
+    const int p2 = (int)(key & 0xffffffffull);
+    const int e2 = w.colvar[p2];
+    // ---- column p2 of B from A (its owner), broadcast, ratio test on the updated constant column ----
+    const int owner = p2 / S, pl2 = p2 - owner * S;
+    const bool mine = (owner == w.rank);
+    double nr_p2 = 0.0;
+    if (mine) nr_p2 = (p2 == p) ? dpiv : snap(__dmul_rn(pinv, A[(size_t)r * S + pl2]), tol);
+    const bool e_in_basis0 = (w.basis0[e2 >> 5] >> (e2 & 31)) & 1u;
+    unsigned ep = 0;
+    unsigned long long *fcll = nullptr;
+    if (G > 1) {
+        ep = ++ctl.epoch;
+        fcll = w.xbuf + xb_fc(G);
+    }
+    key = kKeyNone;
+    var = 0x7fffffff;
+    int crash = 0;
+    for (int i = tid; i <= n; i += kSgThreads) {
+        double f = 0.0;
+        if (mine) {
+            double v;
+            if (i == r) {
+                v = nr_p2;
+            } else {
+                const double a0 = (p2 == p) ? 0.0 : A[(size_t)i * S + pl2];
+                const double fi = fcA[i];
+                v = (fi != 0.0) ? axpy_snap(a0, fi, nr_p2, tol) : a0;
+            }
+            f = (fabs(v) <= tol) ? 0.0 : v;  // substitute() skips a zero coefficient (:203-205)
+        }
+        if (G > 1) {
+            if (mine) {
+                const unsigned long long bits = (unsigned long long)__double_as_longlong(f);
+                for (int g = 0; g < G; ++g) ll_store(w.peers[g] + xb_fc(G) + 2 * i, bits, ep);
+            }
+            f = __longlong_as_double((long long)ll_load(fcll + 2 * i, ep, a.timeout_ns));
+        }
+        fcB[i] = f;
+        if (i < n) {
+            const int nc = w.nonecol[i];
+            crash |= (nc == kNoneInitial && e2 < n) || (nc == e2) || (w.untouched[i] && e_in_basis0);
+            const double coeff = -f;
+            if (coeff > tol) {
+                const double ratio = snap(__ddiv_rn(w.bcol[i], coeff), tol);
+                if (ratio != 0.0 || corrected) {
+                    const unsigned long long k = order_key(ratio);
+                    const int v = w.rowvar[i];
+                    if (k < key || (k == key && v < var)) {
+                        key = k;
+                        var = v;
+                    }
+                }
+            }
+        }
+    }
+    if (corrected) crash = 0;
+    block_argmin(br, key, var, crash);
+    if (tid == 0) {
+        if (crash) {
+            desc[0] = LA_TYPE_ERROR;
+        } else if (key == kKeyNone) {
+            desc[0] = LA_INFINITY;
+        } else {
+            desc[0] = LA_PIVOT;
+            desc[1] = p2;
+            desc[2] = var;
+            desc[3] = ~w.varpos[var];
+        }
+    }
+    fence_proxy_async();  // fcB is read through the async proxy (TMA) by the next sweep
+}
+
+// SlackForm.solve loop (:442-466), pipelined.  Same decisions, same arithmetic, same exits as single_run_loop.
+__device__ __forceinline__ int single_run_loop_pipelined(cg::grid_group &grid, BlockRed &br, SweepSmem &sm,
+                                                         SingleWS &w, const SingleArgs &a, LoopCtl &ctl)
+{
+    const bool corrected = (a.rule != LPB200_RULE_REFERENCE);
+    ctl.streak = 0;
+    unsigned long long key;
+    int var, flag;
+    // the first pivot of the loop is selected step by step (there is no sweep to hide the selection behind)
+    phase_entering(br, w, ctl, a.tol, a.rule, a.rule);
+    grid.sync();
+    reduce_partials(br, w, ctl, 0, key, var, flag);
+    key = exchange_key(br, w, ctl, key, var, false, a.timeout_ns);
+    if (key == kKeyNone) return 0;
+    int p = (int)(key & 0xffffffffull);
+    int e = w.colvar[p];
+    phase_ratio(br, w, ctl, p, e, a.tol, corrected, false, a.timeout_ns);
+    grid.sync();
+    reduce_partials(br, w, ctl, 1, key, var, flag);
+    if (flag) return LPB200_STATUS_REF_TYPE_ERROR;
+    if (key == kKeyNone) return LPB200_STATUS_INFINITY;
+    int l = var;
+    int r = ~w.varpos[l];
+    double *A = w.T, *B = w.T2, *fcA = w.fc, *fcB = w.fc2;
+    int flips = 0, status = 0;
+    for (;;) {
+        if (ctl.npiv >= a.max_pivots) {
+            status = LPB200_STATUS_ITERATION_LIMIT;
+            break;
+        }
+#ifdef LPB_TIMING
+        unsigned long long tlast = globaltimer_ns();
+#endif
+        int *desc = w.state + ST_LA_STATUS + 4 * (ctl.npiv & 1);  // double-buffered by pivot parity
+        if (ctl.bid == 0) lookahead(br, w, a, ctl, A, B, fcA, fcB, desc, p, r, e, l);
+        else phase_sweep_pp(sm, w, ctl, A, B, fcA, p, r, a.tol);
+        LPB_ST(8);
+        grid.sync();
+        LPB_ST(9);
+#ifdef LPB_TIMING
+        if (ctl.bid == 0 && threadIdx.x == 0) g_single_timing[w.rank][10] += 1;
+#endif
+        ++ctl.npiv;
+        {
+            double *t = A; A = B; B = t;
+            t = fcA; fcA = fcB; fcB = t;
+            flips ^= 1;
+        }
+        const int la = desc[0];
+        if (ctl.bid != 0 && w.nranks > 1) {  // the exchanges the control CTA performed: keep the counters uniform
+            ctl.epoch += (la == LA_OPTIMAL) ? 1u : 2u;
+            ctl.kx += 1u;
+        }
+        if (la == LA_OPTIMAL) break;
+        if (la == LA_INFINITY) { status = LPB200_STATUS_INFINITY; break; }
+        if (la == LA_TYPE_ERROR) { status = LPB200_STATUS_REF_TYPE_ERROR; break; }
+        p = desc[1];
+        l = desc[2];
+        r = desc[3];
+        e = w.colvar[p];  // only the control CTA uses it, and it reads it before its own bookkeeping rewrites it
+    }
+    if (flips) {  // the tableau the loop stopped on is what was T2 when it started: make it the kernel's T
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double *t = w.T; w.T = w.T2; w.T2 = t;
+            t = w.fc; w.fc = w.fc2; w.fc2 = t;
+        }
+        ctl.tcur ^= 1;
+        __syncthreads();
+    }
+    return status;
+}
+
+__device__ __forceinline__ int run_loop_auto(cg::grid_group &grid, BlockRed &br, SweepSmem &sm, SingleWS &w,
+                                             const SingleArgs &a, LoopCtl &ctl)
+{
+    if (a.pipelined && a.rule < LPB200_RULE_DANTZIG && ctl.nblk >= 2)
+        return single_run_loop_pipelined(grid, br, sm, w, a, ctl);
+    return single_run_loop(grid, br, sm, w, a, ctl);
 }
 
 __global__ void __launch_bounds__(kSgThreads)
@@ -675,6 +1051,7 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
     ctl.epoch = (w.nranks > 1) ? (unsigned)w.xbuf[kXbEpoch] : 0u;
     ctl.kx = (w.nranks > 1) ? (unsigned)w.xbuf[kXbKx] : 0u;
     ctl.streak = 0;
+    ctl.tcur = 0;
 
     // ---- min_constant, idx = min_index(b) (:591): zeros count as +inf, first minimum wins ----
     int idx0;
@@ -779,7 +1156,7 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
                 phase_ratio(br, w, ctl, m, aux, tol, corrected, devex, a.timeout_ns);  // column m -> fc[]; its partial is unused
                 grid.sync();
                 single_pivot(grid, sm, w, a, ctl, m, idx0, aux, idx0);
-                status = single_run_loop(grid, br, sm, w, a, ctl);  // :526
+                status = run_loop_auto(grid, br, sm, w, a, ctl);  // :526
             }
             if (status == 0) {
                 if (!(fabs(w.bcol[n]) <= tol)) status = LPB200_STATUS_NO_SOLUTION;       // :528-530
@@ -804,7 +1181,7 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
                                 phase_ratio(br, w, ctl, p, ev, tol, corrected, devex, a.timeout_ns);  // column p -> fc[]
                                 grid.sync();
                                 single_pivot(grid, sm, w, a, ctl, p, r, ev, aux);
-                                status = single_run_loop(grid, br, sm, w, a, ctl);
+                                status = run_loop_auto(grid, br, sm, w, a, ctl);
                             }
                         }
                     }
@@ -881,10 +1258,10 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
                     }
                 }
                 grid.sync();
-                status = single_run_loop(grid, br, sm, w, a, ctl);  // :599
+                status = run_loop_auto(grid, br, sm, w, a, ctl);  // :599
             }
         } else {
-            status = single_run_loop(grid, br, sm, w, a, ctl);  // :619
+            status = run_loop_auto(grid, br, sm, w, a, ctl);  // :619
         }
     }
 
@@ -906,6 +1283,7 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
             w.xbuf[kXbKx] = ctl.kx;
         }
         w.state[ST_NCOLS] = (status == LPB200_STATUS_REF_ATTRIBUTE_ERROR) ? 0 : ctl.ncols;  // 0: no tableau was built
+        w.state[ST_TCUR] = ctl.tcur;
     }
 }
 
@@ -916,7 +1294,7 @@ __global__ void simplex_single_state_kernel(const SingleWS *__restrict__ hdr, do
     const SingleWS &w = *hdr;
     const int n = w.n, nv = w.n + w.m + 1;
     const bool built = w.state[ST_NCOLS] != 0;
-    const double *obj = w.T + (size_t)n * w.S;
+    const double *obj = (w.state[ST_TCUR] ? w.T2 : w.T) + (size_t)n * w.S;
     for (int v = blockIdx.x * blockDim.x + threadIdx.x; v <= nv; v += gridDim.x * blockDim.x) {
         double o = 0.0, cst = 0.0;
         if (v == nv) {
@@ -966,9 +1344,11 @@ static size_t carve_single(SingleWS *w, int n, int m, int rank, int nranks, unsi
     w->field = reinterpret_cast<type *>(base + o);        \
     o += up256(sizeof(type) * (size_t)(count));
     CARVE(T, double, (size_t)(n + 1) * w->S)
+    CARVE(T2, double, (size_t)(n + 1) * w->S)
     CARVE(bcol, double, n + 2)
     CARVE(nr, double, w->S)
     CARVE(fc, double, n + 2 + kTileRows)
+    CARVE(fc2, double, n + 2 + kTileRows)
     CARVE(cstage, double, (n > m ? n : m) + 1)
     CARVE(scal, double, 4)
     CARVE(wts, double, w->S)
@@ -1033,6 +1413,10 @@ static int pick_ctas_per_rank(const DeviceInfo &di, int n, int wcols, int groups
     // small problems: no point in more CTAs than there is work
     const long long work = ((long long)(n + 1) * (wcols + 1) + kSgThreads * 8 - 1) / (kSgThreads * 8);
     if (cpr > work) cpr = (int)(work < 1 ? 1 : work);
+    if (const char *g = getenv("LPB_DEBUG_SINGLE_CPR")) {  // measurements: force the CTAs per rank
+        const int v = atoi(g);
+        if (v >= 1 && v <= di.sm_count * per_sm / groups) cpr = v;
+    }
     if (cpr < 1) {
         set_error("lpb200_simplex_single: too many emulated ranks for one cooperative launch");
         return LPB200_E_TOO_LARGE;
@@ -1052,12 +1436,28 @@ static int launch_single(const SingleWS *d_ranks, int groups, int cpr, const dou
     a.max_pivots = max_pivots;
     a.log_cap = log_cap;
     a.cpr = cpr;
+    {
+        const char *g = getenv("LPB_DEBUG_SINGLE_PIPELINE");
+        a.pipelined = !(g && g[0] == '0');
+    }
     a.timeout_ns = (unsigned long long)(timeout_s * 1e9);
     void *params[] = {(void *)&d_ranks, (void *)&a};
     LPB_CUDA(cudaLaunchCooperativeKernel((const void *)simplex_single_kernel, dim3(groups * cpr),
                                          dim3(kSgThreads), params, 0, stream));
     return 0;
 }
+
+#ifdef LPB_TIMING
+// debug builds only (not declared in include/lp_b200.h): read and clear the phase timers of the current device
+extern "C" int lpb_debug_single_timing(unsigned long long *out /* [32][12] */)
+{
+    LPB_CUDA(cudaDeviceSynchronize());
+    LPB_CUDA(cudaMemcpyFromSymbol(out, g_single_timing, sizeof(unsigned long long) * 32 * 12));
+    static unsigned long long zeros[32 * 12];
+    LPB_CUDA(cudaMemcpyToSymbol(g_single_timing, zeros, sizeof(zeros)));
+    return 0;
+}
+#endif
 
 extern "C" int64_t lpb200_simplex_single_workspace_bytes(int n, int m)
 {
