@@ -109,6 +109,7 @@ struct SingleWS {
     unsigned long long *part_key;                 // [2][ctas]  set 0: entering, set 1: leaving
     int *part_var, *part_crash;
     int *state;
+    unsigned *labar;              // counter of the control barrier (pipelined loop)
     unsigned long long *xbuf;                     // this rank's exchange buffer (nranks > 1)
     unsigned long long *const *peers;             // [nranks] every rank's exchange buffer, peer-mapped
     int32_t *status;
@@ -123,6 +124,7 @@ struct SingleArgs {
     int log_cap;
     int cpr;  // CTAs per rank in this launch
     int rule; // LPB200_RULE_*: 0 = the reference's decisions, 1 = Bland, 2 = Dantzig (corrected modes)
+    int nctl_max;   // control CTAs per rank of the pipelined loop, at most (LPB_DEBUG_SINGLE_NCTL)
     int pipelined;  // 1: rules 0/1 run the pipelined loop (one barrier per pivot); 0: step by step (LPB_DEBUG_SINGLE_PIPELINE=0)
     unsigned long long timeout_ns;
 };
@@ -235,6 +237,8 @@ struct LoopCtl {
     unsigned kx;      // key exchanges so far (parity selects the key buffer)
     int streak;       // LPB200_RULE_DANTZIG / DEVEX: degenerate pivots in a row in the current loop
     int tcur;         // 1: the kernel's w.T is the workspace's T2 (the pipelined loop ended on an odd pivot count)
+    int nctl;         // pipelined loop: CTAs 0 .. nctl-1 of the rank are its control CTAs, the others sweep
+    unsigned labar_gen;  // control barriers passed so far (control CTAs only)
     // LPB200_RULE_DEVEX: the last pivot (entering position, its weight) still has to update the weights
     bool upd;
     int p_prev;
@@ -492,6 +496,7 @@ struct SweepSmem {
     double nr[2][kTileCols];
     double fc[2][kTileRows];
     uint64_t bar[2];
+    int tile[2];  // pipelined loop: the tile staged in each buffer (tiles are pulled off a counter)
 };
 
 __device__ __forceinline__ void sweep_issue(SweepSmem &sm, const SingleWS &w, int stage, int tile,
@@ -733,7 +738,6 @@ __device__ __forceinline__ void phase_sweep_pp(SweepSmem &sm, const SingleWS &w,
 {
     const int tid = threadIdx.x;
     const int n = w.n, S = w.S;
-    const int sb = ctl.bid - 1, nsb = ctl.nblk - 1;  // this CTA among the sweepers
     const int lcols = max(0, min(w.wloc, ctl.ncols - w.c_lo));
     const int nstrips = (lcols + kTileCols - 1) / kTileCols;
     const int nrb = (n + kTileRows - 1) / kTileRows;
@@ -741,14 +745,29 @@ __device__ __forceinline__ void phase_sweep_pp(SweepSmem &sm, const SingleWS &w,
     const double pinv = pivot_inverse(fcA[r], tol);
     const double dpiv = snap(-pinv, tol);
     const int pl = p - w.c_lo;  // local position of the entering column; outside [0, S) on the ranks that do not own it
-    int tile = sb;
-    if (tile < ntiles && tid == 0) {
-        fence_proxy_async();
-        sweep_issue_pp(sm, w, A, fcA, r, 0, tile, nstrips);
+    // Tiles are pulled off a counter (one per pivot parity; the control CTAs zero the other one meanwhile): the
+    // control CTAs join the sweep when their look-ahead is done, and nobody waits for a slow CTA at the end.  Thread 0
+    // claims two tiles ahead, so the latency of the atomic is never waited for.
+    unsigned *ctr = w.labar + 1 + (ctl.npiv & 1);
+    int claimed = 0;  // (thread 0) the tile claimed for the iteration after next
+    if (tid == 0) {
+        const int t0 = (int)atomicAdd(ctr, 1u);
+        sm.tile[0] = t0;
+        if (t0 < ntiles) {
+            fence_proxy_async();
+            sweep_issue_pp(sm, w, A, fcA, r, 0, t0, nstrips);
+        }
+        claimed = (int)atomicAdd(ctr, 1u);
     }
-    for (int it = 0; tile < ntiles; tile += nsb, ++it) {
+    __syncthreads();
+    int tile = sm.tile[0];
+    for (int it = 0; tile < ntiles; ++it) {
         const int stage = it & 1;
-        if (tid == 0 && tile + nsb < ntiles) sweep_issue_pp(sm, w, A, fcA, r, stage ^ 1, tile + nsb, nstrips);
+        if (tid == 0) {
+            sm.tile[stage ^ 1] = claimed;
+            if (claimed < ntiles) sweep_issue_pp(sm, w, A, fcA, r, stage ^ 1, claimed, nstrips);
+            claimed = (claimed < ntiles) ? (int)atomicAdd(ctr, 1u) : ntiles;
+        }
         mbar_wait(&sm.bar[stage], (ctl.parity >> stage) & 1u);
         ctl.parity ^= 1u << stage;
         const int strip = tile % nstrips, rb = tile / nstrips;
@@ -794,48 +813,131 @@ __device__ __forceinline__ void phase_sweep_pp(SweepSmem &sm, const SingleWS &w,
                 }
             }
         }
-        __syncthreads();  // everyone is done with sm.*[stage] before it is refilled
+        __syncthreads();  // everyone is done with sm.*[stage] before it is refilled; publishes sm.tile[stage ^ 1]
+        tile = sm.tile[stage ^ 1];
     }
     fence_proxy_async();  // B's rows are read through the async proxy (TMA) by the next pivot's sweep
 }
 
-// Look-ahead of the control CTA (bid == 0) while the sweepers apply pivot (p, r, e, l), A -> B.  Leaves the outcome of
-// the NEXT pivot's selection in desc[] (LA_* code, entering position, leaving variable, its row) and that pivot's
+#ifdef LPB_TIMING
+// inside the look-ahead (pipelined mode; slots 0..5 of g_single_timing): [0] bookkeeping + None records + constant column
+// [1] objective row + keys  [2] key exchange  [3] column from A (owner)  [4] broadcast (owner) / receive  [5] ratio test
+#define LPB_LA_T(slot)                                                \
+    do {                                                              \
+        __syncthreads();                                              \
+        if (threadIdx.x == 0 && ctl.bid == 0) {                       \
+            const unsigned long long _t = globaltimer_ns();           \
+            g_single_timing[w.rank][slot] += _t - la_t;               \
+            la_t = _t;                                                \
+        }                                                             \
+    } while (0)
+#else
+#define LPB_LA_T(slot) do { } while (0)
+#endif
+
+// Barrier among the control CTAs of one rank (bid < ctl.nctl): a counter in global memory that only ever grows; the
+// k-th barrier since it was zeroed (kernel set-up) completes when it reaches k * nctl.  All control CTAs are resident
+// (cooperative launch), so the spin cannot deadlock.
+__device__ __forceinline__ void control_barrier(const SingleWS &w, LoopCtl &ctl)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned target = (++ctl.labar_gen) * (unsigned)ctl.nctl;
+        __threadfence();
+        atomicAdd(w.labar, 1u);
+        while (*reinterpret_cast<volatile unsigned *>(w.labar) < target) {
+        }
+        __threadfence();
+    } else {
+        ++ctl.labar_gen;  // (every thread keeps the count; only thread 0 uses it)
+    }
+    __syncthreads();
+}
+
+// lexicographic (key, var) minimum + OR of the flags over the control CTAs' partials of `set`
+__device__ __forceinline__ void reduce_control(BlockRed &br, const SingleWS &w, const LoopCtl &ctl, int set,
+                                               unsigned long long &key, int &var, int &flag)
+{
+    key = kKeyNone;
+    var = 0x7fffffff;
+    flag = 0;
+    const int lo = set * ctl.nblk;
+    for (int q = lo + threadIdx.x; q < lo + ctl.nctl; q += kSgThreads) {
+        const unsigned long long k = __ldcg(w.part_key + q);
+        const int v = __ldcg(w.part_var + q);
+        if (k < key || (k == key && v < var)) {
+            key = k;
+            var = v;
+        }
+        flag |= __ldcg(w.part_crash + q);
+    }
+    block_argmin(br, key, var, flag);
+}
+
+// Look-ahead of the CONTROL CTAs (bid < ctl.nctl) while the sweepers apply pivot (p, r, e, l), A -> B.  Leaves the outcome
+// of the NEXT pivot's selection in desc[] (LA_* code, entering position, leaving variable, its row) and that pivot's
 // column in fcB[].  In the order of the step-by-step loop: the None records of this pivot (P3), its set bookkeeping
 // (:369-381), the constant column, the objective row (:314-318) with the entering keys (:390-392), the key exchange,
 // the entering column of B computed from A, its broadcast, the ratio test (:394-436).
-__device__ __forceinline__ void lookahead(BlockRed &br, const SingleWS &w, const SingleArgs &a, LoopCtl &ctl,
-                                          const double *A, double *B, const double *fcA, double *fcB, int *desc, int p,
-                                          int r, int e, int l)
+// While the sweepers saturate HBM a dependent memory access costs several microseconds, so the work is spread over
+// nctl x 256 threads with kLaBatch independent accesses in flight each: every phase is one or two memory rounds, and
+// three control barriers separate them.  (One control CTA, one access per iteration: 317 us on eight GPUs against a
+// 166 us sweep; measured with tools/gpu/single_phases.py.)
+__device__ __noinline__ void lookahead(BlockRed &br, const SingleWS &w, const SingleArgs &a, LoopCtl &ctl,
+                                       const double *A, double *B, const double *fcA, double *fcB, int *desc, int p,
+                                       int r, int e, int l)
 {
+    constexpr int kLaBatch = 4;  // independent memory accesses in flight per thread
     const int tid = threadIdx.x;
     const int n = w.n, S = w.S, G = w.nranks;
+    const int gt = ctl.bid * kSgThreads + tid, gs = ctl.nctl * kSgThreads;  // this thread among the control threads
     const double tol = a.tol;
     const bool corrected = (a.rule != LPB200_RULE_REFERENCE);
     const double pinv = pivot_inverse(fcA[r], tol);
     const double dpiv = snap(-pinv, tol);
-    const double nrc = snap(__dmul_rn(pinv, w.bcol[r]), tol);  // the pivot row's constant (:331-336)
-    __syncthreads();  // every thread has read bcol[r] before it is rewritten
-    constexpr int kWorkers = kSgThreads - 32;  // thread kWorkers does the (serial) set bookkeeping meanwhile
-    if (tid == kWorkers) {
+    const double nrc = snap(__dmul_rn(pinv, w.bcol[r]), tol);  // the pivot row's constant (:331-336); bcol[r] itself is
+                                                               // rewritten only after the first control barrier
+#ifdef LPB_TIMING
+    unsigned long long la_t = globaltimer_ns();
+#endif
+    if (gt == 0) w.labar[1 + ((ctl.npiv + 1) & 1)] = 0u;  // the NEXT pivot's tile counter (idle since the last barrier)
+    // ---- phase 1: set bookkeeping (one thread), None records and constant column (everyone else) ----
+    constexpr int kBookThread = kSgThreads - 32;
+    if (gt == kBookThread) {
         if (w.pivot_log != nullptr && ctl.npiv < a.log_cap) {
             w.pivot_log[2 * ctl.npiv] = e;
             w.pivot_log[2 * ctl.npiv + 1] = l;
         }
         single_bookkeeping(w, ctl.track_dep, p, r, e, l);
-    } else if (tid < kWorkers) {
-        for (int i = tid; i <= n; i += kWorkers) {
-            const double f = fcA[i];
-            if (i < n && (f != 0.0 || i == r)) {  // the row is rewritten by this pivot: its only None is column e
-                w.nonecol[i] = e;
-                w.untouched[i] = 0;
+    } else {
+        const int wid = gt < kBookThread ? gt : gt - 1, nw = gs - 1;
+        for (int i0 = wid; i0 <= n; i0 += nw * kLaBatch) {
+            double f[kLaBatch], bv[kLaBatch];
+#pragma unroll
+            for (int j = 0; j < kLaBatch; ++j) {
+                const int i = i0 + j * nw;
+                if (i <= n) {
+                    f[j] = fcA[i];
+                    bv[j] = w.bcol[i];
+                }
             }
-            if (i == r) w.bcol[i] = nrc;
-            else if (f != 0.0) w.bcol[i] = axpy_snap(w.bcol[i], f, nrc, tol);
+#pragma unroll
+            for (int j = 0; j < kLaBatch; ++j) {
+                const int i = i0 + j * nw;
+                if (i <= n) {
+                    if (i < n && (f[j] != 0.0 || i == r)) {  // the row is rewritten by this pivot: its only None is column e
+                        w.nonecol[i] = e;
+                        w.untouched[i] = 0;
+                    }
+                    if (i != r && f[j] != 0.0) w.bcol[i] = axpy_snap(bv[j], f[j], nrc, tol);
+                }
+            }
         }
     }
-    __syncthreads();
-    // ---- objective row of B, and the entering key of every owned column ----
+    control_barrier(w, ctl);  // bookkeeping done (slots / ids of every column are final); everyone has read bcol[r]
+    if (gt == 0) w.bcol[r] = nrc;
+    LPB_LA_T(0);
+    // ---- phase 2: objective row of B, and the entering key of every owned column ----
     unsigned long long key = kKeyNone;
     int var = 0x7fffffff, flag = 0;
     {
@@ -845,32 +947,52 @@ __device__ __forceinline__ void lookahead(BlockRed &br, const SingleWS &w, const
         const int *prio = corrected ? w.colvar : w.colslot;  // Bland: variable id; reference: CPython-set slot
         const double *Ar = A + (size_t)r * S, *An = A + (size_t)n * S;
         double *Bn = B + (size_t)n * S;
-        for (int kl = tid; kl < S; kl += kSgThreads) {
-            double r2 = 0.0;
-            if (kl < lim) r2 = (kl == pl) ? dpiv : snap(__dmul_rn(pinv, Ar[kl]), tol);
-            double o = (kl == pl) ? 0.0 : An[kl];
-            if (fobj != 0.0) o = axpy_snap(o, fobj, r2, tol);
-            Bn[kl] = o;
-            if (kl < lim && o > tol) {
-                const int k = w.c_lo + kl;
-                const unsigned long long kk = ((unsigned long long)(unsigned)prio[k] << 32) | (unsigned)k;
-                key = kk < key ? kk : key;
+        for (int k0 = gt; k0 < S; k0 += gs * kLaBatch) {
+            double rr[kLaBatch], oo[kLaBatch];
+#pragma unroll
+            for (int j = 0; j < kLaBatch; ++j) {
+                const int kl = k0 + j * gs;
+                if (kl < S) {
+                    rr[j] = __ldcg(Ar + kl);
+                    oo[j] = __ldcg(An + kl);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < kLaBatch; ++j) {
+                const int kl = k0 + j * gs;
+                if (kl < S) {
+                    double r2 = 0.0;
+                    if (kl < lim) r2 = (kl == pl) ? dpiv : snap(__dmul_rn(pinv, rr[j]), tol);
+                    double o = (kl == pl) ? 0.0 : oo[j];
+                    if (fobj != 0.0) o = axpy_snap(o, fobj, r2, tol);
+                    Bn[kl] = o;
+                    if (kl < lim && o > tol) {
+                        const int k = w.c_lo + kl;
+                        const unsigned long long kk = ((unsigned long long)(unsigned)__ldcg(prio + k) << 32) | (unsigned)k;
+                        key = kk < key ? kk : key;
+                    }
+                }
             }
         }
     }
     block_argmin(br, key, var, flag);
+    write_partial(w, ctl, 0, key, var, flag);
+    control_barrier(w, ctl);
+    reduce_control(br, w, ctl, 0, key, var, flag);
+    LPB_LA_T(1);
     key = exchange_key(br, w, ctl, key, var, false, a.timeout_ns);
+    LPB_LA_T(2);
     if (key == kKeyNone) {
-        if (tid == 0) desc[0] = LA_OPTIMAL;
+        if (gt == 0) desc[0] = LA_OPTIMAL;
         return;
     }
     const int p2 = (int)(key & 0xffffffffull);
-    const int e2 = w.colvar[p2];
-    // ---- column p2 of B from A (its owner), broadcast, ratio test on the updated constant column ----
+    const int e2 = __ldcg(w.colvar + p2);
+    // ---- phase 3: column p2 of B from A (its owner), broadcast, ratio test on the updated constant column ----
     const int owner = p2 / S, pl2 = p2 - owner * S;
     const bool mine = (owner == w.rank);
     double nr_p2 = 0.0;
-    if (mine) nr_p2 = (p2 == p) ? dpiv : snap(__dmul_rn(pinv, A[(size_t)r * S + pl2]), tol);
+    if (mine) nr_p2 = (p2 == p) ? dpiv : snap(__dmul_rn(pinv, __ldcg(A + (size_t)r * S + pl2)), tol);
     const bool e_in_basis0 = (w.basis0[e2 >> 5] >> (e2 & 31)) & 1u;
     unsigned ep = 0;
     unsigned long long *fcll = nullptr;
@@ -881,47 +1003,105 @@ __device__ __forceinline__ void lookahead(BlockRed &br, const SingleWS &w, const
     key = kKeyNone;
     var = 0x7fffffff;
     int crash = 0;
-    for (int i = tid; i <= n; i += kSgThreads) {
-        double f = 0.0;
-        if (mine) {
-            double v;
-            if (i == r) {
-                v = nr_p2;
-            } else {
-                const double a0 = (p2 == p) ? 0.0 : A[(size_t)i * S + pl2];
-                const double fi = fcA[i];
-                v = (fi != 0.0) ? axpy_snap(a0, fi, nr_p2, tol) : a0;
+    const bool same = (p2 == p);  // the column that changed hands: its old entries count as zero (None)
+    for (int i0 = gt; i0 <= n; i0 += gs * kLaBatch) {
+        double f[kLaBatch];
+        if (mine) {  // pass A (owner): the column, computed from A
+            double a0[kLaBatch], fi[kLaBatch];
+#pragma unroll
+            for (int j = 0; j < kLaBatch; ++j) {
+                const int i = i0 + j * gs;
+                if (i <= n) {
+                    a0[j] = (same || i == r) ? 0.0 : __ldcg(A + (size_t)i * S + pl2);
+                    fi[j] = fcA[i];
+                }
             }
-            f = (fabs(v) <= tol) ? 0.0 : v;  // substitute() skips a zero coefficient (:203-205)
-        }
-        if (G > 1) {
-            if (mine) {
-                const unsigned long long bits = (unsigned long long)__double_as_longlong(f);
-                for (int g = 0; g < G; ++g) ll_store(w.peers[g] + xb_fc(G) + 2 * i, bits, ep);
+#pragma unroll
+            for (int j = 0; j < kLaBatch; ++j) {
+                const int i = i0 + j * gs;
+                if (i <= n) {
+                    double v;
+                    if (i == r) v = nr_p2;
+                    else v = (fi[j] != 0.0) ? axpy_snap(a0[j], fi[j], nr_p2, tol) : a0[j];
+                    f[j] = (fabs(v) <= tol) ? 0.0 : v;  // substitute() skips a zero coefficient (:203-205)
+                }
             }
-            f = __longlong_as_double((long long)ll_load(fcll + 2 * i, ep, a.timeout_ns));
+            if (G > 1) {  // pass B (owner): one LL packet per element into every OTHER rank's buffer
+#pragma unroll
+                for (int j = 0; j < kLaBatch; ++j) {
+                    const int i = i0 + j * gs;
+                    if (i <= n) {
+                        const unsigned long long bits = (unsigned long long)__double_as_longlong(f[j]);
+                        for (int g = 0; g < G; ++g)
+                            if (g != w.rank) ll_store(w.peers[g] + xb_fc(G) + 2 * i, bits, ep);
+                    }
+                }
+            }
+        } else {  // pass C (the others): kLaBatch packets polled at a time
+            unsigned long long w0[kLaBatch], w1[kLaBatch];
+#pragma unroll
+            for (int j = 0; j < kLaBatch; ++j) {
+                const int i = i0 + j * gs;
+                if (i <= n)
+                    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];"
+                                 : "=l"(w0[j]), "=l"(w1[j])
+                                 : "l"(fcll + 2 * i)
+                                 : "memory");
+            }
+#pragma unroll
+            for (int j = 0; j < kLaBatch; ++j) {
+                const int i = i0 + j * gs;
+                if (i <= n) {
+                    unsigned long long bits;
+                    if ((unsigned)(w0[j] >> 32) == ep && (unsigned)(w1[j] >> 32) == ep)
+                        bits = (w0[j] & 0xffffffffull) | (w1[j] << 32);
+                    else
+                        bits = ll_load(fcll + 2 * i, ep, a.timeout_ns);  // not there yet: wait for this one
+                    f[j] = __longlong_as_double((long long)bits);
+                }
+            }
         }
-        fcB[i] = f;
-        if (i < n) {
-            const int nc = w.nonecol[i];
-            crash |= (nc == kNoneInitial && e2 < n) || (nc == e2) || (w.untouched[i] && e_in_basis0);
-            const double coeff = -f;
-            if (coeff > tol) {
-                const double ratio = snap(__ddiv_rn(w.bcol[i], coeff), tol);
-                if (ratio != 0.0 || corrected) {
-                    const unsigned long long k = order_key(ratio);
-                    const int v = w.rowvar[i];
-                    if (k < key || (k == key && v < var)) {
-                        key = k;
-                        var = v;
+        // pass D: the ratio test (every rank, redundantly, on the replicated constant column)
+        double bv[kLaBatch];
+        int nc[kLaBatch], ut[kLaBatch], rv[kLaBatch];
+#pragma unroll
+        for (int j = 0; j < kLaBatch; ++j) {
+            const int i = i0 + j * gs;
+            if (i <= n) fcB[i] = f[j];
+            if (i < n) {
+                bv[j] = __ldcg(w.bcol + i);
+                nc[j] = __ldcg(w.nonecol + i);
+                ut[j] = __ldcg(w.untouched + i);
+                rv[j] = __ldcg(w.rowvar + i);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kLaBatch; ++j) {
+            const int i = i0 + j * gs;
+            if (i < n) {
+                crash |= (nc[j] == kNoneInitial && e2 < n) || (nc[j] == e2) || (ut[j] && e_in_basis0);
+                const double coeff = -f[j];
+                if (coeff > tol) {
+                    const double ratio = snap(__ddiv_rn(bv[j], coeff), tol);
+                    if (ratio != 0.0 || corrected) {
+                        const unsigned long long k = order_key(ratio);
+                        if (k < key || (k == key && rv[j] < var)) {
+                            key = k;
+                            var = rv[j];
+                        }
                     }
                 }
             }
         }
     }
+    LPB_LA_T(3);
     if (corrected) crash = 0;
     block_argmin(br, key, var, crash);
-    if (tid == 0) {
+    write_partial(w, ctl, 1, key, var, crash);
+    control_barrier(w, ctl);
+    reduce_control(br, w, ctl, 1, key, var, crash);
+    LPB_LA_T(5);
+    if (gt == 0) {
         if (crash) {
             desc[0] = LA_TYPE_ERROR;
         } else if (key == kKeyNone) {
@@ -930,7 +1110,7 @@ __device__ __forceinline__ void lookahead(BlockRed &br, const SingleWS &w, const
             desc[0] = LA_PIVOT;
             desc[1] = p2;
             desc[2] = var;
-            desc[3] = ~w.varpos[var];
+            desc[3] = ~__ldcg(w.varpos + var);
         }
     }
     fence_proxy_async();  // fcB is read through the async proxy (TMA) by the next sweep
@@ -944,6 +1124,7 @@ __device__ __forceinline__ int single_run_loop_pipelined(cg::grid_group &grid, B
     ctl.streak = 0;
     unsigned long long key;
     int var, flag;
+    if (ctl.bid == 0 && threadIdx.x == 0) w.labar[1] = w.labar[2] = 0u;  // tile counters (two grid barriers follow)
     // the first pivot of the loop is selected step by step (there is no sweep to hide the selection behind)
     phase_entering(br, w, ctl, a.tol, a.rule, a.rule);
     grid.sync();
@@ -970,9 +1151,10 @@ __device__ __forceinline__ int single_run_loop_pipelined(cg::grid_group &grid, B
         unsigned long long tlast = globaltimer_ns();
 #endif
         int *desc = w.state + ST_LA_STATUS + 4 * (ctl.npiv & 1);  // double-buffered by pivot parity
-        if (ctl.bid == 0) lookahead(br, w, a, ctl, A, B, fcA, fcB, desc, p, r, e, l);
-        else phase_sweep_pp(sm, w, ctl, A, B, fcA, p, r, a.tol);
+        if (ctl.bid < ctl.nctl) lookahead(br, w, a, ctl, A, B, fcA, fcB, desc, p, r, e, l);
         LPB_ST(8);
+        phase_sweep_pp(sm, w, ctl, A, B, fcA, p, r, a.tol);  // the control CTAs join once the next pivot is decided
+        LPB_ST(7);
         grid.sync();
         LPB_ST(9);
 #ifdef LPB_TIMING
@@ -985,7 +1167,7 @@ __device__ __forceinline__ int single_run_loop_pipelined(cg::grid_group &grid, B
             flips ^= 1;
         }
         const int la = desc[0];
-        if (ctl.bid != 0 && w.nranks > 1) {  // the exchanges the control CTA performed: keep the counters uniform
+        if (ctl.bid >= ctl.nctl && w.nranks > 1) {  // the exchanges the control CTAs performed: keep the counters uniform
             ctl.epoch += (la == LA_OPTIMAL) ? 1u : 2u;
             ctl.kx += 1u;
         }
@@ -1017,7 +1199,7 @@ __device__ __forceinline__ int run_loop_auto(cg::grid_group &grid, BlockRed &br,
     return single_run_loop(grid, br, sm, w, a, ctl);
 }
 
-__global__ void __launch_bounds__(kSgThreads)
+__global__ void __launch_bounds__(kSgThreads, 2)
 simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
 {
     cg::grid_group grid = cg::this_grid();
@@ -1052,6 +1234,9 @@ simplex_single_kernel(const SingleWS *__restrict__ ranks, const SingleArgs a)
     ctl.kx = (w.nranks > 1) ? (unsigned)w.xbuf[kXbKx] : 0u;
     ctl.streak = 0;
     ctl.tcur = 0;
+    ctl.nctl = max(1, min(a.nctl_max, ctl.nblk / 4));
+    ctl.labar_gen = 0u;
+    if (gtid == 0) *w.labar = 0u;  // (ordered before any control barrier by the grid.sync()s of the set-up)
 
     // ---- min_constant, idx = min_index(b) (:591): zeros count as +inf, first minimum wins ----
     int idx0;
@@ -1368,6 +1553,7 @@ static size_t carve_single(SingleWS *w, int n, int m, int rank, int nranks, unsi
     CARVE(part_var, int, 2 * kMaxSingleGrid)
     CARVE(part_crash, int, 2 * kMaxSingleGrid)
     CARVE(state, int, ST_COUNT)
+    CARVE(labar, unsigned, 4)
 #undef CARVE
     return o;
 }
@@ -1439,6 +1625,9 @@ static int launch_single(const SingleWS *d_ranks, int groups, int cpr, const dou
     {
         const char *g = getenv("LPB_DEBUG_SINGLE_PIPELINE");
         a.pipelined = !(g && g[0] == '0');
+        const char *c = getenv("LPB_DEBUG_SINGLE_NCTL");
+        a.nctl_max = c ? atoi(c) : 16;
+        if (a.nctl_max < 1) a.nctl_max = 1;
     }
     a.timeout_ns = (unsigned long long)(timeout_s * 1e9);
     void *params[] = {(void *)&d_ranks, (void *)&a};

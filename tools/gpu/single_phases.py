@@ -43,7 +43,48 @@ def dump(tag):
     return {"tag": tag, "us_per_pivot": float(mean.sum()), "phases_us": dict(zip(NAMES, [float(v) for v in mean]))}
 
 
+def main_sharded():
+    """Under torchrun: the config-5 LP column-sharded over the ranks, 60 pivots; every rank prints its own timers
+    (pipelined mode: slots 0..5 are the look-ahead's sub-phases, 'bookkeeping + sweep' its total on the control CTA)."""
+    import torch
+    import torch.distributed as dist
+    from linear_programming_b200.sharded import ShardedComm, column_shard
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    dev = torch.device("cuda", torch.cuda.current_device())
+    dist.init_process_group("nccl", device_id=dev)
+    n, m = int(os.environ.get("PH_N", "16383")), int(os.environ.get("PH_M", "32767"))
+    comm = ShardedComm(max_n=n)
+    lo, cnt = column_shard(m, world, rank)
+    A, b, c = workloads.single_lp(n, m, seed=5, col_lo=lo, col_cnt=cnt)
+    dA, db, dc = (torch.from_numpy(v).to(dev) for v in (A, b, c))
+    for rep in range(2):
+        comm.solve(dA, db, dc, n, m, max_pivots=60)
+        torch.cuda.synchronize()
+        dist.barrier()
+        for rk in range(world):
+            if rk == rank and rep == 1 and rank in (0, 1, world - 1):
+                global NAMES
+                NAMES = ["LA bookkeeping+bcol", "LA objective row", "LA key exchange", "LA column from A", "LA broadcast/receive",
+                         "LA ratio", "-", "-", "look-ahead total", "barrier wait"]
+                dump("rank %d of %d, %dx%d" % (rank, world, n, m))
+            elif rk == rank:
+                dump_quiet()
+            dist.barrier()
+    comm.close()
+    dist.destroy_process_group()
+
+
+def dump_quiet():
+    L = _lib.lib()
+    out = (ctypes.c_ulonglong * (32 * 12))()
+    L.lpb_debug_single_timing.restype = ctypes.c_int
+    L.lpb_debug_single_timing(out)
+
+
 def main():
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        return main_sharded()
     n, m, cap = 100, 100, 1500
     A, b, c = (v[0] for v in workloads.simplex_batch("D2", 1, n, m, seed=9))
     res = []
