@@ -59,7 +59,10 @@ namespace lpb {
 
 constexpr int kSgThreads = 256;
 constexpr int kTileCols = 2 * kSgThreads;  // 512 doubles: one double2 per thread
-constexpr int kTileRows = 64;
+#ifndef LPB_TILE_ROWS
+#define LPB_TILE_ROWS 64
+#endif
+constexpr int kTileRows = LPB_TILE_ROWS;
 constexpr int kRowUnroll = 8;
 constexpr int kMaxRanks = 32;
 constexpr int kDegenerateStreak = 8;  // Dantzig: degenerate pivots in a row before Bland takes over (as in the batch kernel)
@@ -706,10 +709,11 @@ __device__ __forceinline__ unsigned long long driveout_key(cg::grid_group &grid,
 // it can be computed from the OLD tableau, the pivot column fc[] and the old pivot row -- provided the old values are
 // still there.  So the sweep is not done in place: pivot k reads tableau buffer A and writes buffer B, pivot k+1
 // reads B and writes A (same HBM traffic: every element is read once and written once either way; 2 x 4.3 GB at
-// 16384 x 32768 is small change next to 180 GB).  While CTAs 1 .. nblk-1 of a rank sweep A -> B, CTA 0 of the rank --
-// the control CTA -- performs pivot k's set bookkeeping, updates the constant column and the objective row, picks the
-// next entering column (key exchange with the other ranks' control CTAs), computes that column of B from A (the owner)
-// and broadcasts it, and runs the ratio test: by the time the sweep ends, pivot k+1 is decided.  The fixed cost of a
+// 16384 x 32768 is small change next to 180 GB).  While the other CTAs of a rank sweep A -> B, its first few CTAs --
+// the control group (8 by default, LPB_DEBUG_SINGLE_NCTL) -- perform pivot k's set bookkeeping, update the constant column and the objective row, pick the
+// next entering column (key exchange with the other ranks' control CTAs), compute that column of B from A (the owner)
+// and broadcast it, run the ratio test -- and then join the sweep (tiles are pulled off a counter): by the time the
+// sweep ends, pivot k+1 is decided.  The fixed cost of a
 // pivot (four grid barriers, three selection phases, two NVLink exchanges: 20 us on one GPU, 23-27 us on eight, measured
 // with tools/gpu/single_phases.py) overlaps the sweep; what is left on the critical path is one barrier.
 // Every value is produced by the same operations on the same operands as in the step-by-step loop: same bits.
@@ -721,12 +725,12 @@ __device__ __forceinline__ unsigned long long driveout_key(cg::grid_group &grid,
 // (make_pivot_constraint :325-345) in registers.  Unlike the in-place sweep every row is written (a row with a zero
 // factor is copied) and the old pivot row is never overwritten, so no CTA ever reads what another one writes.
 __device__ __forceinline__ void sweep_issue_pp(SweepSmem &sm, const SingleWS &w, const double *A, const double *fcA,
-                                               int r, int stage, int tile, int nstrips)
+                                               int r, int stage, int tile, int nstrips, int trows)
 {
     const int strip = tile % nstrips, rb = tile / nstrips;
-    const int c0 = strip * kTileCols, r0 = rb * kTileRows;
+    const int c0 = strip * kTileCols, r0 = rb * trows;
     const int cols = min(kTileCols, w.S - c0);                 // even (S is a multiple of 16)
-    const int rows = (min(kTileRows, w.n - r0) + 1) & ~1;      // fc[] is padded: reading one element past is harmless
+    const int rows = (min(trows, w.n - r0) + 1) & ~1;          // fc[] is padded: reading one element past is harmless
     const uint32_t bnr = (uint32_t)cols * 8u, bfc = (uint32_t)rows * 8u;
     mbar_expect_tx(&sm.bar[stage], bnr + bfc);
     tma_load_1d(sm.nr[stage], A + (size_t)r * w.S + c0, bnr, &sm.bar[stage]);
@@ -740,7 +744,11 @@ __device__ __forceinline__ void phase_sweep_pp(SweepSmem &sm, const SingleWS &w,
     const int n = w.n, S = w.S;
     const int lcols = max(0, min(w.wloc, ctl.ncols - w.c_lo));
     const int nstrips = (lcols + kTileCols - 1) / kTileCols;
-    const int nrb = (n + kTileRows - 1) / kTileRows;
+    // tile height: 64 rows when every CTA gets many tiles (one GPU: 55 each), 32 when it gets few (eight GPUs: 7
+    // each) -- the end of a sweep idles CTAs for up to one tile.  Measured, 16384 x 32768: one GPU 1.315 ms per pivot
+    // with 64 rows against 1.323 with 32; eight GPUs 0.1829 ms against 0.1752 (tools/gpu/pp_tiles.sh)
+    const int trows = (nstrips * ((n + kTileRows - 1) / kTileRows) < 16 * ctl.nblk) ? kTileRows / 2 : kTileRows;
+    const int nrb = (n + trows - 1) / trows;
     const int ntiles = nstrips * nrb;
     const double pinv = pivot_inverse(fcA[r], tol);
     const double dpiv = snap(-pinv, tol);
@@ -755,7 +763,7 @@ __device__ __forceinline__ void phase_sweep_pp(SweepSmem &sm, const SingleWS &w,
         sm.tile[0] = t0;
         if (t0 < ntiles) {
             fence_proxy_async();
-            sweep_issue_pp(sm, w, A, fcA, r, 0, t0, nstrips);
+            sweep_issue_pp(sm, w, A, fcA, r, 0, t0, nstrips, trows);
         }
         claimed = (int)atomicAdd(ctr, 1u);
     }
@@ -765,14 +773,14 @@ __device__ __forceinline__ void phase_sweep_pp(SweepSmem &sm, const SingleWS &w,
         const int stage = it & 1;
         if (tid == 0) {
             sm.tile[stage ^ 1] = claimed;
-            if (claimed < ntiles) sweep_issue_pp(sm, w, A, fcA, r, stage ^ 1, claimed, nstrips);
+            if (claimed < ntiles) sweep_issue_pp(sm, w, A, fcA, r, stage ^ 1, claimed, nstrips, trows);
             claimed = (claimed < ntiles) ? (int)atomicAdd(ctr, 1u) : ntiles;
         }
         mbar_wait(&sm.bar[stage], (ctl.parity >> stage) & 1u);
         ctl.parity ^= 1u << stage;
         const int strip = tile % nstrips, rb = tile / nstrips;
-        const int c0 = strip * kTileCols, r0 = rb * kTileRows;
-        const int rows = min(kTileRows, n - r0);
+        const int c0 = strip * kTileCols, r0 = rb * trows;
+        const int rows = min(trows, n - r0);
         const int col = c0 + 2 * tid;
         if (col < S) {
             const double2 raw = reinterpret_cast<const double2 *>(sm.nr[stage])[tid];
@@ -1626,7 +1634,7 @@ static int launch_single(const SingleWS *d_ranks, int groups, int cpr, const dou
         const char *g = getenv("LPB_DEBUG_SINGLE_PIPELINE");
         a.pipelined = !(g && g[0] == '0');
         const char *c = getenv("LPB_DEBUG_SINGLE_NCTL");
-        a.nctl_max = c ? atoi(c) : 16;
+        a.nctl_max = c ? atoi(c) : 8;
         if (a.nctl_max < 1) a.nctl_max = 1;
     }
     a.timeout_ns = (unsigned long long)(timeout_s * 1e9);
