@@ -133,7 +133,9 @@ int lpb200_simplex_batch_ex(int B, int n, int m, const void *A, int a_dtype, con
  * Single large LP, grid-wide: the condensed tableau lives in HBM and every pivot is one
  * streaming sweep over it by all SMs (cooperative persistent kernel).  Same semantics and
  * outputs as one problem of the batch call.  `workspace` is a device buffer of at least
- * lpb200_simplex_single_workspace_bytes(n, m) bytes (the tableau plus small vectors).
+ * lpb200_simplex_single_workspace_bytes(n, m) bytes: TWO copies of the condensed tableau (2 x 8(n+1)(m+1) bytes,
+ * 8.6 GB at 16384 x 32768 -- the pivot loop sweeps from one into the other so that the next pivot can be selected
+ * while the current one is applied) plus small vectors.
  * stats[0] = kernel milliseconds (CUDA events), stats[1] = pivots (nullable, host memory).
  */
 int64_t lpb200_simplex_single_workspace_bytes(int n, int m);
