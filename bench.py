@@ -93,15 +93,25 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def source_sha16():
-    """Hash of the CUDA/C++ sources the library is built from: ties committed ncu summaries to a build."""
+KERNEL_SOURCES = {  # the files a kernel's device code comes from (host-side edits elsewhere do not stale its ncu facts)
+    "simplex_batched_kernel": ["simplex_batched.cu", "simplex_batched_impl.cuh", "lp_common.cuh"],
+    "simplex_single_kernel": ["simplex_single.cu", "lp_common.cuh"],
+    "gauss_jordan_batched_kernel": ["gauss_jordan_batched.cu", "lp_common.cuh"],
+    "verify_bounds_kernel": ["verify_bounds.cu", "lp_common.cuh"],
+}
+
+
+def source_sha16(kernel=None):
+    """Hash of the CUDA/C++ sources the library is built from (all of csrc/, or the files of one kernel): ties
+    committed ncu summaries to a build."""
     h = hashlib.sha256()
     csrc = os.path.join(ROOT, "linear_programming_b200", "csrc")
-    for name in sorted(os.listdir(csrc)):
-        if name.endswith((".cu", ".cuh", ".h", ".cpp")):
-            with open(os.path.join(csrc, name), "rb") as f:
-                h.update(name.encode())
-                h.update(f.read())
+    names = sorted(KERNEL_SOURCES[kernel]) if kernel in KERNEL_SOURCES else \
+        sorted(n for n in os.listdir(csrc) if n.endswith((".cu", ".cuh", ".h", ".cpp")))
+    for name in names:
+        with open(os.path.join(csrc, name), "rb") as f:
+            h.update(name.encode())
+            h.update(f.read())
     return h.hexdigest()[:16]
 
 
@@ -117,7 +127,7 @@ def ncu_facts(kernel: str):
         return None
     if not rec:
         return None
-    if rec.get("src_sha16") != source_sha16():
+    if rec.get("src_sha16") != source_sha16(kernel):
         return {"stale": True, "captured_src_sha16": rec.get("src_sha16"), "file": rec.get("file")}
     return rec
 
@@ -463,7 +473,7 @@ def bench_batch(ctx, args):
         "kernel": "simplex_batched_kernel", "launch_ms": avg_kern_s * 1e3,
         "launch_ms_each": [round(v, 3) for v in kern_ms],
         "algorithmic_bytes_per_launch": alg_bytes, "algorithmic_bytes_per_pivot": bytes_per_pivot,
-        "pivots_per_launch": pivots_step, "src_sha16": source_sha16(),
+        "pivots_per_launch": pivots_step, "src_sha16": source_sha16("simplex_batched_kernel"),
         "note": "the tableau of an LP stays in shared memory for the whole solve, so the pipe that binds the kernel "
                 "is shared memory (128 B/clk/SM): frac = algorithmic bytes (16*(n+1)*(m+1) per pivot, SURVEY 8(d)) / "
                 "time / shared-memory peak.  The same bytes against the HBM peak (effective_vs_hbm) exceed 1: HBM "

@@ -285,10 +285,11 @@ static thread_local long long g_last_lanes[4] = {0, 0, 0, 0};
 // share one host compete for its memory bandwidth, and then the cores' reads only take bandwidth from the copy
 // engines (round 1: 8 GPUs x 4 threads lost 9 %, 4 GPUs x 8 threads were never measured and regressed).  A probe call
 // lets the copy-engine lane run alone for its first kProbeChunks chunks and only then starts the narrowing lane:
-//   r1 = chunk rate of the copy engine alone,   r2 = aggregate chunk rate of both lanes afterwards;
-// the second lane is kept while r2 > 1.05 * r1.  The verdict holds for the thread's next kGateEvery large calls, then
+//   r1 = chunk rate of the copy engine alone (its first chunks, the pipeline filling up, left out),
+//   r2 = aggregate chunk rate of both lanes afterwards;
+// the second lane is kept while r2 > 1.10 * r1.  The verdict holds for the thread's next kGateEvery large calls, then
 // one call probes again.  LPB_HOST_NARROW=0 / 1 forces the lane off / on (no probe); LPB_DEBUG_GATE=1 prints the rates.
-constexpr int kProbeChunks = 4, kGateEvery = 64;
+constexpr int kProbeChunks = 7, kProbeSkip = 2, kGateEvery = 64;
 struct LaneGate {
     int verdict = 0;  // 0: not measured yet, +1: both lanes, -1: copy engine only
     int age = 0;      // large calls since the last probe
@@ -529,15 +530,17 @@ extern "C" int lpb200_simplex_batch_ex(int B, int n, int m, const void *A_v, int
             for (int s = 0; s < nsets_used; ++s)
                 if (set[s].stream) cudaStreamSynchronize(set[s].stream);
             const clk::time_point t_end = clk::now();
-            // completions of the copy lane before the narrowing lane started
+            // completions of the copy lane before the narrowing lane started; the first kProbeSkip of them are the
+            // pipeline filling up (first copy in, first kernel, first results out) and would make the copy engine look
+            // slower than it is -- at eight ranks that bias switched the lane on and cost 10 % (1.95 M against 2.2 M LPs/s)
             size_t k1 = 0;
             while (k1 < copy_times.size() && copy_times[k1] <= t_narrow) ++k1;
-            if (k1 >= 3 && nchunks > (long long)k1 + 4) {
-                const double d1 = std::chrono::duration<double>(copy_times[k1 - 1] - copy_times[0]).count();
+            if (k1 >= (size_t)kProbeSkip + 3 && nchunks > (long long)k1 + 4) {
+                const double d1 = std::chrono::duration<double>(copy_times[k1 - 1] - copy_times[kProbeSkip]).count();
                 const double d2 = std::chrono::duration<double>(t_end - copy_times[k1 - 1]).count();
-                g_gate.r1 = d1 > 0 ? (double)(k1 - 1) / d1 : 0.0;
+                g_gate.r1 = d1 > 0 ? (double)(k1 - 1 - kProbeSkip) / d1 : 0.0;
                 g_gate.r2 = d2 > 0 ? (double)(nchunks - (long long)k1) / d2 : 0.0;
-                g_gate.verdict = (g_gate.r2 > 1.05 * g_gate.r1) ? 1 : -1;
+                g_gate.verdict = (g_gate.r2 > 1.10 * g_gate.r1) ? 1 : -1;
                 g_gate.age = 0;
                 if (getenv("LPB_DEBUG_GATE"))
                     fprintf(stderr, "[lpb gate] copy engine alone %.1f chunks/s, both lanes %.1f chunks/s -> narrowing lane %s\n",

@@ -49,13 +49,9 @@ def main():
         return x * UNIT.get(u, 1.0) if scale_units else x
 
     sha = args.sha16
-    if sha is None:
-        p = os.path.splitext(args.report)[0] + ".sha"
-        if os.path.exists(p):
-            sha = open(p).read().strip()
-        else:
-            import bench
-            sha = bench.source_sha16()
+    if sha is None:  # the kernel's own files (bench.KERNEL_SOURCES), as they are NOW: run this right after the capture
+        import bench
+        sha = bench.source_sha16(args.kernel)
     dram = (num("dram__bytes_read.sum") or 0.0) + (num("dram__bytes_write.sum") or 0.0)
     wave = num("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", False)
     stalls = {}
