@@ -14,6 +14,9 @@
 #ifndef LPB_WARP_ROWS
 #define LPB_WARP_ROWS 0
 #endif
+#ifndef LPB_LANE_REDUCE
+#define LPB_LANE_REDUCE 1  // per-warp partials / entering keys reduced lane-parallel with redux.sync (0: every thread reads all)
+#endif
 
 namespace lpb {
 namespace LPB_NS {
@@ -381,6 +384,26 @@ __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool 
     }
     if (forced) crash = 0;
     if (__syncthreads_or(crash)) return -2;
+#if LPB_LANE_REDUCE
+    // lane w of every warp takes partial w (ONE shared-memory wavefront per warp instead of nsw broadcast loads per
+    // thread: 126 of the 2 480 wavefronts of a pivot went here), three redux.sync steps give the lexicographic minimum
+    {
+        const int lane = tid & 31;
+        unsigned long long key = kKeyNone;
+        unsigned id = 0x7fffffffu;
+        if (lane < nsw) {
+            const RatioPartial r = part[lane];
+            key = r.key;
+            id = (unsigned)r.id;
+        }
+        const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+        const unsigned mh = __reduce_min_sync(0xffffffffu, hi);
+        const unsigned ml = __reduce_min_sync(0xffffffffu, hi == mh ? lo : 0xffffffffu);
+        const unsigned mi = __reduce_min_sync(0xffffffffu, (hi == mh && lo == ml) ? id : 0x7fffffffu);
+        if (best_key) *best_key = ((unsigned long long)mh << 32) | ml;
+        return (mh == 0xffffffffu && ml == 0xffffffffu) ? -1 : (int)mi;
+    }
+#else
     RatioPartial best = part[0];
     for (int w = 1; w < nsw; ++w) {
         const RatioPartial r = part[w];
@@ -388,6 +411,7 @@ __device__ __forceinline__ int stage_and_ratio(const Ctx &c, int p, int e, bool 
     }
     if (best_key) *best_key = best.key;
     return best.key == kKeyNone ? -1 : best.id;
+#endif
 }
 
 // ---- set bookkeeping by one lane of the 9th warp, overlapped with the sweep (:369-381) ----
@@ -613,6 +637,17 @@ constexpr int kKeySlots = kSweepWarps + 1;               // sweep-warp partial k
 constexpr int kKeyVecs = (kKeySlots + 1 + 3) / 4;        // + the reselect flag, read as uint4
 __device__ __forceinline__ int next_entering(const Ctx &c, int ncols)
 {
+#if LPB_LANE_REDUCE
+    static_assert(kKeySlots + 1 <= 32, "one lane per key slot");
+    const int lane = threadIdx.x & 31;
+    const unsigned v = (lane <= kKeySlots) ? c.redu32[lane] : 0xffffffffu;  // one wavefront per warp
+    if (__shfl_sync(0xffffffffu, v, kKeySlots) != 0u) {
+        __syncthreads();  // everyone has read the flag before the bookkeeping lane can rewrite it
+        return select_entering(c, ncols);
+    }
+    const unsigned best = __reduce_min_sync(0xffffffffu, lane < kKeySlots ? v : 0xffffffffu);
+    return best == 0xffffffffu ? -1 : (int)(best & 0xffffu);
+#else
     unsigned u[kKeyVecs * 4];
 #pragma unroll
     for (int q = 0; q < kKeyVecs; ++q) {
@@ -630,8 +665,8 @@ __device__ __forceinline__ int next_entering(const Ctx &c, int ncols)
 #pragma unroll
     for (int q = 1; q < kKeySlots; ++q) best = min(best, u[q]);
     return best == 0xffffffffu ? -1 : (int)(best & 0xffffu);
+#endif
 }
-
 
 #if LPB_WARP_ROWS
 // =========================================================================================
