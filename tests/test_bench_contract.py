@@ -37,3 +37,35 @@ def test_reference_arm_other_ranks_stay_silent():
     out = _run({"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"})
     assert out.returncode == 0, out.stderr[-2000:]
     assert not [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
+
+
+def test_ncu_facts_are_reported_only_for_the_build_they_were_taken_from(tmp_path, monkeypatch):
+    """bench.py quotes ncu numbers (`traffic`, wavefronts per pivot, DRAM bytes per system) from profiles/ncu_facts.json
+    only while the hash recorded with the capture equals the hash of the kernel's own source files NOW; a capture of
+    another build is reported as stale (-> `traffic: null`), never silently."""
+    import importlib
+    import json
+    sys.path.insert(0, ROOT)
+    bench = importlib.import_module("bench")
+    for k in ("simplex_batched_kernel", "simplex_single_kernel", "gauss_jordan_batched_kernel"):
+        h = bench.source_sha16(k)
+        assert len(h) == 16 and h != bench.source_sha16()          # per-kernel hash differs from the whole-tree one
+        assert h == bench.source_sha16(k)                            # deterministic
+    fake_root = tmp_path
+    (fake_root / "profiles").mkdir()
+    csrc = fake_root / "linear_programming_b200" / "csrc"
+    csrc.mkdir(parents=True)
+    for name in set(sum(bench.KERNEL_SOURCES.values(), [])):
+        (csrc / name).write_text("// " + name + "\n")
+    monkeypatch.setattr(bench, "ROOT", str(fake_root))
+    fresh = bench.source_sha16("simplex_single_kernel")
+    facts = {"simplex_single_kernel": {"src_sha16": fresh, "dram_bytes_per_pivot": 8.59e9, "file": "x.csv"},
+             "gauss_jordan_batched_kernel": {"src_sha16": "0123456789abcdef", "dram_bytes_per_system": 1.0, "file": "y.csv"}}
+    (fake_root / "profiles" / "ncu_facts.json").write_text(json.dumps(facts))
+    assert bench.ncu_facts("simplex_single_kernel")["dram_bytes_per_pivot"] == 8.59e9
+    assert bench.ncu_facts("gauss_jordan_batched_kernel")["stale"] is True
+    assert bench.ncu_facts("simplex_batched_kernel") is None          # no capture at all
+    (csrc / "simplex_single.cu").write_text("// edited\n")             # the kernel changes -> its facts go stale
+    assert bench.ncu_facts("simplex_single_kernel")["stale"] is True
+    (csrc / "host_narrow.cpp").write_text("// host-side edit\n")       # ... but not another file's edit
+    assert bench.ncu_facts("gauss_jordan_batched_kernel")["captured_src_sha16"] == "0123456789abcdef"
