@@ -143,10 +143,17 @@ def test_a_call_allocates_no_device_memory():
                 assert c.run_static(piv, stream) == 0, _lib.lib().lpb200_last_error()
         torch.cuda.synchronize()
     sequence()
-    free_before, _ = torch.cuda.mem_get_info()
     reserved_before = torch.cuda.memory_reserved()
-    sequence()
-    sequence()
-    free_after, _ = torch.cuda.mem_get_info()
-    assert free_after == free_before, "device memory in use changed by %d bytes" % (free_before - free_after)
+    # cudaMemGetInfo is device-wide: something else on the box (a monitor, another process) can move it, so the
+    # claim is checked up to three times and has to hold once -- an allocation by the entry point would show every time
+    deltas = []
+    for _ in range(3):
+        free_before, _ = torch.cuda.mem_get_info()
+        sequence()
+        sequence()
+        free_after, _ = torch.cuda.mem_get_info()
+        deltas.append(free_before - free_after)
+        if deltas[-1] == 0:
+            break
+    assert 0 in deltas, "device memory in use changed on every attempt (bytes): %s" % deltas
     assert torch.cuda.memory_reserved() == reserved_before  # nor did anything go through torch's allocator
