@@ -45,16 +45,30 @@ def one(job):
             "optimum": float(r["optimum"]).hex() if r["optimum"] is not None else None}
 
 
+def one_single(shape):
+    """configs[4]'s generator (workloads.single_lp, seed 5) at sizes the reference can hold: wide tableaus."""
+    n, m = shape
+    A, b, c = workloads.single_lp(n, m, seed=5)
+    r = rh.run_reference(A, b, c, timeout_s=900.0)
+    assert r["status"] is not None
+    return {"dist": "single_lp", "index": 0, "n": n, "m": m, "input_crc": input_crc(A, b, c), "status": r["status"],
+            "npivots": len(r["pivots"]), "pivots": [list(p) for p in r["pivots"]],
+            "x": [float(v).hex() for v in r["x"]] if r["x"] is not None else None,
+            "optimum": float(r["optimum"]).hex() if r["optimum"] is not None else None}
+
+
 def main():
     jobs = [(d, i) for d, cnt in COUNTS for i in range(cnt)]
     jobs.sort(key=lambda j: j[0] == "D1")  # the slow ones first
     with multiprocessing.Pool(os.cpu_count()) as pool:
         cases = pool.map(one, jobs, chunksize=1)
     cases.sort(key=lambda c: (c["dist"], c["index"]))
+    with multiprocessing.Pool(2) as pool:
+        singles = pool.map(one_single, [(128, 256), (256, 512)])
     out = {"meta": {"generator": "tests/golden/make_bench_golden.py", "reference": "week-2/diet/simplex.py (unmodified)",
                     "python": "%d.%d.%d" % sys.version_info[:3], "n": N, "m": M, "seed": 2,
                     "inputs": "linear_programming_b200.workloads.simplex_batch(dist, count, 100, 100, seed=2)[index]"},
-           "cases": cases}
+           "cases": cases, "single_lp_cases": singles}
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "bench_shape_golden.json")
     with open(path, "w") as f:
         json.dump(out, f, separators=(",", ":"))

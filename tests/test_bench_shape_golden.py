@@ -105,3 +105,30 @@ def test_grid_wide_kernel_at_the_headline_shape(bench_golden, monkeypatch):
             sh = solve_sharded_emulated(A[i], b[i], c[i], 4, max_pivots=cap, log_cap=cap)
             for g in range(4):
                 _check_result(sh, g, k, "4 ranks, rank %d %s/%d" % (g, dist, i))
+
+
+def test_oracle_on_the_config5_generator(oracle_lib, bench_golden):
+    """workloads.single_lp (the generator of BASELINE.json configs[4]) at the sizes the Python reference can hold."""
+    for k in bench_golden["single_lp_cases"]:
+        A, b, c = workloads.single_lp(k["n"], k["m"], seed=5)
+        assert _crc(A, b, c) == k["input_crc"]
+        r = oracle_lib.simplex(A, b, c, max_pivots=100000)
+        assert r["status"] == k["status"] and [list(p) for p in r["pivots"]] == k["pivots"]
+        assert [float(v).hex() for v in r["x"]] == k["x"] and float(r["objective"]).hex() == k["optimum"]
+
+
+@pytest.mark.gpu
+def test_grid_wide_and_sharded_kernel_on_the_config5_generator(bench_golden):
+    """The grid-wide kernel (pipelined loop, default grid) and 2 / 8 emulated column-sharded ranks against the reference's
+    own answers on config 5's generator: status, pivot sequence, x and optimum bits."""
+    import linear_programming_b200 as lp
+    from linear_programming_b200.sharded import solve_sharded_emulated
+    for k in bench_golden["single_lp_cases"]:
+        A, b, c = workloads.single_lp(k["n"], k["m"], seed=5)
+        cap = k["npivots"] + 4
+        res = lp.solve_batch(A[None], b[None], c[None], mode="single", max_pivots=cap, log_cap=cap)
+        _check_result(res, 0, k, "single %dx%d" % (k["n"], k["m"]))
+        for nranks in (2, 8):
+            sh = solve_sharded_emulated(A, b, c, nranks, max_pivots=cap, log_cap=cap)
+            for g in range(nranks):
+                _check_result(sh, g, k, "%d ranks, rank %d, %dx%d" % (nranks, g, k["n"], k["m"]))
