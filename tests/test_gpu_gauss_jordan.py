@@ -141,3 +141,19 @@ def test_per_system_status_finds_the_singular_systems(oracle_lib, n, pivoting):
                                      return_status=True)
     assert np.array_equal(sd.cpu().numpy(), want_status)
     assert np.array_equal(xd.cpu().numpy()[good].view(np.int64), want.view(np.int64))
+
+
+def test_engine_vs_the_compiled_reference_at_config3_size(oracle_lib):
+    """Straight against the UNMODIFIED reference (energy_values.cc compiled with its own flags, oracle/_ref -- it travels
+    to the GPU box), not through the restatement: 8 systems of 512 x 512 (BASELINE.json configs[2]), most with a planted
+    zero pivot, through both entry points of the engine."""
+    import linear_programming_b200 as lp
+    if not oracle_lib.ref_gauss_jordan_available():
+        pytest.skip("oracle/_ref not built (no reference tree where the repository was built)")
+    a, b = workloads.gauss_jordan_batch(8, n=512, seed=13, swap_frac=0.75)
+    want = np.stack([oracle_lib.ref_gauss_jordan(a[i], b[i]) for i in range(8)])
+    got = lp.solve_equation_batch(a, b)
+    assert np.array_equal(got.view(np.int64), want.view(np.int64))
+    import torch
+    xd, st = lp.solve_equation_batch(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda(), return_status=True)
+    assert np.array_equal(xd.cpu().numpy().view(np.int64), want.view(np.int64)) and bool((st == -1).all())

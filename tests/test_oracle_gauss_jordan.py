@@ -119,3 +119,16 @@ def test_partial_pivoting_equals_reference_rule_when_diagonal_dominates(oracle_l
     x0, _ = oracle_lib.gauss_jordan_batch(a, b)
     x1, _ = oracle_lib.gauss_jordan_batch(a, b, pivoting="partial")
     assert np.array_equal(x0.view(np.int64), x1.view(np.int64))
+
+
+@pytest.mark.parametrize("n,count", [(256, 3), (512, 4)])
+def test_live_reference_at_config3_size(oracle_lib, n, count):
+    """The compiled, unmodified energy_values.cc (oracle/_ref) at the size BASELINE.json configs[2] names, with planted
+    zero pivots (its row swap, :100-110): both forms of the restatement reproduce every bit."""
+    if not oracle_lib.ref_gauss_jordan_available():
+        pytest.skip("oracle/_ref not built (no reference tree on this machine)")
+    a, b = workloads.gauss_jordan_batch(count, n=n, seed=12, swap_frac=0.75)
+    for i in range(count):
+        ref = oracle_lib.ref_gauss_jordan(a[i], b[i])
+        assert np.array_equal(ref.view(np.int64), oracle_lib.gauss_jordan(a[i], b[i], full_sweep=True).view(np.int64))
+        assert np.array_equal(ref.view(np.int64), oracle_lib.gauss_jordan(a[i], b[i], full_sweep=False).view(np.int64))
